@@ -1,0 +1,100 @@
+/* libmixfe -- B200-native (sm_100a) DSP front end for stem-aware mixing-style learning.
+ *
+ * C ABI of the drop-in boundary.  The reference (barry-mir/mixing-style-transfer) has no FFI
+ * layer of its own; each entry point below names the reference Python interface it replaces
+ * (paths relative to the reference checkout).  All pointers marked "device" are CUDA device
+ * pointers on the plan's device; every call is stream-ordered and asynchronous on `cuda_stream`
+ * (a cudaStream_t passed as void*), never synchronises the host in steady state and never
+ * allocates once the plan's workspace has reached its high-water mark.
+ *
+ * Return value: 0 on success, a negative MIXFE_E* code on failure; mixfe_last_error() returns a
+ * thread-local human-readable message for the last failure on the calling thread.
+ */
+#ifndef MIXFE_H
+#define MIXFE_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIXFE_ABI_VERSION 1
+
+#define MIXFE_OK 0
+#define MIXFE_EINVAL (-1)       /* bad argument (shape, stride, NULL) */
+#define MIXFE_EUNSUPPORTED (-2) /* configuration the kernels do not cover */
+#define MIXFE_ECUDA (-3)        /* CUDA runtime error (message has the cudaError string) */
+#define MIXFE_ESHORT (-4)       /* T <= n_fft/2: reflect padding impossible (torch.stft raises RuntimeError) */
+
+#define MIXFE_NUM_STEMS 4   /* vocals, bass, drums, other -- src/model.py:54, src/mixing_utils.py:287 */
+
+typedef struct mixfe_plan mixfe_plan;
+
+/* Augmentation decisions for ONE clip, drawn on the host in the reference's order
+ * (src/mixing_utils.py:372-419; RNG draw order in SURVEY.md section 3.5).  Index = stem in dict
+ * order vocals, bass, drums, other. */
+typedef struct mixfe_aug_params {
+    float gain_lin[MIXFE_NUM_STEMS];     /* 10^(gain_db/20) as fp32, 1.0f when the gain gate did not fire (:389-392) */
+    int tilt_on[MIXFE_NUM_STEMS];        /* spectral-tilt gate (:395) */
+    double tilt_sos[MIXFE_NUM_STEMS][6]; /* one biquad b0 b1 b2 a0 a1 a2 = scipy butter(2, ...) (:426-429) */
+    int comp_on[MIXFE_NUM_STEMS];        /* static compressor gate (:399), threshold -20 dB ratio 4 (:435) */
+    int bw_on[MIXFE_NUM_STEMS];          /* bandwidth-limit gate (:403) */
+    double bw_sos[MIXFE_NUM_STEMS][12];  /* two biquads = scipy butter(4, cutoff, 'low') (:452) */
+    int reverb_on;                       /* reverb gate (:409); impulse row must be valid when set */
+    int _pad;
+} mixfe_aug_params;
+
+int mixfe_abi_version(void);
+const char* mixfe_last_error(void);
+
+/* Replaces MixingFeatureExtractor.__init__ (src/mixing_utils.py:19-51) and
+ * MelSpectrogramPreprocessor.__init__ (src/model.py:25-39): builds the device-side constants
+ * (FFT twiddles, 2-tap sparse mel table from an HTK filterbank with f_min=0, f_max=sr/2,
+ * norm=None) for one (sample_rate, n_fft, hop, n_mels).  n_spectral_bins = 0 selects the 3-band
+ * spectral features (D = 64), > 0 the detailed curve (D = 4*(n_bins+2+9)+8, :53-69). */
+int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, int hop,
+                      int n_mels, int n_spectral_bins);
+int mixfe_plan_destroy(mixfe_plan* plan);
+
+/* Optional: replace the plan's filterbank by a host matrix fb[n_fft/2+1][n_mels] (row-major),
+ * e.g. the `mel_scale.fb` buffer of a reference checkpoint. */
+int mixfe_plan_set_filterbank(mixfe_plan* plan, const float* fb_host);
+
+int mixfe_feature_dim(const mixfe_plan* plan);          /* get_feature_dim(), src/mixing_utils.py:53-69 */
+int mixfe_num_frames(const mixfe_plan* plan, int T);    /* 1 + T / hop (center=True framing of torch.stft) */
+size_t mixfe_workspace_bytes(const mixfe_plan* plan);   /* current size of the plan-owned device workspace */
+
+/* Replaces MixingFeatureExtractor.extract_all_features (src/mixing_utils.py:71-105, per clip) and
+ * MelSpectrogramPreprocessor.forward (src/model.py:41-67, batched) in ONE pass over the audio.
+ *   stems[s]        device, fp32; element (b, c, t) of stem s at stems[s][b*stride_b + c*stride_c + t]
+ *   features        device [B][D] fp32 in the reference's sorted-key layout (:320-357), or NULL
+ *   logmel          device, (b, ch, m, f) at logmel[b*logmel_stride_b + (ch*n_mels + m)*F + f],
+ *                   ch = 2*stem + channel, F = mixfe_num_frames(T); natural log of (mel power + 1e-10); or NULL
+ * Returns MIXFE_ESHORT when T <= n_fft/2. */
+int mixfe_features_logmel(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
+                          long long stride_b, long long stride_c, int B, int T,
+                          float* features, float* logmel, long long logmel_stride_b,
+                          void* cuda_stream);
+
+/* Replaces AudioAugmenter.augment_stems (src/mixing_utils.py:372-419) for B clips with the
+ * decisions of `params` (host array of B entries).  in/out use the same addressing as above;
+ * out must not alias in.  impulse: device [B][L] fp32 reverb impulses (row b read only when
+ * params[b].reverb_on), L = int(sample_rate*0.5) in the reference (:460). */
+int mixfe_augment(mixfe_plan* plan, const float* const in[MIXFE_NUM_STEMS],
+                  float* const out[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,
+                  int B, int T, const mixfe_aug_params* params, const float* impulse, int L,
+                  void* cuda_stream);
+
+/* Test hook: mel POWER (before the log) for every channel, same addressing as logmel. */
+int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
+                          long long stride_b, long long stride_c, int B, int T,
+                          float* melpow, long long melpow_stride_b, void* cuda_stream);
+
+/* Number of kernel launches issued through this library since load (bench.py's gpu_launches). */
+long long mixfe_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIXFE_H */

@@ -1,0 +1,243 @@
+"""ctypes binding of libmixfe.so (include/mixfe.h) and its in-tree nvcc build.
+
+There is NO CPU fallback: if the shared library is missing or cannot be loaded, every entry point
+raises.  Tensors are only used here as owners of device memory; the arithmetic is in csrc/.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+from typing import Optional, Sequence
+
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_REPO = os.path.dirname(_PKG)
+CSRC = os.path.join(_PKG, "csrc")
+LIB_PATH = os.path.join(_PKG, "libmixfe.so")
+INCLUDE = os.path.join(_REPO, "include", "mixfe.h")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+STEMS = ("vocals", "bass", "drums", "other")   # reference: src/model.py:54, src/mixing_utils.py:287
+
+E_INVAL, E_UNSUPPORTED, E_CUDA, E_SHORT = -1, -2, -3, -4
+
+
+def _sources():
+    out = [INCLUDE]
+    for f in sorted(os.listdir(CSRC)):
+        if f.endswith((".cu", ".cuh", ".h")):
+            out.append(os.path.join(CSRC, f))
+    return out
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/mixfe.cu for sm_100a into libmixfe.so next to this file (needs nvcc, no GPU)."""
+    newest = max(os.path.getmtime(p) for p in _sources())
+    if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", LIB_PATH, os.path.join(CSRC, "mixfe.cu")]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+class AugParams(ctypes.Structure):
+    """mixfe_aug_params (include/mixfe.h)."""
+    _fields_ = [
+        ("gain_lin", ctypes.c_float * 4),
+        ("tilt_on", ctypes.c_int * 4),
+        ("tilt_sos", (ctypes.c_double * 6) * 4),
+        ("comp_on", ctypes.c_int * 4),
+        ("bw_on", ctypes.c_int * 4),
+        ("bw_sos", (ctypes.c_double * 12) * 4),
+        ("reverb_on", ctypes.c_int),
+        ("_pad", ctypes.c_int),
+    ]
+
+
+_lib: Optional[ctypes.CDLL] = None
+_lock = threading.Lock()
+
+# every symbol include/mixfe.h declares (tests check the library exports all of them)
+EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_plan_destroy",
+           "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
+           "mixfe_features_logmel", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count")
+
+
+def lib() -> ctypes.CDLL:
+    """Load libmixfe.so (once).  Raises RuntimeError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: the CUDA extension has not been built "
+                "(run `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        vp, ll, ci = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int
+        L.mixfe_abi_version.restype = ci
+        L.mixfe_last_error.restype = ctypes.c_char_p
+        L.mixfe_plan_create.argtypes = [ctypes.POINTER(vp), ci, ci, ci, ci, ci, ci]
+        L.mixfe_plan_destroy.argtypes = [vp]
+        L.mixfe_plan_set_filterbank.argtypes = [vp, vp]
+        L.mixfe_feature_dim.argtypes = [vp]
+        L.mixfe_num_frames.argtypes = [vp, ci]
+        L.mixfe_workspace_bytes.argtypes = [vp]
+        L.mixfe_workspace_bytes.restype = ctypes.c_size_t
+        L.mixfe_features_logmel.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp, ll, vp]
+        L.mixfe_debug_mel_power.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, vp]
+        L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
+                                    ctypes.POINTER(AugParams), vp, ci, vp]
+        L.mixfe_launch_count.restype = ll
+        _lib = L
+    return _lib
+
+
+def launch_count() -> int:
+    return int(lib().mixfe_launch_count())
+
+
+def _check(rc: int) -> None:
+    if rc == 0:
+        return
+    msg = lib().mixfe_last_error().decode("utf-8", "replace")
+    if rc == E_SHORT:
+        raise RuntimeError(msg)                 # what torch.stft's reflect pad raises in the reference
+    if rc == E_INVAL:
+        raise ValueError(msg)
+    if rc == E_UNSUPPORTED:
+        raise NotImplementedError(msg)
+    raise RuntimeError(f"libmixfe error {rc}: {msg}")
+
+
+def _ptr(t: Optional[torch.Tensor]) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream(device: torch.device) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def unify_stems(stems: Sequence[torch.Tensor]):
+    """4 x (B,2,T) CUDA fp32 tensors with unit time stride and a COMMON (batch, channel) stride."""
+    st = [s if (s.dtype == torch.float32) else s.float() for s in stems]
+    shape = st[0].shape
+    for s in st:
+        if s.shape != shape:
+            raise ValueError(f"stems have different shapes: {tuple(s.shape)} vs {tuple(shape)}")
+    strides = {(s.stride(0), s.stride(1), s.stride(2)) for s in st}
+    ok = len(strides) == 1 and st[0].stride(2) == 1 and st[0].stride(1) >= shape[2] and \
+        (shape[0] == 1 or st[0].stride(0) >= shape[2])
+    if not ok:
+        st = [s.contiguous() for s in st]
+    return st, st[0].stride(0), st[0].stride(1)
+
+
+class Plan:
+    """Owner of a mixfe_plan (constant tables + workspace) bound to one CUDA device."""
+
+    def __init__(self, device: torch.device, sample_rate: int, n_fft: int, hop: int, n_mels: int,
+                 n_spectral_bins: int = 0, fb: Optional[torch.Tensor] = None):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("libmixfe plans live on CUDA devices; there is no CPU path")
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        torch.cuda.init()
+        with torch.cuda.device(idx):
+            torch.cuda.current_stream()          # make sure the primary context exists
+            h = ctypes.c_void_p()
+            _check(lib().mixfe_plan_create(ctypes.byref(h), idx, sample_rate, n_fft, hop, n_mels, n_spectral_bins))
+        self._h = h
+        self.n_mels = n_mels
+        self.hop = hop
+        self.n_fft = n_fft
+        self.feature_dim = int(lib().mixfe_feature_dim(self._h))
+        if fb is not None:
+            self.set_filterbank(fb)
+
+    def set_filterbank(self, fb: torch.Tensor) -> None:
+        fb = fb.detach().to("cpu", torch.float32).contiguous()
+        if tuple(fb.shape) != (self.n_fft // 2 + 1, self.n_mels):
+            raise ValueError(f"filterbank shape {tuple(fb.shape)}")
+        _check(lib().mixfe_plan_set_filterbank(self._h, ctypes.c_void_p(fb.data_ptr())))
+
+    def num_frames(self, T: int) -> int:
+        return 1 + T // self.hop
+
+    def workspace_bytes(self) -> int:
+        return int(lib().mixfe_workspace_bytes(self._h))
+
+    def features_logmel(self, stems: Sequence[torch.Tensor], want_features: bool = True,
+                        want_logmel: bool = True, features_out: Optional[torch.Tensor] = None,
+                        logmel_out: Optional[torch.Tensor] = None):
+        """stems: 4 CUDA tensors (B,2,T).  Returns (features (B,D) | None, logmel (B,8,n_mels,F) | None)."""
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        F = self.num_frames(T)
+        feats = lm = None
+        if want_features:
+            feats = features_out if features_out is not None else \
+                torch.empty((B, self.feature_dim), dtype=torch.float32, device=self.device)
+        if want_logmel:
+            lm = logmel_out if logmel_out is not None else \
+                torch.empty((B, 8, self.n_mels, F), dtype=torch.float32, device=self.device)
+            if lm.stride(3) != 1 or lm.stride(2) != F or lm.stride(1) != self.n_mels * F:
+                raise ValueError("logmel_out must be contiguous in its last three dims")
+        ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_features_logmel(self._h, ptrs, sb, sc, B, T, _ptr(feats), _ptr(lm),
+                                               0 if lm is None else lm.stride(0), _stream(self.device)))
+        return feats, lm
+
+    def debug_mel_power(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        out = torch.empty((B, 8, self.n_mels, self.num_frames(T)), dtype=torch.float32, device=self.device)
+        ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_debug_mel_power(self._h, ptrs, sb, sc, B, T, _ptr(out), out.stride(0),
+                                               _stream(self.device)))
+        return out
+
+    def augment(self, stems: Sequence[torch.Tensor], params, impulse: Optional[torch.Tensor]):
+        """stems: 4 CUDA tensors (B,2,T); params: ctypes array of B AugParams; impulse (B,L) or None."""
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        outs = [torch.empty_strided(s.shape, s.stride(), dtype=torch.float32, device=self.device) for s in st]
+        pin = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        pout = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in outs])
+        L = 0
+        if impulse is not None:
+            impulse = impulse.to(self.device, torch.float32).contiguous()
+            L = impulse.shape[-1]
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_augment(self._h, pin, pout, sb, sc, B, T, params, _ptr(impulse), L,
+                                       _stream(self.device)))
+        return outs
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            try:
+                lib().mixfe_plan_destroy(self._h)
+            finally:
+                self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,52 @@
+// The plan object behind the opaque mixfe_plan handle of include/mixfe.h.
+#pragma once
+
+#include "common.cuh"
+
+struct mixfe_plan {
+    int device = 0, sr = 0, n_fft = 0, hop = 0, n_mels = 0, n_mels_pad = 0, n_bins = 0, D = 0, n_freq = 0;
+    std::vector<float> fb;              // host [n_freq][n_mels]
+    // device constant tables
+    float2* d_tw = nullptr;
+    float2* d_twfine = nullptr;         // exp(-2 pi i e / 2^20), e in [0, 1024): fine twiddles of the long FFT
+    int* d_frow0 = nullptr;
+    int2* d_gdesc = nullptr;
+    float2* d_gw = nullptr;
+    unsigned char* d_wtab = nullptr;
+    int n_groups = 0, nw2 = 0;
+    // K1 shared-memory map
+    int nxs = 0, smem_k1 = 0;
+    int off_ex = 0, off_tw = 0, off_s = 0, off_frow0 = 0, off_gdesc = 0, off_gw = 0, off_wtab = 0, off_red = 0;
+    // plan-owned workspace (grows to the high-water mark, then never reallocates)
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    void* aug_params_dev = nullptr;     // device copy of the per-clip augmentation decisions
+    void* aug_params_host = nullptr;    // pinned staging buffer for them
+    size_t aug_params_cap = 0;
+};
+
+namespace mixfe {
+
+inline int ensure_workspace(mixfe_plan* pl, size_t bytes, cudaStream_t stream) {
+    if (bytes <= pl->ws_bytes) return MIXFE_OK;
+    if (pl->ws) {
+        MIXFE_CUDA(cudaStreamSynchronize(stream));      // growth only: the old buffer may still be in use
+        MIXFE_CUDA(cudaFree(pl->ws));
+        pl->ws = nullptr;
+        pl->ws_bytes = 0;
+    }
+    MIXFE_CUDA(cudaMalloc(&pl->ws, bytes));
+    pl->ws_bytes = bytes;
+    return MIXFE_OK;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev); else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace mixfe
