@@ -94,6 +94,17 @@ int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
 /* Number of kernel launches issued through this library since load (bench.py's gpu_launches). */
 long long mixfe_launch_count(void);
 
+/* Measurement hook: when enabled, every launch of the plan's kernels is bracketed by CUDA events on the
+ * launching stream.  mixfe_plan_kernel_time() synchronises those events, returns the accumulated device
+ * time (ms) and launch count of kernel `which` since the last query, and resets the accumulator. */
+#define MIXFE_KERNEL_FEATURES 0   /* K1: fused STFT/mel/log/statistics */
+#define MIXFE_KERNEL_FINALIZE 1   /* K2: per-clip feature finalize */
+#define MIXFE_KERNEL_AUGMENT 2    /* K3: gain/biquad/compressor scan */
+#define MIXFE_KERNEL_REVERB 3     /* K4/K5: FFT-domain reverb + redistribution (all its launches) */
+#define MIXFE_NUM_KERNELS 4
+int mixfe_plan_enable_timing(mixfe_plan* plan, int enable);
+int mixfe_plan_kernel_time(mixfe_plan* plan, int which, double* total_ms, long long* launches);
+
 #ifdef __cplusplus
 }
 #endif

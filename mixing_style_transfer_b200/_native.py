@@ -71,7 +71,8 @@ _lock = threading.Lock()
 # every symbol include/mixfe.h declares (tests check the library exports all of them)
 EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_plan_destroy",
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
-           "mixfe_features_logmel", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count")
+           "mixfe_features_logmel", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
+           "mixfe_plan_enable_timing", "mixfe_plan_kernel_time")
 
 
 def lib() -> ctypes.CDLL:
@@ -102,6 +103,8 @@ def lib() -> ctypes.CDLL:
         L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
                                     ctypes.POINTER(AugParams), vp, ci, vp]
         L.mixfe_launch_count.restype = ll
+        L.mixfe_plan_enable_timing.argtypes = [vp, ci]
+        L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
     return _lib
 
@@ -228,6 +231,17 @@ class Plan:
             _check(lib().mixfe_augment(self._h, pin, pout, sb, sc, B, T, params, _ptr(impulse), L,
                                        _stream(self.device)))
         return outs
+
+    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3}
+
+    def enable_timing(self, on: bool = True) -> None:
+        _check(lib().mixfe_plan_enable_timing(self._h, 1 if on else 0))
+
+    def kernel_time(self, which: str):
+        """(total device ms, launches) of kernel family `which` since the last query (CUDA events)."""
+        ms, n = ctypes.c_double(), ctypes.c_longlong()
+        _check(lib().mixfe_plan_kernel_time(self._h, self.KERNELS[which], ctypes.byref(ms), ctypes.byref(n)))
+        return ms.value, n.value
 
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:

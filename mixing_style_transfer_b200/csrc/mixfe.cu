@@ -153,7 +153,10 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     p.wtab = pl->d_wtab; p.want_stats = features ? 1 : 0;
     p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_frow0 = pl->off_frow0;
     p.off_gdesc = pl->off_gdesc; p.off_gw = pl->off_gw; p.off_wtab = pl->off_wtab; p.off_red = pl->off_red;
-    k1_features<<<dim3(n_tiles, B), kK1Threads, pl->smem_k1, stream>>>(p);
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
+        k1_features<<<dim3(n_tiles, B), kK1Threads, pl->smem_k1, stream>>>(p);
+    }
     MIXFE_CUDA(cudaGetLastError());
     launch_counter()++;
     if (features) {
@@ -161,7 +164,10 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         q.part_spec = p.part_spec; q.part_td = p.part_td; q.features = features;
         q.B = B; q.T = T; q.F = F; q.n_mels = pl->n_mels; q.n_mels_pad = pl->n_mels_pad; q.n_tiles = n_tiles;
         q.n_bins = pl->n_bins; q.D = pl->D;
-        k2_finalize<<<B, kK2Threads, 0, stream>>>(q);
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_FINALIZE, stream);
+            k2_finalize<<<B, kK2Threads, 0, stream>>>(q);
+        }
         MIXFE_CUDA(cudaGetLastError());
         launch_counter()++;
     }
@@ -239,6 +245,32 @@ int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
     MIXFE_CUDA(cudaDeviceSynchronize());            // tables may be in use by queued launches
     pl->fb.assign(fb_host, fb_host + (size_t)pl->n_freq * pl->n_mels);
     return build_mel_tables(pl);
+}
+
+int mixfe_plan_enable_timing(mixfe_plan* pl, int enable) {
+    if (!pl) return fail(MIXFE_EINVAL, "null plan");
+    pl->timing = enable != 0;
+    return MIXFE_OK;
+}
+
+int mixfe_plan_kernel_time(mixfe_plan* pl, int which, double* total_ms, long long* launches) {
+    if (!pl || which < 0 || which >= MIXFE_NUM_KERNELS) return fail(MIXFE_EINVAL, "bad plan or kernel id");
+    DeviceGuard guard(pl->device);
+    double tot = 0.0;
+    long long n = 0;
+    for (auto& pr : pl->ev[which]) {
+        MIXFE_CUDA(cudaEventSynchronize(pr.second));
+        float ms = 0.0f;
+        MIXFE_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+        tot += ms;
+        ++n;
+        cudaEventDestroy(pr.first);
+        cudaEventDestroy(pr.second);
+    }
+    pl->ev[which].clear();
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = n;
+    return MIXFE_OK;
 }
 
 int mixfe_feature_dim(const mixfe_plan* pl) { return pl ? pl->D : fail(MIXFE_EINVAL, "null plan"); }

@@ -23,6 +23,9 @@ struct mixfe_plan {
     void* aug_params_dev = nullptr;     // device copy of the per-clip augmentation decisions
     void* aug_params_host = nullptr;    // pinned staging buffer for them
     size_t aug_params_cap = 0;
+    // optional per-kernel timing (bench.py): event pairs recorded around launches, drained on query
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[MIXFE_NUM_KERNELS];
 };
 
 namespace mixfe {
@@ -39,6 +42,24 @@ inline int ensure_workspace(mixfe_plan* pl, size_t bytes, cudaStream_t stream) {
     pl->ws_bytes = bytes;
     return MIXFE_OK;
 }
+
+// RAII bracket: records an event pair around the launches issued in its scope when timing is on.
+struct KernelTimer {
+    mixfe_plan* pl;
+    int which;
+    cudaStream_t stream;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    KernelTimer(mixfe_plan* p, int w, cudaStream_t s) : pl(p), which(w), stream(s) {
+        if (pl->timing && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess)
+            cudaEventRecord(e0, stream);
+    }
+    ~KernelTimer() {
+        if (e0 && e1) {
+            cudaEventRecord(e1, stream);
+            pl->ev[which].emplace_back(e0, e1);
+        }
+    }
+};
 
 struct DeviceGuard {
     int prev = -1;

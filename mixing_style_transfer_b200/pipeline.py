@@ -1,0 +1,77 @@
+"""Host-resident batches: chunked H2D -> kernels -> D2H with the three legs overlapped.
+
+The reference computes features in DataLoader workers on CPU tensors (src/data.py:231-265) and ships
+stems to the GPU afterwards (src/train.py:231).  With the front end on the GPU the stems cross PCIe
+first; this helper is the user-facing call for that case: pinned host stems in, pinned host features
+and log-mels out, copies of chunk i+1 and i-1 overlapping the kernels of chunk i.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from ._native import STEMS
+
+
+class HostPipeline:
+    def __init__(self, extractor, n_clips: int, T: int, chunk: int = 12, device=None, with_logmel: bool = True):
+        self.fe = extractor
+        self.device = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
+        self.plan = extractor._plan(self.device)
+        self.n, self.T, self.chunk = n_clips, T, max(1, min(chunk, n_clips))
+        self.with_logmel = with_logmel
+        F = self.plan.num_frames(T)
+        # two device slots so that chunk i+1 uploads while chunk i computes
+        self.slots = []
+        for _ in range(2):
+            self.slots.append({
+                "stems": [torch.empty((self.chunk, 2, T), dtype=torch.float32, device=self.device) for _ in STEMS],
+                "feat": torch.empty((self.chunk, self.plan.feature_dim), dtype=torch.float32, device=self.device),
+                "lm": torch.empty((self.chunk, 8, self.plan.n_mels, F), dtype=torch.float32, device=self.device)
+                if with_logmel else None,
+                "uploaded": torch.cuda.Event(), "computed": torch.cuda.Event(), "drained": torch.cuda.Event(),
+            })
+        self.s_up = torch.cuda.Stream(self.device)
+        self.s_run = torch.cuda.Stream(self.device)
+        self.s_down = torch.cuda.Stream(self.device)
+        self.h2d_bytes = 4 * 2 * T * 4 * n_clips
+        self.d2h_bytes = 4 * n_clips * (self.plan.feature_dim + (8 * self.plan.n_mels * F if with_logmel else 0))
+
+    @staticmethod
+    def pinned_like(shape) -> torch.Tensor:
+        return torch.empty(shape, dtype=torch.float32, pin_memory=True)
+
+    def run(self, host_stems: Dict[str, torch.Tensor], feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
+        """host_stems: dict of pinned (N,2,T); feat_out pinned (N,D); lm_out pinned (N,8,n_mels,F) or None.
+        Returns after everything has landed in host memory."""
+        cur = torch.cuda.current_stream(self.device)
+        for s in (self.s_up, self.s_run, self.s_down):
+            s.wait_stream(cur)
+        n_chunks = (self.n + self.chunk - 1) // self.chunk
+        for i in range(n_chunks):
+            lo, hi = i * self.chunk, min(self.n, (i + 1) * self.chunk)
+            m = hi - lo
+            slot = self.slots[i & 1]
+            with torch.cuda.stream(self.s_up):
+                if i >= 2:
+                    self.s_up.wait_event(slot["computed"])       # kernels of chunk i-2 have consumed the slot
+                for d, name in zip(slot["stems"], STEMS):
+                    d[:m].copy_(host_stems[name][lo:hi], non_blocking=True)
+                slot["uploaded"].record(self.s_up)
+            with torch.cuda.stream(self.s_run):
+                self.s_run.wait_event(slot["uploaded"])
+                if i >= 2:
+                    self.s_run.wait_event(slot["drained"])        # outputs of chunk i-2 have left the slot
+                self.plan.features_logmel([d[:m] for d in slot["stems"]], True, self.with_logmel,
+                                          features_out=slot["feat"][:m],
+                                          logmel_out=slot["lm"][:m] if self.with_logmel else None)
+                slot["computed"].record(self.s_run)
+            with torch.cuda.stream(self.s_down):
+                self.s_down.wait_event(slot["computed"])
+                feat_out[lo:hi].copy_(slot["feat"][:m], non_blocking=True)
+                if self.with_logmel:
+                    lm_out[lo:hi].copy_(slot["lm"][:m], non_blocking=True)
+                slot["drained"].record(self.s_down)
+        self.s_down.synchronize()
+        self.s_run.synchronize()
