@@ -64,6 +64,12 @@ struct K1Params {
     int off_ex, off_tw, off_s, off_frow0, off_gdesc, off_gw, off_wtab, off_red;
 };
 
+__device__ __forceinline__ float ln_fast(float x) {               // x >= 1e-10: never denormal
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y * 0.69314718055994531f;
+}
+
 __device__ __forceinline__ float fast_sigmoid_neg(float x) {     // 1 / (1 + exp(x))
     return __fdividef(1.0f, 1.0f + __expf(x));
 }
@@ -272,22 +278,30 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 const int m = 4 * g + q;
                 const float* prow = pt + frow0[m] * kPRS + 4 * j8;
                 const float2* wp = gw + gd.y + q;
-                float a0 = 0.0f, a1 = 0.0f;
-#pragma unroll 4
-                for (int j = 0; j < gd.x; ++j) {
+                float a0 = 0.0f, a1 = 0.0f, c0 = 0.0f, c1 = 0.0f;
+                for (int j = 0; j < gd.x; j += 2) {          // gd.x is even (host pads with zero taps)
                     const float4 v = *reinterpret_cast<const float4*>(prow + j * kPRS);
+                    const float4 u = *reinterpret_cast<const float4*>(prow + (j + 1) * kPRS);
                     const float2 w = wp[4 * j];
+                    const float2 x = wp[4 * j + 4];
                     a0 = fmaf(w.x, v.x, a0);
-                    a0 = fmaf(w.y, v.y, a0);
                     a1 = fmaf(w.x, v.z, a1);
+                    c0 = fmaf(x.x, u.x, c0);
+                    c1 = fmaf(x.x, u.z, c1);
+                    a0 = fmaf(w.y, v.y, a0);
                     a1 = fmaf(w.y, v.w, a1);
+                    c0 = fmaf(x.y, u.y, c0);
+                    c1 = fmaf(x.y, u.w, c1);
                 }
+                a0 += c0;
+                a1 += c1;
                 *reinterpret_cast<float2*>(meltile + m * 16 + 2 * j8) = make_float2(a0, a1);
             }
         }
         __syncthreads();
 
         // ---- epilogue A: logs, spectral partial sums, S tiles / masking ----------------------
+        const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;          // frames of this tile that exist
         for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
             const int m = r >> 1, ch = r & 1;
             const float4 v0 = *reinterpret_cast<const float4*>(meltile + m * 16 + ch * 8);
@@ -296,11 +310,17 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             float lg[8];
             float slog = 0.0f, smel = 0.0f;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                lg[t] = __logf(v[t] + 1e-10f);
-                if (t0 + t < p.F) {
-                    slog += lg[t];
-                    smel += v[t];
+            for (int t = 0; t < 8; ++t) lg[t] = ln_fast(v[t] + 1e-10f);
+            if (nvalid == kTF) {
+                slog = ((lg[0] + lg[1]) + (lg[2] + lg[3])) + ((lg[4] + lg[5]) + (lg[6] + lg[7]));
+                smel = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+            } else {
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    if (t < nvalid) {
+                        slog += lg[t];
+                        smel += v[t];
+                    }
                 }
             }
             *reinterpret_cast<float4*>(logtile + m * 16 + ch * 8) = make_float4(lg[0], lg[1], lg[2], lg[3]);
@@ -328,7 +348,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     const float s2[4] = {A2.x, A2.y, A2.z, A2.w}, s3[4] = {Sc.x, Sc.y, Sc.z, Sc.w};
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        if (t0 + 4 * h + i < p.F) {
+                        if (4 * h + i < nvalid) {
                             const float m01 = fmaxf(s0[i], s1[i]), m23 = fmaxf(s2[i], s3[i]);
                             // sigmoid(max_{j != i} S_j - S_i) = 1 / (1 + exp(S_i - max_others))
                             msum[0] += fast_sigmoid_neg(s0[i] - fmaxf(s1[i], m23));
@@ -344,13 +364,20 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
 
         // ---- epilogue B: coalesced store of the log-mel tile (32-byte runs along time) --------
         {
-            const int n = p.n_mels * 16;
-            for (int i = tid; i < n; i += kK1Threads) {
-                const int m = i >> 4, col = i & 15, ch = col >> 3, t = col & 7;
-                if (t0 + t < p.F) {
-                    const long long o = ((long long)(2 * s + ch) * p.n_mels + m) * p.F + t0 + t;
-                    if (p.logmel) p.logmel[(long long)b * p.lm_stride_b + o] = logtile[i];
-                    if (p.melpow) p.melpow[(long long)b * p.mp_stride_b + o] = meltile[i];
+            const int col = tid & 15, ch = col >> 3, t = col & 7, m0 = tid >> 4;
+            if (t < nvalid) {
+                const long long o = ((long long)(2 * s + ch) * p.n_mels + m0) * p.F + t0 + t;
+                const long long step = 16ll * p.F;
+                if (p.logmel) {
+                    float* dst = p.logmel + (long long)b * p.lm_stride_b + o;
+                    const float* src = logtile + tid;
+#pragma unroll 4
+                    for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kK1Threads) *dst = *src;
+                }
+                if (p.melpow) {
+                    float* dst = p.melpow + (long long)b * p.mp_stride_b + o;
+                    const float* src = meltile + tid;
+                    for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kK1Threads) *dst = *src;
                 }
             }
         }

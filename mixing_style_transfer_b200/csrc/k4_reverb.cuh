@@ -1,1 +1,384 @@
+// K4/K5: stereo reverb of the augmented mixture as an FFT-domain cross-correlation, and the
+// energy-weighted redistribution onto the stems.
+//
+// Reference behaviour being replaced (src/mixing_utils.py of the reference):
+//   :458-479  apply_reverb   F.conv1d(x[None,None], h[None,None], padding=L//2)[..., :T] per channel, i.e. the
+//                            cross-correlation r[n] = sum_k x[n + k - L//2] h[k] with L = 22050 taps
+//                            (22.8 s per call on 8 CPU cores), then 0.7 x + 0.3 r
+//   :409-417  redistribution s_i += mix_rev * (mean(s_i^2) / (sum_j mean(s_j^2) + 1e-8)) * 0.3
+//
+// Method: the mixture's L and R are packed as one complex signal (h is real, so the correlation
+// acts on both parts independently) and correlated with h through a 2^20-point FFT computed as
+// 1024 x 1024 (four-step) with the same one-warp 1024-point transform as the STFT kernel:
+//   columns  (stride-1024 transforms + inter-step twiddle)   k4_cols<kColsX | kColsH>
+//   rows     X: forward, times H, forward again (= inverse of the conjugate), twiddle;  H: forward
+//   columns  last transform, conjugate, 1/N, wet/dry mix and redistribution in the epilogue
+// Frequency-domain data stays in the transposed order the four-step algorithm produces, so no
+// transposition pass exists.  Clips longer than N - L + 1 samples are processed as overlap-save
+// segments.
 #pragma once
+
+#include "fft32.cuh"
+#include "k3_augment.cuh"
+#include "plan.cuh"
+
+namespace mixfe {
+
+constexpr int kRevN1 = 1024, kRevN2 = 1024;
+constexpr int kRevN = kRevN1 * kRevN2;           // 2^20
+constexpr int kColsPerCta = 8;
+constexpr int kColStride = kRevN1 + 4;           // float2 elements per staged column
+
+// One warp, 1024 points: in v[n1] = x[32 n1 + lane]; out v[k2] = X[lane + 32 k2].
+// exw: 1024 float2 of warp-private shared memory; tw[k1*32 + n2] = exp(-2 pi i n2 k1/1024) in shared memory.
+__device__ __forceinline__ void warp_fft1024(float (&re)[32], float (&im)[32], float2* exw, const float2* tw, int lane) {
+    dft32_dif(re, im);
+#pragma unroll
+    for (int k1 = 0; k1 < 32; ++k1) {
+        const float yr = re[brev5(k1)], yi = im[brev5(k1)];
+        float2 o;
+        if (k1 == 0) {
+            o = make_float2(yr, yi);
+        } else {
+            const float2 t = tw[k1 * 32 + lane];
+            o.x = fmaf(yr, t.x, -yi * t.y);
+            o.y = fmaf(yr, t.y, yi * t.x);
+        }
+        exw[k1 * 32 + (lane ^ k1)] = o;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int n2 = 0; n2 < 32; ++n2) {
+        const float2 v = exw[lane * 32 + (n2 ^ lane)];
+        re[n2] = v.x;
+        im[n2] = v.y;
+    }
+    __syncwarp();
+    dft32_dif(re, im);
+    float tr[32], ti[32];
+#pragma unroll
+    for (int k2 = 0; k2 < 32; ++k2) { tr[k2] = re[brev5(k2)]; ti[k2] = im[brev5(k2)]; }
+#pragma unroll
+    for (int k2 = 0; k2 < 32; ++k2) { re[k2] = tr[k2]; im[k2] = ti[k2]; }
+}
+
+// exp(-2 pi i e / 2^20) from two 1024-entry tables: e = 1024 hi + lo.
+__device__ __forceinline__ float2 twiddle_long(const float2* __restrict__ tw_lin, const float2* __restrict__ tw_fine, unsigned e) {
+    const float2 a = __ldg(tw_lin + (e >> 10)), c = __ldg(tw_fine + (e & 1023u));
+    return make_float2(fmaf(a.x, c.x, -a.y * c.y), fmaf(a.x, c.y, a.y * c.x));
+}
+
+struct K4Params {
+    float* out[kNumStems];                 // augmented stems (K3 output); updated in place by the last pass
+    long long stride_b, stride_c;
+    int T, L, half, seg_len, n_seg, n_chunks;
+    const int* slot_clip;                  // [n_slots] clip index of each reverb slot
+    const float* impulse;                  // [B][L]
+    float2* X;                             // [n_slots][n_seg][2^20]
+    float2* H;                             // [n_slots][2^20]
+    const double* part_energy;             // [B][4][2][n_chunks]
+    const float2* tw;                      // [1024] 32x32 twiddles
+    const float2* tw_lin;                  // [1024] exp(-2 pi i j/1024)
+    const float2* tw_fine;                 // [1024] exp(-2 pi i e/2^20)
+};
+
+enum { kColsX = 0, kColsH = 1, kColsInv = 2 };
+
+// grid (128 column groups, n_seg, n_slots); 8 warps, warp w transforms column 8*group + w.
+template <int MODE>
+__global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* const tile = reinterpret_cast<float2*>(smem_raw);                   // [8][kColStride]
+    float2* const tw = tile + kColsPerCta * kColStride;                          // [1024]
+    __shared__ float share[kNumStems];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int col0 = blockIdx.x * kColsPerCta, seg = blockIdx.y, slot = blockIdx.z;
+    const int b = p.slot_clip[slot];
+    const long long seg0 = (long long)seg * p.seg_len;
+    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * kRevN;
+    float2* const Hs = p.H + (long long)slot * kRevN;
+
+    for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
+    if (MODE == kColsInv) {
+        // energy shares of the four stems (recomputed by every CTA: 8 * n_chunks doubles per stem)
+        if (warp < kNumStems) {
+            double e = 0.0;
+            const double* src = p.part_energy + ((long long)b * kNumStems + warp) * 2 * p.n_chunks;
+            for (int i = lane; i < 2 * p.n_chunks; i += 32) e += src[i];
+            e = warp_sum(e);
+            if (lane == 0) share[warp] = (float)(e / (2.0 * (double)p.T));       // mean over (2, T)
+        }
+        __syncthreads();
+        if (tid == 0) {
+            const float tot = ((share[0] + share[1]) + share[2]) + share[3] + 1e-8f;
+            for (int s = 0; s < kNumStems; ++s) share[s] = share[s] / tot;
+        }
+    }
+    // ---- stage 1024 rows x 8 columns ------------------------------------------------------------
+    {
+        const int c = tid & 7;
+        for (int r = tid >> 3; r < kRevN1; r += 32) {
+            const long long n = (long long)r * kRevN2 + col0 + c;
+            float2 v = make_float2(0.0f, 0.0f);
+            if (MODE == kColsX) {
+                const long long t = seg0 - p.half + n;
+                if (t >= 0 && t < p.T) {
+                    const long long o = (long long)b * p.stride_b + t;
+                    float mL = 0.0f, mR = 0.0f;
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {              // ((0 + v) + b) + d) + o
+                        mL += p.out[s][o];
+                        mR += p.out[s][o + p.stride_c];
+                    }
+                    v = make_float2(mL, mR);
+                }
+            } else if (MODE == kColsH) {
+                if (n < p.L) v.x = __ldg(p.impulse + (long long)b * p.L + n);
+            } else {
+                v = Xs[n];
+            }
+            tile[c * kColStride + r] = v;
+        }
+    }
+    __syncthreads();
+    // ---- one column per warp ----------------------------------------------------------------------
+    {
+        float2* const colbuf = tile + warp * kColStride;
+        float re[32], im[32];
+#pragma unroll
+        for (int n1 = 0; n1 < 32; ++n1) {
+            const float2 v = colbuf[32 * n1 + lane];
+            re[n1] = v.x;
+            im[n1] = v.y;
+        }
+        __syncwarp();
+        warp_fft1024(re, im, colbuf, tw, lane);                   // the column's own storage is the exchange buffer
+        const unsigned n2 = (unsigned)(col0 + warp);
+#pragma unroll
+        for (int k2 = 0; k2 < 32; ++k2) {
+            const unsigned k1 = (unsigned)(lane + 32 * k2);       // output index of the column transform
+            float2 o;
+            if (MODE == kColsInv) {
+                o = make_float2(re[k2] * (1.0f / (float)kRevN), -im[k2] * (1.0f / (float)kRevN));
+            } else {
+                const float2 w = twiddle_long(p.tw_lin, p.tw_fine, (n2 * k1) & (unsigned)(kRevN - 1));
+                o = make_float2(fmaf(re[k2], w.x, -im[k2] * w.y), fmaf(re[k2], w.y, im[k2] * w.x));
+            }
+            colbuf[k1] = o;
+        }
+    }
+    __syncthreads();
+    // ---- write back (coalesced 64-byte runs) / reverb epilogue --------------------------------------
+    {
+        const int c = tid & 7;
+        for (int r = tid >> 3; r < kRevN1; r += 32) {
+            const long long n = (long long)r * kRevN2 + col0 + c;
+            const float2 v = tile[c * kColStride + r];
+            if (MODE == kColsX) {
+                Xs[n] = v;
+            } else if (MODE == kColsH) {
+                Hs[n] = v;
+            } else {
+                const long long t = seg0 + n;                        // c[m] is the output sample seg0 + m
+                if (n < p.seg_len && t < p.T) {
+                    const long long o = (long long)b * p.stride_b + t;
+                    float y[kNumStems][2];
+                    float mL = 0.0f, mR = 0.0f;
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {
+                        y[s][0] = p.out[s][o];
+                        y[s][1] = p.out[s][o + p.stride_c];
+                        mL += y[s][0];
+                        mR += y[s][1];
+                    }
+                    const float wetL = mL * 0.7f + v.x * 0.3f, wetR = mR * 0.7f + v.y * 0.3f;      // :478-479
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {
+                        p.out[s][o] = y[s][0] + (wetL * share[s]) * 0.3f;                       // :417
+                        p.out[s][o + p.stride_c] = y[s][1] + (wetR * share[s]) * 0.3f;
+                    }
+                }
+            }
+        }
+    }
+}
+
+enum { kRowsX = 0, kRowsH = 1 };
+
+// grid (128 row groups, n_seg, n_slots); 8 warps, warp w transforms row 8*group + w.
+template <int MODE>
+__global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* const exall = reinterpret_cast<float2*>(smem_raw);                  // [8][1024]
+    float2* const tw = exall + 8 * 1024;                                        // [1024]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int row = blockIdx.x * 8 + warp, seg = blockIdx.y, slot = blockIdx.z;
+    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * kRevN + (long long)row * kRevN2;
+    float2* const Hs = p.H + (long long)slot * kRevN + (long long)row * kRevN2;
+    for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
+    __syncthreads();
+    float2* const exw = exall + warp * 1024;
+    float2* const data = MODE == kRowsH ? Hs : Xs;
+    float re[32], im[32];
+#pragma unroll
+    for (int n1 = 0; n1 < 32; ++n1) {
+        const float2 v = data[32 * n1 + lane];
+        re[n1] = v.x;
+        im[n1] = v.y;
+    }
+    warp_fft1024(re, im, exw, tw, lane);                              // X[row][lane + 32 k2]
+    if (MODE == kRowsH) {
+#pragma unroll
+        for (int k2 = 0; k2 < 32; ++k2) Hs[32 * k2 + lane] = make_float2(re[k2], im[k2]);
+        return;
+    }
+    // correlation: R = X conj(H).  r = IFFT(R) = conj(FFT(conj(R)))/N and conj(R) = conj(X) H.
+#pragma unroll
+    for (int k2 = 0; k2 < 32; ++k2) {
+        const float2 h = Hs[32 * k2 + lane];
+        const float xr = re[k2], xi = -im[k2];
+        re[k2] = fmaf(xr, h.x, -xi * h.y);
+        im[k2] = fmaf(xr, h.y, xi * h.x);
+    }
+    warp_fft1024(re, im, exw, tw, lane);                              // now indexed by n2 = lane + 32 j
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const unsigned n2 = (unsigned)(lane + 32 * j);
+        const float2 w = twiddle_long(p.tw_lin, p.tw_fine, (n2 * (unsigned)row) & (unsigned)(kRevN - 1));
+        Xs[n2] = make_float2(fmaf(re[j], w.x, -im[j] * w.y), fmaf(re[j], w.y, im[j] * w.x));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side of mixfe_augment
+// ------------------------------------------------------------------------------------------------
+inline double pole_radius(double a1, double a2) {
+    const double disc = a1 * a1 - 4.0 * a2;
+    if (disc < 0.0) return std::sqrt(a2);
+    const double r1 = std::fabs((-a1 + std::sqrt(disc)) * 0.5), r2 = std::fabs((-a1 - std::sqrt(disc)) * 0.5);
+    return r1 > r2 ? r1 : r2;
+}
+
+inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* const out[kNumStems],
+                       long long stride_b, long long stride_c, int B, int T, const mixfe_aug_params* params,
+                       const float* impulse, int L, cudaStream_t stream) {
+    if (!pl || !in || !out || !params) return fail(MIXFE_EINVAL, "null argument");
+    for (int s = 0; s < kNumStems; ++s) {
+        if (!in[s] || !out[s]) return fail(MIXFE_EINVAL, "stem pointer %d is NULL", s);
+        if (in[s] == out[s]) return fail(MIXFE_EINVAL, "out must not alias in");
+    }
+    if (B < 0 || T <= 0) return fail(MIXFE_EINVAL, "bad B or T");
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535) return fail(MIXFE_EINVAL, "B > 65535 clips per call");
+    if (stride_c < T || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
+    DeviceGuard guard(pl->device);
+
+    // ---- decisions -> kernel form; pole radii size the warm-up of the chunked scan ---------------
+    std::vector<AugClipDev> clips(B);
+    std::vector<int> slot_clip;
+    double rmax = 0.0;
+    for (int b = 0; b < B; ++b) {
+        AugClipDev& c = clips[b];
+        std::memset(&c, 0, sizeof c);
+        const mixfe_aug_params& q = params[b];
+        for (int s = 0; s < kNumStems; ++s) {
+            c.gain[s] = q.gain_lin[s];
+            c.flags[s] = (q.tilt_on[s] ? 1 : 0) | (q.comp_on[s] ? 2 : 0) | (q.bw_on[s] ? 4 : 0);
+            for (int sec = 0; sec < 3; ++sec) {
+                const double* sos = sec == 0 ? q.tilt_sos[s] : q.bw_sos[s] + 6 * (sec - 1);
+                const bool on = sec == 0 ? q.tilt_on[s] != 0 : q.bw_on[s] != 0;
+                if (!on) continue;
+                const double a0 = sos[3];
+                if (a0 == 0.0) return fail(MIXFE_EINVAL, "clip %d stem %d: a0 = 0", b, s);
+                c.sos[s][sec][0] = sos[0] / a0; c.sos[s][sec][1] = sos[1] / a0; c.sos[s][sec][2] = sos[2] / a0;
+                c.sos[s][sec][3] = sos[4] / a0; c.sos[s][sec][4] = sos[5] / a0;
+                const double r = pole_radius(c.sos[s][sec][3], c.sos[s][sec][4]);
+                if (!(r < 1.0)) return fail(MIXFE_EINVAL, "clip %d stem %d: unstable filter section (pole radius %g)", b, s, r);
+                rmax = std::max(rmax, r);
+            }
+        }
+        c.reverb_on = q.reverb_on ? 1 : 0;
+        c.reverb_slot = -1;
+        if (c.reverb_on) {
+            if (!impulse || L <= 0) return fail(MIXFE_EINVAL, "clip %d wants reverb but no impulse was given", b);
+            c.reverb_slot = (int)slot_clip.size();
+            slot_clip.push_back(b);
+        }
+    }
+    // warm-up so that r^warm < 1e-13, in whole 512-sample blocks; chunk >= 8 * warm keeps the overhead <= 12.5 %
+    int warm = 0;
+    if (rmax > 0.0) {
+        const double need = std::log(1e-13) / std::log(rmax);
+        warm = need > 4.0e6 ? 1 << 30 : ((int)std::ceil(need) + kAugBlock - 1) / kAugBlock * kAugBlock;
+    }
+    int chunk = 8192;
+    while (chunk < 8 * (long long)warm && chunk < T) chunk *= 2;
+    if (chunk >= T || warm >= T) { chunk = (T + kAugBlock - 1) / kAugBlock * kAugBlock; warm = 0; }   // one exact chunk per row
+    const int n_chunks = (T + chunk - 1) / chunk;
+
+    // ---- workspace -------------------------------------------------------------------------------------
+    const int n_slots = (int)slot_clip.size();
+    int n_seg = 0, seg_len = 0;
+    if (n_slots) {
+        if (L > kRevN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevN / 2);
+        seg_len = kRevN - L + 1;
+        n_seg = (T + seg_len - 1) / seg_len;
+    }
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_clips = carve(sizeof(AugClipDev) * B);
+    const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
+    const size_t o_slots = carve(sizeof(int) * (size_t)std::max(1, n_slots));
+    const size_t o_X = carve(sizeof(float2) * (size_t)kRevN * n_slots * std::max(1, n_seg));
+    const size_t o_H = carve(sizeof(float2) * (size_t)kRevN * n_slots);
+    int rc = ensure_workspace(pl, off, stream);
+    if (rc) return rc;
+    char* ws = reinterpret_cast<char*>(pl->ws);
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
+    if (n_slots)
+        MIXFE_CUDA(cudaMemcpyAsync(ws + o_slots, slot_clip.data(), sizeof(int) * n_slots, cudaMemcpyHostToDevice, stream));
+
+    K3Params p3{};
+    for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in[s]; p3.out[s] = out[s]; }
+    p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = chunk; p3.warm = warm;
+    p3.n_chunks = n_chunks; p3.clips = reinterpret_cast<const AugClipDev*>(ws + o_clips);
+    p3.part_energy = reinterpret_cast<double*>(ws + o_energy);
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
+        k3_augment<<<dim3((n_chunks + kAugWarps - 1) / kAugWarps, 2, B), kAugWarps * 32, 0, stream>>>(p3);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter()++;
+    if (!n_slots) return MIXFE_OK;
+
+    K4Params p4{};
+    for (int s = 0; s < kNumStems; ++s) p4.out[s] = out[s];
+    p4.stride_b = stride_b; p4.stride_c = stride_c; p4.T = T; p4.L = L; p4.half = L / 2; p4.seg_len = seg_len;
+    p4.n_seg = n_seg; p4.n_chunks = n_chunks; p4.slot_clip = reinterpret_cast<const int*>(ws + o_slots);
+    p4.impulse = impulse; p4.X = reinterpret_cast<float2*>(ws + o_X); p4.H = reinterpret_cast<float2*>(ws + o_H);
+    p4.part_energy = p3.part_energy; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
+    const int smem_cols = (kColsPerCta * kColStride + 1024) * (int)sizeof(float2);
+    const int smem_rows = (8 * 1024 + 1024) * (int)sizeof(float2);
+    if (!pl->k4_attr_done) {
+        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
+        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
+        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsInv>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
+        MIXFE_CUDA(cudaFuncSetAttribute(k4_rows<kRowsX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_rows));
+        MIXFE_CUDA(cudaFuncSetAttribute(k4_rows<kRowsH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_rows));
+        pl->k4_attr_done = true;
+    }
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_REVERB, stream);
+        const dim3 g1(kRevN2 / kColsPerCta, 1, n_slots), gs(kRevN2 / kColsPerCta, n_seg, n_slots);
+        k4_cols<kColsH><<<g1, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsH><<<dim3(kRevN1 / 8, 1, n_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsX><<<gs, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsX><<<dim3(kRevN1 / 8, n_seg, n_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsInv><<<gs, 256, smem_cols, stream>>>(p4);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 5;
+    return MIXFE_OK;
+}
+
+}  // namespace mixfe

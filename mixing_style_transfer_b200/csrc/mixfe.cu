@@ -69,6 +69,7 @@ int build_mel_tables(mixfe_plan* pl) {
     for (int g = 0; g < ng; ++g) {
         int nmax = 0;
         for (int q = 0; q < 4; ++q) nmax = std::max(nmax, rows[4 * g + q]);
+        nmax = (nmax + 1) & ~1;                          // K1 walks two rows per iteration
         gdesc[g] = make_int2(nmax, (int)gw.size());
         for (int j = 0; j < nmax; ++j)
             for (int q = 0; q < 4; ++q) {
@@ -211,7 +212,7 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     const int sd = n_spectral_bins > 0 ? n_spectral_bins + 2 : 5;
     pl->D = 4 * (6 + sd + 3) + 4 + 4;
     pl->fb = default_filterbank(sample_rate, n_fft, n_mels);
-    std::vector<float2> tw(1024), twf(1024);
+    std::vector<float2> tw(1024), twf(1024), twl(1024);
     for (int k1 = 0; k1 < 32; ++k1)
         for (int n2 = 0; n2 < 32; ++n2) {
             const double a = -2.0 * M_PI * (double)(k1 * n2) / 1024.0;
@@ -220,9 +221,12 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     for (int e = 0; e < 1024; ++e) {
         const double a = -2.0 * M_PI * (double)e / 1048576.0;
         twf[e] = make_float2((float)std::cos(a), (float)std::sin(a));
+        const double c = -2.0 * M_PI * (double)e / 1024.0;
+        twl[e] = make_float2((float)std::cos(c), (float)std::sin(c));
     }
     int rc = upload(&pl->d_tw, tw);
     if (!rc) rc = upload(&pl->d_twfine, twf);
+    if (!rc) rc = upload(&pl->d_twlin, twl);
     if (!rc) rc = build_mel_tables(pl);
     if (rc) { mixfe_plan_destroy(pl); return rc; }
     *out = pl;
@@ -232,7 +236,7 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
 int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
-    cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_frow0); cudaFree(pl->d_gdesc);
+    cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_frow0); cudaFree(pl->d_gdesc);
     cudaFree(pl->d_gw); cudaFree(pl->d_wtab); cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;

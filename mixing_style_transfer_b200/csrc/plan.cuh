@@ -8,6 +8,7 @@ struct mixfe_plan {
     std::vector<float> fb;              // host [n_freq][n_mels]
     // device constant tables
     float2* d_tw = nullptr;
+    float2* d_twlin = nullptr;          // exp(-2 pi i j / 1024), j in [0, 1024)
     float2* d_twfine = nullptr;         // exp(-2 pi i e / 2^20), e in [0, 1024): fine twiddles of the long FFT
     int* d_frow0 = nullptr;
     int2* d_gdesc = nullptr;
@@ -24,6 +25,7 @@ struct mixfe_plan {
     void* aug_params_host = nullptr;    // pinned staging buffer for them
     size_t aug_params_cap = 0;
     // optional per-kernel timing (bench.py): event pairs recorded around launches, drained on query
+    bool k4_attr_done = false;          // dynamic shared-memory opt-in of the reverb kernels
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[MIXFE_NUM_KERNELS];
 };
