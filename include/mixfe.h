@@ -91,6 +91,10 @@ int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
                           long long stride_b, long long stride_c, int B, int T,
                           float* melpow, long long melpow_stride_b, void* cuda_stream);
 
+/* Test hook: launch shape of the fused feature kernel K1 -- resident CTAs per SM (2 on a B200 for the
+ * reference configuration), its dynamic shared memory, and the steps of the warp-local mel walk. */
+int mixfe_debug_feature_kernel_config(const mixfe_plan* plan, int* ctas_per_sm, int* smem_bytes, int* mel_steps);
+
 /* Number of kernel launches issued through this library since load (bench.py's gpu_launches). */
 long long mixfe_launch_count(void);
 

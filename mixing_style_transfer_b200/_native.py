@@ -72,7 +72,7 @@ _lock = threading.Lock()
 EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_plan_destroy",
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
-           "mixfe_plan_enable_timing", "mixfe_plan_kernel_time")
+           "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config")
 
 
 def lib() -> ctypes.CDLL:
@@ -103,6 +103,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
                                     ctypes.POINTER(AugParams), vp, ci, vp]
         L.mixfe_launch_count.restype = ll
+        L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
@@ -183,6 +184,12 @@ class Plan:
 
     def workspace_bytes(self) -> int:
         return int(lib().mixfe_workspace_bytes(self._h))
+
+    def k1_config(self) -> dict:
+        """Launch shape of the fused feature kernel: resident CTAs per SM, dynamic smem, mel-walk steps."""
+        a, b, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        _check(lib().mixfe_debug_feature_kernel_config(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return {"ctas_per_sm": a.value, "smem_bytes": b.value, "mel_steps": c.value}
 
     def features_logmel(self, stems: Sequence[torch.Tensor], want_features: bool = True,
                         want_logmel: bool = True, features_out: Optional[torch.Tensor] = None,

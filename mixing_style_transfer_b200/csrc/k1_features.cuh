@@ -12,21 +12,24 @@
 // The reference runs 12 STFTs per clip (each a (2,T) real FFT + dense 513x128 matmul); here each
 // stem's L and R are packed into ONE complex 1024-point FFT per frame, shared by all consumers.
 //
-// Work decomposition.  grid = (frame tiles, clips); a CTA of 8 warps owns TF = 8 consecutive
-// frames of one clip and walks the 4 stems.  Per stem:
+// Work decomposition.  Persistent CTAs (2 per SM) of 8 warps stride over (clip, frame-tile) items;
+// a tile is TF = 8 consecutive frames and the CTA walks its 4 stems.  Per (tile, stem):
 //   stage   samples [t0*hop - 512, t0*hop + 7*hop + 512) of L and R, reflect-padded at the clip
-//           edges, interleaved as float2 in shared memory (128-bit global loads in the interior)
+//           edges, interleaved as float2 in shared memory.  Interior tiles use cp.async, issued one
+//           (tile, stem) AHEAD -- right after every warp has pulled its frame into registers -- so
+//           the copy overlaps the FFT phase of the current stem.
 //   FFT     one warp per frame: Hann window on the fly, 32 x 32 four-step FFT with the
-//           transposition through a swizzled shared buffer, L/R untangled with warp shuffles,
-//           power of bins 0..512 left in registers
-//   P tile  powers written as rows of (2 bins x 16 columns), column = channel*8 + frame
-//   mel     every quarter-warp owns one mel filter: LDS.128 of 2 bins x 2 columns, LDS.64 of the
-//           two filter taps, 4 FMAs; result tile [mel][channel][frame] in shared memory
-//   epilog  log(mel + 1e-10) -> coalesced global store; per-(stem, mel) sums of log and power for
-//           the band / tilt / flatness features; S = (mel_L + mel_R)/2 kept for the masking term
-// Time-domain statistics come from the tile's own hop region, read once for all 4 stems so the
-// mixture never exists in memory.  Per-tile partials go to a workspace (no float atomics: results
-// are run-to-run deterministic) and K2 reduces them in double precision.
+//           transposition through a swizzled warp-private shared buffer, L/R untangled with warp
+//           shuffles; the 513 (L, R) powers go to a warp-private column in the same buffer
+//   mel     WARP-LOCAL: lane l owns filters l, 32+l, 64+l, 96+l of its warp's frame and walks their
+//           contiguous support (weights from a [step][lane] table, powers at lo(filter)+step);
+//           no CTA barrier between FFT and mel.  Result: 128 x (L, R) mel powers per warp.
+//   epilog  thread (mel, channel) gathers the 8 frames of the 8 warps: log(mel + 1e-10), per-(stem,
+//           mel) sums of log and power for the band / tilt / flatness features, S = (mel_L+mel_R)/2
+//           kept for the masking term; the log tile is then stored with coalesced 32-byte runs.
+// Time-domain statistics come from the tile's own hop region, read once for all 4 stems (128-bit
+// loads) so the mixture never exists in memory.  Per-tile partials go to a workspace (no float
+// atomics: results are run-to-run deterministic) and K2 reduces them in double precision.
 #pragma once
 
 #include "common.cuh"
@@ -38,16 +41,24 @@ constexpr int kTF = 8;             // frames per CTA tile
 constexpr int kK1Threads = 256;    // 8 warps, one frame each
 constexpr int kNfft = 1024;
 constexpr int kNfreq = 513;
-constexpr int kPRS = 36;           // floats per P-tile row (32 used + pad to keep 16 B alignment)
-constexpr int kPRows = 288;        // 257 rows of bin pairs + zeroed overshoot rows for ragged groups
 constexpr int kTdN = 40;           // floats per tile of time-domain partials
-constexpr int kMaxGroupsPerWarp = 8;
+constexpr int kMaxSlots = 4;       // mel filters per lane (n_mels <= 128)
+// warp-private shared region (8 KB): [0, 8192) exchange during the FFT; afterwards
+//   [0, kPvBytes)                 (L, R) power column, bins 0..512 + zero-weight overshoot
+//   [kPvBytes, +1024)             this frame's 128 x (L, R) mel powers
+//   [kLogOff, +1024)              1/8 of the CTA's log tile (16 mel rows x 16 columns)
+constexpr int kWarpRegion = 8192;
+constexpr int kPvEntries = 544;
+constexpr int kPvBytes = kPvEntries * 8;            // 4352
+constexpr int kMelOff = kPvBytes;                   // 4352
+constexpr int kLogOff = kMelOff + 1024;             // 5376
 
 struct K1Params {
     const float* stem[kNumStems];
     long long stride_b, stride_c;
-    int B, T, F, hop, n_mels, n_mels_pad, n_tiles, n_groups;
+    int B, T, F, hop, n_mels, n_mels_pad, n_tiles;
     int nxs;                         // staged samples per channel = (kTF-1)*hop + 1024
+    long long total_items;           // B * n_tiles
     float* logmel;
     long long lm_stride_b;
     float* melpow;                   // debug output (mel power before the log) or nullptr
@@ -55,13 +66,15 @@ struct K1Params {
     float2* part_spec;               // [B][n_tiles][4][n_mels_pad] (sum log, sum mel)
     float* part_td;                  // [B][n_tiles][kTdN]
     const float2* tw;                // [1024] tw[k1*32+n2] = exp(-2 pi i n2 k1 / 1024)
-    const int* frow0;                // [n_mels_pad] first P-tile row of each filter
-    const int2* gdesc;               // [n_groups] {rows to walk, offset into gw}
-    const float2* gw;                // filter taps, [group][row][quarter] -> (w(even bin), w(odd bin))
-    int nw2;
-    const unsigned char* wtab;       // [8*kMaxGroupsPerWarp + 8] groups of each warp, then counts
+    const float* wsteps;             // [n_wsteps][32] filter weights, slot-major
+    const int* flo;                  // [n_slots][32] byte offset (8 * first bin) of filter 32*slot + lane
+    int n_slots, n_wsteps;
+    int slot_len[kMaxSlots];         // steps per slot (even)
+    int slot_woff[kMaxSlots];        // first step of the slot in wsteps
     int want_stats;
-    int off_ex, off_tw, off_s, off_frow0, off_gdesc, off_gw, off_wtab, off_red;
+    unsigned* sm_ticket;             // [n_sms] ever-increasing arrival counters, one per SM
+    int skew_ns;                     // start delay of every second CTA that lands on an SM (0 = none)
+    int off_ex, off_tw, off_s, off_wsteps, off_flo, off_red;
 };
 
 __device__ __forceinline__ float ln_fast(float x) {               // x >= 1e-10: never denormal
@@ -74,119 +87,213 @@ __device__ __forceinline__ float fast_sigmoid_neg(float x) {     // 1 / (1 + exp
     return __fdividef(1.0f, 1.0f + __expf(x));
 }
 
-__global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_constant__ K1Params p) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    float2* const xs = reinterpret_cast<float2*>(smem);
-    float* const meltile = reinterpret_cast<float*>(smem);                    // aliases xs (after the FFT phase)
-    float* const logtile = meltile + p.n_mels_pad * 16;
-    float2* const ex = reinterpret_cast<float2*>(smem + p.off_ex);
-    float* const pt = reinterpret_cast<float*>(smem + p.off_ex);              // aliases ex (after the FFT phase)
-    float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);
-    float* const S = reinterpret_cast<float*>(smem + p.off_s);                // [3][n_mels_pad][8]
-    int* const frow0 = reinterpret_cast<int*>(smem + p.off_frow0);
-    int2* const gdesc = reinterpret_cast<int2*>(smem + p.off_gdesc);
-    float2* const gw = reinterpret_cast<float2*>(smem + p.off_gw);
-    unsigned char* const wtab = smem + p.off_wtab;
-    float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+// Shared-memory accesses whose ORDER matters for latency hiding: volatile asm keeps ptxas from sinking a
+// load next to its first use (it does, to save registers, and every load then costs a full LDS latency).
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+template <int IMM>
+__device__ __forceinline__ float2 lds64(unsigned addr) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(addr), "n"(IMM));
+    return v;
+}
+template <int IMM>
+__device__ __forceinline__ void sts64(unsigned addr, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0+%1], {%2, %3};" ::"r"(addr), "n"(IMM), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x, b = blockIdx.y;
-    const int t0 = tile * kTF;
+// Stage the samples of (clip b, tile, stem s) into xs.  Interior tiles: asynchronous 4-byte copies that
+// interleave L and R; edge tiles: synchronous loads with torch's 'reflect' indexing.
+__device__ __forceinline__ void k1_stage(const K1Params& p, float2* xs, int b, int tile, int s, int tid) {
+    const float* gL = p.stem[s] + (long long)b * p.stride_b;
+    const float* gR = gL + p.stride_c;
+    const long long base = (long long)tile * kTF * p.hop - kNfft / 2;
+    if (base >= 0 && base + p.nxs <= (long long)p.T) {
+        gL += base;
+        gR += base;
+#pragma unroll 4
+        for (int i = tid; i < p.nxs; i += kK1Threads) {
+            cp_async4(&xs[i].x, gL + i);
+            cp_async4(&xs[i].y, gR + i);
+        }
+    } else {
+        for (int i = tid; i < p.nxs; i += kK1Threads) {
+            long long j = base + i;
+            if (j < 0) j = -j;                               // torch 'reflect': -i -> i
+            if (j >= p.T) j = 2ll * (p.T - 1) - j;           // T-1+i -> T-1-i
+            j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);        // frames past F only; keeps loads in bounds
+            xs[i] = make_float2(__ldg(gL + j), __ldg(gR + j));
+        }
+    }
+}
 
-    // ---- constant tables -> shared memory ------------------------------------------------
-    for (int i = tid; i < 1024; i += kK1Threads) tw[i] = p.tw[i];
-    for (int i = tid; i < p.n_mels_pad; i += kK1Threads) frow0[i] = p.frow0[i];
-    for (int i = tid; i < p.n_groups; i += kK1Threads) gdesc[i] = p.gdesc[i];
-    for (int i = tid; i < p.nw2; i += kK1Threads) gw[i] = p.gw[i];
-    if (tid < 8 * kMaxGroupsPerWarp + 8) wtab[tid] = p.wtab[tid];
-
-    // ---- time-domain statistics over the hop region this tile owns --------------------------
-    if (p.want_stats) {
-        float acc[33];
+// Time-domain partials of the hop region a tile owns: per stem sum L, sum R, sum L^2, sum R^2,
+// sum (L-R)^2, sum (L+R)^2, max|L|, max|R| (slots 8s..8s+7) and the mixture energy (slot 32).
+__device__ __forceinline__ void k1_accumulate(float (&acc)[33], const float (&L)[kNumStems], const float (&R)[kNumStems]) {
+    float mL = 0.0f, mR = 0.0f;
 #pragma unroll
-        for (int i = 0; i < 33; ++i) acc[i] = 0.0f;
-        const long long own0 = (long long)t0 * p.hop;
-        long long rem = (long long)p.T - own0;
-        const int own_n = rem < 0 ? 0 : (rem > (long long)kTF * p.hop ? kTF * p.hop : (int)rem);
-        const long long cb = (long long)b * p.stride_b + own0;
+    for (int s = 0; s < kNumStems; ++s) {
+        acc[s * 8 + 0] += L[s];
+        acc[s * 8 + 1] += R[s];
+        acc[s * 8 + 2] = fmaf(L[s], L[s], acc[s * 8 + 2]);
+        acc[s * 8 + 3] = fmaf(R[s], R[s], acc[s * 8 + 3]);
+        const float d = L[s] - R[s], m = L[s] + R[s];
+        acc[s * 8 + 4] = fmaf(d, d, acc[s * 8 + 4]);
+        acc[s * 8 + 5] = fmaf(m, m, acc[s * 8 + 5]);
+        acc[s * 8 + 6] = fmaxf(acc[s * 8 + 6], fabsf(L[s]));
+        acc[s * 8 + 7] = fmaxf(acc[s * 8 + 7], fabsf(R[s]));
+        mL += L[s];                                  // ((0 + v) + b) + d) + o, as sum(stems.values())
+        mR += R[s];
+    }
+    acc[32] = fmaf(mL, mL, fmaf(mR, mR, acc[32]));
+}
+
+// `scratch` is the (idle) 64 KB exchange region.  Contains one __syncthreads; the caller provides
+// the barrier that separates the reduce from the next writer of `scratch`.
+__device__ __forceinline__ void k1_time_stats(const K1Params& p, float* scratch, int b, int tile, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    float acc[33];
+#pragma unroll
+    for (int i = 0; i < 33; ++i) acc[i] = 0.0f;
+    const long long own0 = (long long)tile * kTF * p.hop;
+    const long long rem = (long long)p.T - own0;
+    const int own_n = rem < 0 ? 0 : (rem > (long long)kTF * p.hop ? kTF * p.hop : (int)rem);
+    const long long cb = (long long)b * p.stride_b + own0;
+    unsigned long long amask = (unsigned long long)own_n;
+#pragma unroll
+    for (int s = 0; s < kNumStems; ++s)
+        amask |= reinterpret_cast<unsigned long long>(p.stem[s] + cb) |
+                 reinterpret_cast<unsigned long long>(p.stem[s] + cb + p.stride_c);
+    if ((amask & 15ull) == 0) {
+        // 128-bit path: every row start is 16-byte aligned and the region is a whole number of float4
+        // (own_n is part of the mask: a multiple of 16 samples)
+        for (int i = tid; i < (own_n >> 2); i += kK1Threads) {
+            float4 vL[kNumStems], vR[kNumStems];
+#pragma unroll
+            for (int s = 0; s < kNumStems; ++s) {
+                vL[s] = __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb) + i);
+                vR[s] = __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb + p.stride_c) + i);
+            }
+            {
+                const float L[4] = {vL[0].x, vL[1].x, vL[2].x, vL[3].x}, R[4] = {vR[0].x, vR[1].x, vR[2].x, vR[3].x};
+                k1_accumulate(acc, L, R);
+            }
+            {
+                const float L[4] = {vL[0].y, vL[1].y, vL[2].y, vL[3].y}, R[4] = {vR[0].y, vR[1].y, vR[2].y, vR[3].y};
+                k1_accumulate(acc, L, R);
+            }
+            {
+                const float L[4] = {vL[0].z, vL[1].z, vL[2].z, vL[3].z}, R[4] = {vR[0].z, vR[1].z, vR[2].z, vR[3].z};
+                k1_accumulate(acc, L, R);
+            }
+            {
+                const float L[4] = {vL[0].w, vL[1].w, vL[2].w, vL[3].w}, R[4] = {vR[0].w, vR[1].w, vR[2].w, vR[3].w};
+                k1_accumulate(acc, L, R);
+            }
+        }
+    } else {
         for (int i = tid; i < own_n; i += kK1Threads) {
-            float mL = 0.0f, mR = 0.0f;
+            float L[kNumStems], R[kNumStems];
 #pragma unroll
             for (int s = 0; s < kNumStems; ++s) {
                 const float* g = p.stem[s] + cb + i;
-                const float L = __ldg(g), R = __ldg(g + p.stride_c);
-                acc[s * 8 + 0] += L;
-                acc[s * 8 + 1] += R;
-                acc[s * 8 + 2] = fmaf(L, L, acc[s * 8 + 2]);
-                acc[s * 8 + 3] = fmaf(R, R, acc[s * 8 + 3]);
-                const float d = L - R, m = L + R;
-                acc[s * 8 + 4] = fmaf(d, d, acc[s * 8 + 4]);
-                acc[s * 8 + 5] = fmaf(m, m, acc[s * 8 + 5]);
-                acc[s * 8 + 6] = fmaxf(acc[s * 8 + 6], fabsf(L));
-                acc[s * 8 + 7] = fmaxf(acc[s * 8 + 7], fabsf(R));
-                mL += L;                                 // ((0 + v) + b) + d) + o, as sum(stems.values())
-                mR += R;
+                L[s] = __ldg(g);
+                R[s] = __ldg(g + p.stride_c);
             }
-            acc[32] = fmaf(mL, mL, fmaf(mR, mR, acc[32]));
+            k1_accumulate(acc, L, R);
         }
-        float* const scratch = reinterpret_cast<float*>(ex);       // [33][256], exchange region is idle
+    }
 #pragma unroll
-        for (int q = 0; q < 33; ++q) scratch[q * kK1Threads + tid] = acc[q];
-        __syncthreads();
-        for (int q = warp; q < 33; q += 8) {
-            const bool is_max = q < 32 && (q & 7) >= 6;
-            float v = is_max ? 0.0f : 0.0f;
-            for (int j = 0; j < 8; ++j) {
-                const float u = scratch[q * kK1Threads + lane + 32 * j];
-                v = is_max ? fmaxf(v, u) : v + u;
-            }
-            v = is_max ? warp_max(v) : warp_sum(v);
-            if (lane == 0) p.part_td[((long long)b * p.n_tiles + tile) * kTdN + q] = v;
+    for (int q = 0; q < 33; ++q) scratch[q * kK1Threads + tid] = acc[q];
+    __syncthreads();
+    for (int q = warp; q < 33; q += 8) {
+        const bool is_max = q < 32 && (q & 7) >= 6;
+        float v = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float u = scratch[q * kK1Threads + lane + 32 * j];
+            v = is_max ? fmaxf(v, u) : v + u;
         }
-        // the next write into the exchange region happens after the post-staging __syncthreads
+        v = is_max ? warp_max(v) : warp_sum(v);
+        if (lane == 0) p.part_td[((long long)b * p.n_tiles + tile) * kTdN + q] = v;
+    }
+}
+
+__global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_constant__ K1Params p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float2* const xs = reinterpret_cast<float2*>(smem);
+    unsigned char* const ex = smem + p.off_ex;                                // 8 warp regions of 8 KB
+    float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);              // [31][32], rows k1 = 1..31
+    float* const S = reinterpret_cast<float*>(smem + p.off_s);                // [3][2][n_mels_pad][4]
+    float* const wsteps = reinterpret_cast<float*>(smem + p.off_wsteps);      // [n_wsteps][32]
+    int* const flo = reinterpret_cast<int*>(smem + p.off_flo);                // [n_slots][32]
+    float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    long long item = blockIdx.x;
+    if (item >= p.total_items) return;
+
+    // ---- constant tables -> shared memory (once per persistent CTA) ----------------------------
+    for (int i = tid; i < 31 * 32; i += kK1Threads) tw[i] = p.tw[32 + i];      // rows k1 = 1..31
+    for (int i = tid; i < p.n_wsteps * 32; i += kK1Threads) wsteps[i] = p.wsteps[i];
+    for (int i = tid; i < p.n_slots * 32; i += kK1Threads) flo[i] = p.flo[i];
+
+    unsigned char* const region = ex + warp * kWarpRegion;
+    float2* const exw = reinterpret_cast<float2*>(region);
+    float2* const pv = reinterpret_cast<float2*>(region);
+    float2* const melw = reinterpret_cast<float2*>(region + kMelOff);
+
+    int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
+    k1_stage(p, xs, b, tile, 0, tid);
+
+    // Persistent CTAs that share an SM start together and, with identical work per tile, would stay in
+    // lockstep: both in the FP-bound FFT phase, then both in the shared-memory-bound phases.  Delaying
+    // every second arrival on an SM keeps the two CTAs in complementary phases.
+    if (p.skew_ns > 0) {
+        if (tid == 0) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            const unsigned ticket = atomicAdd(p.sm_ticket + smid, 1u);
+            if (ticket & 1u) {
+                unsigned long long t0, t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                do {
+                    __nanosleep(500);
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                } while (t1 - t0 < (unsigned long long)p.skew_ns);
+            }
+        }
+        __syncthreads();
     }
 
-    float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};      // masking partial sums of this thread
+    for (;;) {
+        const int t0 = tile * kTF;
+        const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;          // frames of this tile that exist
+        const long long next_item = item + gridDim.x;
+        float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};                     // masking partial sums of this thread
 
-    for (int s = 0; s < kNumStems; ++s) {
-        // ---- stage the samples of stem s -------------------------------------------------
-        {
-            const float* gL = p.stem[s] + (long long)b * p.stride_b;
-            const float* gR = gL + p.stride_c;
-            const long long base = (long long)t0 * p.hop - kNfft / 2;
-            const bool interior = base >= 0 && base + p.nxs <= (long long)p.T && (p.nxs & 3) == 0 &&
-                                  ((reinterpret_cast<unsigned long long>(gL + base) |
-                                    reinterpret_cast<unsigned long long>(gR + base)) & 15ull) == 0;
-            if (interior) {
-                const float4* vL = reinterpret_cast<const float4*>(gL + base);
-                const float4* vR = reinterpret_cast<const float4*>(gR + base);
-                float4* dst = reinterpret_cast<float4*>(xs);
-                for (int i = tid; i < (p.nxs >> 2); i += kK1Threads) {
-                    const float4 a = __ldg(vL + i), c = __ldg(vR + i);
-                    dst[2 * i] = make_float4(a.x, c.x, a.y, c.y);
-                    dst[2 * i + 1] = make_float4(a.z, c.z, a.w, c.w);
-                }
-            } else {
-                for (int i = tid; i < p.nxs; i += kK1Threads) {
-                    long long j = base + i;
-                    if (j < 0) j = -j;                               // torch 'reflect': -i -> i
-                    if (j >= p.T) j = 2ll * (p.T - 1) - j;           // T-1+i -> T-1-i
-                    j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);        // frames past F only; keeps loads in bounds
-                    xs[i] = make_float2(__ldg(gL + j), __ldg(gR + j));
-                }
-            }
-        }
-        __syncthreads();
+        for (int s = 0; s < kNumStems; ++s) {
+            cp_async_wait_all();
+            __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
+            if (s == 0 && p.want_stats) k1_time_stats(p, reinterpret_cast<float*>(ex), b, tile, tid);
 
-        // ---- FFT of frame t0 + warp -------------------------------------------------------
-        float PL[16], PR[16];
-        float PnyL = 0.0f, PnyR = 0.0f;                 // bin 512 (lane 0 only)
-        if (t0 + warp < p.F) {
+            // ---- frame t0 + warp -> registers, Hann window on the fly ------------------------
             float re[32], im[32];
-            {
-                const float2 wl = tw[32 + lane];        // exp(-2 pi i lane/1024)
+            const bool active = warp < nvalid;
+            if (active) {
+                const float2 wl = tw[lane];             // row k1 = 1: exp(-2 pi i lane/1024)
                 const float cb = wl.x, sb = -wl.y;
-                const float2* xp = xs + warp * p.hop + lane;
+                const unsigned xa = smem_u32(xs + warp * p.hop + lane);
+#pragma unroll
+                for (int n1 = 0; n1 < 32; ++n1) {       // all 32 loads in flight before the first multiply
+                    const float2 v = lds64<0>(xa + n1 * 256);
+                    re[n1] = v.x;
+                    im[n1] = v.y;
+                }
 #pragma unroll
                 for (int n1 = 0; n1 < 32; ++n1) {
                     // 0.5 * hann[32 n1 + lane]; cos(a + b) with a = 2 pi n1/32 (immediate), b per lane.
@@ -194,211 +301,226 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     const float ca = n1 < 16 ? w32_re(n1) : -w32_re(n1 - 16);
                     const float sa = n1 < 16 ? w32_sin(n1) : -w32_sin(n1 - 16);
                     const float wv = fmaf(0.25f * sa, sb, fmaf(-0.25f * ca, cb, 0.25f));
-                    const float2 v = xp[32 * n1];
-                    re[n1] = v.x * wv;
-                    im[n1] = v.y * wv;
+                    re[n1] *= wv;
+                    im[n1] *= wv;
                 }
             }
-            dft32_dif(re, im);
-            float2* const exw = ex + warp * 1024;
-#pragma unroll
-            for (int k1 = 0; k1 < 32; ++k1) {
-                const float yr = re[brev5(k1)], yi = im[brev5(k1)];
-                float2 o;
-                if (k1 == 0) {
-                    o = make_float2(yr, yi);
-                } else {
-                    const float2 t = tw[k1 * 32 + lane];
-                    o.x = fmaf(yr, t.x, -yi * t.y);
-                    o.y = fmaf(yr, t.y, yi * t.x);
-                }
-                exw[k1 * 32 + (lane ^ k1)] = o;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int n2 = 0; n2 < 32; ++n2) {
-                const float2 v = exw[lane * 32 + (n2 ^ lane)];
-                re[n2] = v.x;
-                im[n2] = v.y;
-            }
-            dft32_dif(re, im);
-            // lane holds X[lane + 32 k2] at index brev5(k2).  Untangle L (real part) and R (imag part):
-            // |L_k|^2 = |X_k + conj(X_{N-k})|^2, |R_k|^2 = |X_k - conj(X_{N-k})|^2 (scale folded into the window).
-            const int src = (32 - lane) & 31;
-#pragma unroll
-            for (int k2 = 0; k2 < 16; ++k2) {
-                float qr = __shfl_sync(kFullMask, re[brev5(31 - k2)], src);
-                float qi = __shfl_sync(kFullMask, im[brev5(31 - k2)], src);
-                if (lane == 0) {                         // N - 32 k2 lives in lane 0 itself, register (32 - k2) & 31
-                    qr = re[brev5((32 - k2) & 31)];
-                    qi = im[brev5((32 - k2) & 31)];
-                }
-                const float xr = re[brev5(k2)], xi = im[brev5(k2)];
-                const float a = xr + qr, bb = xi - qi, c = xr - qr, d = xi + qi;
-                PL[k2] = fmaf(a, a, bb * bb);
-                PR[k2] = fmaf(c, c, d * d);
-            }
+            __syncthreads();                 // B0': xs is dead, the statistics scratch is dead
+
+            // ---- prefetch the next (tile, stem) while this one is transformed -------------------
             {
-                const float xr = re[brev5(16)], xi = im[brev5(16)];      // bin 512 is its own partner
-                PnyL = 4.0f * xr * xr;
-                PnyR = 4.0f * xi * xi;
-            }
-        } else {
-#pragma unroll
-            for (int k2 = 0; k2 < 16; ++k2) PL[k2] = PR[k2] = 0.0f;
-        }
-        __syncthreads();          // all warps are done with xs and with their exchange buffers
-
-        // ---- P tile: row = bin >> 1, position = 2*column + (bin & 1), column = channel*8 + frame
-        {
-#pragma unroll
-            for (int k2 = 0; k2 < 16; ++k2) {
-                float* row = pt + ((lane >> 1) + 16 * k2) * kPRS + (lane & 1);
-                row[2 * warp] = PL[k2];
-                row[2 * (8 + warp)] = PR[k2];
-            }
-            if (lane == 0) {
-                float* row = pt + 256 * kPRS;
-                row[2 * warp] = PnyL;
-                row[2 * (8 + warp)] = PnyR;
-                row[2 * warp + 1] = 0.0f;               // "bin 513" slot
-                row[2 * (8 + warp) + 1] = 0.0f;
-            }
-            for (int i = tid; i < (kPRows - 257) * kPRS; i += kK1Threads) pt[257 * kPRS + i] = 0.0f;
-        }
-        __syncthreads();
-
-        // ---- sparse mel projection: one filter per quarter-warp ------------------------------
-        {
-            const int q = lane >> 3, j8 = lane & 7;
-            const int ng = wtab[8 * kMaxGroupsPerWarp + warp];
-            for (int gi = 0; gi < ng; ++gi) {
-                const int g = wtab[warp * kMaxGroupsPerWarp + gi];
-                const int2 gd = gdesc[g];
-                const int m = 4 * g + q;
-                const float* prow = pt + frow0[m] * kPRS + 4 * j8;
-                const float2* wp = gw + gd.y + q;
-                float a0 = 0.0f, a1 = 0.0f, c0 = 0.0f, c1 = 0.0f;
-                for (int j = 0; j < gd.x; j += 2) {          // gd.x is even (host pads with zero taps)
-                    const float4 v = *reinterpret_cast<const float4*>(prow + j * kPRS);
-                    const float4 u = *reinterpret_cast<const float4*>(prow + (j + 1) * kPRS);
-                    const float2 w = wp[4 * j];
-                    const float2 x = wp[4 * j + 4];
-                    a0 = fmaf(w.x, v.x, a0);
-                    a1 = fmaf(w.x, v.z, a1);
-                    c0 = fmaf(x.x, u.x, c0);
-                    c1 = fmaf(x.x, u.z, c1);
-                    a0 = fmaf(w.y, v.y, a0);
-                    a1 = fmaf(w.y, v.w, a1);
-                    c0 = fmaf(x.y, u.y, c0);
-                    c1 = fmaf(x.y, u.w, c1);
+                int nb = b, ntile = tile, ns = s + 1;
+                if (ns == kNumStems) {
+                    nb = (int)(next_item / p.n_tiles);
+                    ntile = (int)(next_item - (long long)nb * p.n_tiles);
+                    ns = 0;
                 }
-                a0 += c0;
-                a1 += c1;
-                *reinterpret_cast<float2*>(meltile + m * 16 + 2 * j8) = make_float2(a0, a1);
+                if (s + 1 < kNumStems || next_item < p.total_items) k1_stage(p, xs, nb, ntile, ns, tid);
             }
-        }
-        __syncthreads();
 
-        // ---- epilogue A: logs, spectral partial sums, S tiles / masking ----------------------
-        const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;          // frames of this tile that exist
-        for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
-            const int m = r >> 1, ch = r & 1;
-            const float4 v0 = *reinterpret_cast<const float4*>(meltile + m * 16 + ch * 8);
-            const float4 v1 = *reinterpret_cast<const float4*>(meltile + m * 16 + ch * 8 + 4);
-            const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-            float lg[8];
-            float slog = 0.0f, smel = 0.0f;
+            if (active) {
+#pragma unroll 1
+                for (int pass = 0; pass < 2; ++pass) {          // one copy of the 32-point DFT in the instruction stream
+                    dft32_dif(re, im);
+                    if (pass == 0) {
+                        // inter-pass twiddles in batches of 8, the next batch in flight while this one is used;
+                        // element (k1, lane) of the exchange goes to k1*32 + (lane ^ k1)  (256-byte rows, XOR swizzle)
+                        const unsigned twa = smem_u32(tw + lane) - 256;            // the table starts at row k1 = 1
+                        const unsigned wa = smem_u32(exw) ^ (lane * 8);           // region is 8 KB aligned
+                        float2 tq[2][8];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) lg[t] = ln_fast(v[t] + 1e-10f);
-            if (nvalid == kTF) {
-                slog = ((lg[0] + lg[1]) + (lg[2] + lg[3])) + ((lg[4] + lg[5]) + (lg[6] + lg[7]));
-                smel = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-            } else {
+                        for (int q = 1; q < 8; ++q) tq[0][q] = lds64<0>(twa + q * 256);
 #pragma unroll
-                for (int t = 0; t < 8; ++t) {
-                    if (t < nvalid) {
-                        slog += lg[t];
-                        smel += v[t];
+                        for (int g = 0; g < 4; ++g) {
+                            if (g < 3) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) tq[(g + 1) & 1][q] = lds64<0>(twa + (8 * g + 8 + q) * 256);
+                            }
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const int k1 = 8 * g + q;
+                                const float yr = re[brev5(k1)], yi = im[brev5(k1)];
+                                if (k1 == 0) {
+                                    sts64<0>(wa, yr, yi);
+                                } else {
+                                    const float2 t = tq[g & 1][q];
+                                    sts64<0>((wa ^ (k1 * 8)) + k1 * 256, fmaf(yr, t.x, -yi * t.y), fmaf(yr, t.y, yi * t.x));
+                                }
+                            }
+                        }
+                        __syncwarp();
+                        const unsigned ra = smem_u32(exw) + lane * 264;           // lane*256 + lane*8
+#pragma unroll
+                        for (int n2 = 0; n2 < 32; ++n2) {
+                            const float2 v = lds64<0>(ra ^ (n2 * 8));
+                            re[n2] = v.x;
+                            im[n2] = v.y;
+                        }
+                        __syncwarp();            // the exchange buffer becomes the power column
                     }
                 }
-            }
-            *reinterpret_cast<float4*>(logtile + m * 16 + ch * 8) = make_float4(lg[0], lg[1], lg[2], lg[3]);
-            *reinterpret_cast<float4*>(logtile + m * 16 + ch * 8 + 4) = make_float4(lg[4], lg[5], lg[6], lg[7]);
-            slog += __shfl_xor_sync(kFullMask, slog, 1);
-            smel += __shfl_xor_sync(kFullMask, smel, 1);
-            if (ch == 0 && p.want_stats)
-                p.part_spec[(((long long)b * p.n_tiles + tile) * kNumStems + s) * p.n_mels_pad + m] =
-                    make_float2(slog, smel);
-        }
-        if (p.want_stats) {
-            for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
-                const int m = r >> 1, h = r & 1;             // h selects frames 4h .. 4h+3
-                const float4 vL = *reinterpret_cast<const float4*>(meltile + m * 16 + 4 * h);
-                const float4 vR = *reinterpret_cast<const float4*>(meltile + m * 16 + 8 + 4 * h);
-                const float4 Sc = make_float4(0.5f * (vL.x + vR.x), 0.5f * (vL.y + vR.y),
-                                              0.5f * (vL.z + vR.z), 0.5f * (vL.w + vR.w));
-                if (s < 3) {
-                    *reinterpret_cast<float4*>(S + (s * p.n_mels_pad + m) * 8 + 4 * h) = Sc;
-                } else if (m < p.n_mels) {
-                    const float4 A0 = *reinterpret_cast<const float4*>(S + (0 * p.n_mels_pad + m) * 8 + 4 * h);
-                    const float4 A1 = *reinterpret_cast<const float4*>(S + (1 * p.n_mels_pad + m) * 8 + 4 * h);
-                    const float4 A2 = *reinterpret_cast<const float4*>(S + (2 * p.n_mels_pad + m) * 8 + 4 * h);
-                    const float s0[4] = {A0.x, A0.y, A0.z, A0.w}, s1[4] = {A1.x, A1.y, A1.z, A1.w};
-                    const float s2[4] = {A2.x, A2.y, A2.z, A2.w}, s3[4] = {Sc.x, Sc.y, Sc.z, Sc.w};
+                // lane holds X[lane + 32 k2] at index brev5(k2).  Untangle L (real part) and R (imag part):
+                // |L_k|^2 = |X_k + conj(X_{N-k})|^2, |R_k|^2 = |X_k - conj(X_{N-k})|^2 (scale folded into the window).
+                const int src = (32 - lane) & 31;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if (4 * h + i < nvalid) {
-                            const float m01 = fmaxf(s0[i], s1[i]), m23 = fmaxf(s2[i], s3[i]);
-                            // sigmoid(max_{j != i} S_j - S_i) = 1 / (1 + exp(S_i - max_others))
-                            msum[0] += fast_sigmoid_neg(s0[i] - fmaxf(s1[i], m23));
-                            msum[1] += fast_sigmoid_neg(s1[i] - fmaxf(s0[i], m23));
-                            msum[2] += fast_sigmoid_neg(s2[i] - fmaxf(m01, s3[i]));
-                            msum[3] += fast_sigmoid_neg(s3[i] - fmaxf(m01, s2[i]));
+                for (int k2 = 0; k2 < 16; ++k2) {
+                    float qr = __shfl_sync(kFullMask, re[brev5(31 - k2)], src);
+                    float qi = __shfl_sync(kFullMask, im[brev5(31 - k2)], src);
+                    if (lane == 0) {                         // N - 32 k2 lives in lane 0 itself, register (32 - k2) & 31
+                        qr = re[brev5((32 - k2) & 31)];
+                        qi = im[brev5((32 - k2) & 31)];
+                    }
+                    const float xr = re[brev5(k2)], xi = im[brev5(k2)];
+                    const float a = xr + qr, bb = xi - qi, c = xr - qr, d = xi + qi;
+                    pv[lane + 32 * k2] = make_float2(fmaf(a, a, bb * bb), fmaf(c, c, d * d));
+                }
+                if (lane == 0) {
+                    const float xr = re[brev5(16)], xi = im[brev5(16)];      // bin 512 is its own partner
+                    pv[512] = make_float2(4.0f * xr * xr, 4.0f * xi * xi);
+                }
+                __syncwarp();
+
+                // ---- warp-local sparse mel projection --------------------------------------------
+#pragma unroll 1
+                for (int j = 0; j < p.n_slots; ++j) {
+                    {
+                        const int e = flo[j * 32 + lane];          // byte offset of the first bin | filter << 16
+                        const unsigned char* pb = region + (e & 0xffff);
+                        const float* wp = wsteps + p.slot_woff[j] * 32 + lane;
+                        float aL = 0.0f, aR = 0.0f, cL = 0.0f, cR = 0.0f, eL = 0.0f, eR = 0.0f, gL = 0.0f, gR = 0.0f;
+                        const int n = p.slot_len[j];
+#pragma unroll 1
+                        for (int i = 0; i < n; i += 4) {
+                            const float2 v0 = *reinterpret_cast<const float2*>(pb + 8 * i);
+                            const float2 v1 = *reinterpret_cast<const float2*>(pb + 8 * i + 8);
+                            const float2 v2 = *reinterpret_cast<const float2*>(pb + 8 * i + 16);
+                            const float2 v3 = *reinterpret_cast<const float2*>(pb + 8 * i + 24);
+                            const float w0 = wp[32 * i], w1 = wp[32 * i + 32], w2 = wp[32 * i + 64], w3 = wp[32 * i + 96];
+                            aL = fmaf(w0, v0.x, aL);
+                            aR = fmaf(w0, v0.y, aR);
+                            cL = fmaf(w1, v1.x, cL);
+                            cR = fmaf(w1, v1.y, cR);
+                            eL = fmaf(w2, v2.x, eL);
+                            eR = fmaf(w2, v2.y, eR);
+                            gL = fmaf(w3, v3.x, gL);
+                            gR = fmaf(w3, v3.y, gR);
+                        }
+                        melw[32 * j + (e >> 16)] = make_float2((aL + cL) + (eL + gL), (aR + cR) + (eR + gR));
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < kMaxSlots; ++j) melw[32 * j + lane] = make_float2(0.0f, 0.0f);
+            }
+            __syncthreads();                 // B1: the 8 mel columns of the tile are complete
+
+            // ---- epilogue A: logs, spectral partial sums, S tiles / masking ----------------------
+            for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
+                const int m = r >> 1, ch = r & 1;
+                const float* src = reinterpret_cast<const float*>(ex + kMelOff) + r;
+                float v[8], lg[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[t] = src[t * (kWarpRegion / 4)];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) lg[t] = ln_fast(v[t] + 1e-10f);
+                float slog = 0.0f, smel = 0.0f;
+                if (nvalid == kTF) {
+                    slog = ((lg[0] + lg[1]) + (lg[2] + lg[3])) + ((lg[4] + lg[5]) + (lg[6] + lg[7]));
+                    smel = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        if (t < nvalid) {
+                            slog += lg[t];
+                            smel += v[t];
                         }
                     }
                 }
+                // log tile chunk of 16 mel rows x 16 columns per warp region; float4 slot q is stored at
+                // q ^ ((q >> 3) & 1) so that the 128-bit stores of a quarter-warp hit distinct banks
+                float4* lt = reinterpret_cast<float4*>(ex + (m >> 4) * kWarpRegion + kLogOff);
+                const int q = (m & 15) * 4 + ch * 2;
+                lt[q ^ ((q >> 3) & 1)] = make_float4(lg[0], lg[1], lg[2], lg[3]);
+                lt[(q + 1) ^ ((q >> 3) & 1)] = make_float4(lg[4], lg[5], lg[6], lg[7]);
+                slog += __shfl_xor_sync(kFullMask, slog, 1);
+                smel += __shfl_xor_sync(kFullMask, smel, 1);
+                if (ch == 0 && p.want_stats)
+                    p.part_spec[(((long long)b * p.n_tiles + tile) * kNumStems + s) * p.n_mels_pad + m] =
+                        make_float2(slog, smel);
+            }
+            if (p.want_stats) {
+                for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
+                    const int h = r >= p.n_mels_pad ? 1 : 0, m = r - h * p.n_mels_pad;   // h selects frames 4h .. 4h+3
+                    float sc[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 lr = *reinterpret_cast<const float2*>(ex + (4 * h + i) * kWarpRegion + kMelOff + m * 8);
+                        sc[i] = 0.5f * (lr.x + lr.y);
+                    }
+                    if (s < 3) {
+                        *reinterpret_cast<float4*>(S + ((s * 2 + h) * p.n_mels_pad + m) * 4) = make_float4(sc[0], sc[1], sc[2], sc[3]);
+                    } else if (m < p.n_mels) {
+                        const float4 A0 = *reinterpret_cast<const float4*>(S + ((0 * 2 + h) * p.n_mels_pad + m) * 4);
+                        const float4 A1 = *reinterpret_cast<const float4*>(S + ((1 * 2 + h) * p.n_mels_pad + m) * 4);
+                        const float4 A2 = *reinterpret_cast<const float4*>(S + ((2 * 2 + h) * p.n_mels_pad + m) * 4);
+                        const float s0[4] = {A0.x, A0.y, A0.z, A0.w}, s1[4] = {A1.x, A1.y, A1.z, A1.w};
+                        const float s2[4] = {A2.x, A2.y, A2.z, A2.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if (4 * h + i < nvalid) {
+                                const float m01 = fmaxf(s0[i], s1[i]), m23 = fmaxf(s2[i], sc[i]);
+                                // sigmoid(max_{j != i} S_j - S_i) = 1 / (1 + exp(S_i - max_others))
+                                msum[0] += fast_sigmoid_neg(s0[i] - fmaxf(s1[i], m23));
+                                msum[1] += fast_sigmoid_neg(s1[i] - fmaxf(s0[i], m23));
+                                msum[2] += fast_sigmoid_neg(s2[i] - fmaxf(m01, sc[i]));
+                                msum[3] += fast_sigmoid_neg(sc[i] - fmaxf(m01, s2[i]));
+                            }
+                        }
+                    }
+                }
+                if (s == kNumStems - 1) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
+                    if (lane == 0) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) red[warp * 4 + i] = msum[i];
+                    }
+                }
+            }
+            __syncthreads();                 // B2: log tile complete (and `red` when s == 3)
+
+            // ---- epilogue B: coalesced store of the log-mel tile (32-byte runs along time) --------
+            {
+                const int col = tid & 15, ch = col >> 3, t = col & 7, m0 = tid >> 4;
+                if (t < nvalid) {
+                    const long long o = ((long long)(2 * s + ch) * p.n_mels + m0) * p.F + t0 + t;
+                    const long long step = 16ll * p.F;
+                    if (p.logmel) {
+                        float* dst = p.logmel + (long long)b * p.lm_stride_b + o;
+                        const int q = tid >> 2;
+                        const float* src = reinterpret_cast<const float*>(ex + kLogOff) + (((q ^ ((q >> 3) & 1)) << 2) | (tid & 3));
+#pragma unroll 8
+                        for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kWarpRegion / 4) *dst = *src;
+                    }
+                    if (p.melpow) {
+                        float* dst = p.melpow + (long long)b * p.mp_stride_b + o;
+                        const float* src = reinterpret_cast<const float*>(ex + t * kWarpRegion + kMelOff) + ch;
+                        for (int m = m0; m < p.n_mels; m += 16, dst += step) *dst = src[2 * m];
+                    }
+                }
+                if (s == kNumStems - 1 && p.want_stats && tid < 4) {
+                    float v = 0.0f;
+                    for (int w = 0; w < 8; ++w) v += red[w * 4 + tid];
+                    p.part_td[((long long)b * p.n_tiles + tile) * kTdN + 33 + tid] = v;
+                }
             }
         }
-        __syncthreads();
-
-        // ---- epilogue B: coalesced store of the log-mel tile (32-byte runs along time) --------
-        {
-            const int col = tid & 15, ch = col >> 3, t = col & 7, m0 = tid >> 4;
-            if (t < nvalid) {
-                const long long o = ((long long)(2 * s + ch) * p.n_mels + m0) * p.F + t0 + t;
-                const long long step = 16ll * p.F;
-                if (p.logmel) {
-                    float* dst = p.logmel + (long long)b * p.lm_stride_b + o;
-                    const float* src = logtile + tid;
-#pragma unroll 4
-                    for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kK1Threads) *dst = *src;
-                }
-                if (p.melpow) {
-                    float* dst = p.melpow + (long long)b * p.mp_stride_b + o;
-                    const float* src = meltile + tid;
-                    for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kK1Threads) *dst = *src;
-                }
-            }
-        }
-        __syncthreads();          // xs (= meltile/logtile) is restaged next
+        if (next_item >= p.total_items) break;
+        item = next_item;
+        b = (int)(item / p.n_tiles);
+        tile = (int)(item - (long long)b * p.n_tiles);
     }
-
-    // ---- masking partial sums of the tile --------------------------------------------------
-    if (p.want_stats) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
-        if (lane == 0) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) red[warp * 4 + i] = msum[i];
-        }
-        __syncthreads();
-        if (tid < 4) {
-            float v = 0.0f;
-            for (int w = 0; w < 8; ++w) v += red[w * 4 + tid];
-            p.part_td[((long long)b * p.n_tiles + tile) * kTdN + 33 + tid] = v;
-        }
-    }
+    cp_async_wait_all();
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -3,7 +3,9 @@
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -Xcompiler -fPIC -shared
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <numeric>
 
 #include "common.cuh"
@@ -51,71 +53,120 @@ std::vector<float> default_filterbank(int sr, int n_fft, int n_mels) {
     return fb;
 }
 
-// Turn the (n_freq, n_mels) matrix into the grouped 2-tap tables K1 walks.
+// Turn the (n_freq, n_mels) matrix into the per-lane tables of K1's warp-local mel projection:
+// lane l of a warp owns filters l, 32+l, ... (one per slot); a slot is walked for as many steps as its
+// longest filter has bins between its first and last non-zero weight.
 int build_mel_tables(mixfe_plan* pl) {
-    const int nf = pl->n_freq, nm = pl->n_mels, nmp = pl->n_mels_pad;
+    const int nf = pl->n_freq, nm = pl->n_mels;
+    const int n_slots = (nm + 31) / 32;
+    if (n_slots > kMaxSlots) return fail(MIXFE_EUNSUPPORTED, "n_mels=%d needs more than %d filters per lane", nm, kMaxSlots);
     auto w = [&](int k, int m) -> float { return (k < nf && m < nm) ? pl->fb[(size_t)k * nm + m] : 0.0f; };
-    std::vector<int> frow0(nmp, 0), rows(nmp, 0);
+    std::vector<int> lo(n_slots * 32, 0), len(n_slots * 32, 0);
     for (int m = 0; m < nm; ++m) {
-        int lo = -1, hi = -1;
+        int first = -1, last = -1;
         for (int k = 0; k < nf; ++k)
-            if (w(k, m) != 0.0f) { if (lo < 0) lo = k; hi = k; }
-        if (lo >= 0) { frow0[m] = lo >> 1; rows[m] = (hi >> 1) - frow0[m] + 1; }
+            if (w(k, m) != 0.0f) { if (first < 0) first = k; last = k; }
+        if (first >= 0) { lo[m] = first; len[m] = last - first + 1; }
     }
-    const int ng = nmp / 4;
-    std::vector<int2> gdesc(ng);
-    std::vector<float2> gw;
-    std::vector<int> cost(ng);
-    for (int g = 0; g < ng; ++g) {
-        int nmax = 0;
-        for (int q = 0; q < 4; ++q) nmax = std::max(nmax, rows[4 * g + q]);
-        nmax = (nmax + 1) & ~1;                          // K1 walks two rows per iteration
-        gdesc[g] = make_int2(nmax, (int)gw.size());
-        for (int j = 0; j < nmax; ++j)
-            for (int q = 0; q < 4; ++q) {
-                const int m = 4 * g + q, r = frow0[m] + j;
-                if (r >= kPRows) return fail(MIXFE_EUNSUPPORTED, "mel filter %d reaches past the P tile", m);
-                gw.push_back(make_float2(w(2 * r, m), w(2 * r + 1, m)));
+    std::vector<int> flo(n_slots * 32);
+    std::vector<float> wsteps;
+    int n_wsteps = 0;
+    for (int j = 0; j < kMaxSlots; ++j) { pl->slot_len[j] = 0; pl->slot_woff[j] = 0; }
+    for (int j = 0; j < n_slots; ++j) {
+        int nmin = 0;
+        for (int l = 0; l < 32; ++l) nmin = std::max(nmin, len[32 * j + l]);
+        nmin = std::max(4, (nmin + 3) & ~3);             // K1 walks four steps per iteration
+        // A lane may start its walk before its filter's first bin (zero weights) as long as the walk still
+        // covers the support.  Use that slack, and the freedom of which lane takes which filter, to give
+        // the 16 lanes of each half-warp start bins with distinct residues mod 16: the 64-bit loads of the
+        // power column are then free of bank conflicts.  Bipartite matching filter -> (half-warp, residue).
+        int n = nmin;
+        std::vector<int> pos_of(32, -1), start_of(32, 0);
+        // natural order first: when the slot's filters are narrow and closely spaced the loads already take the
+        // minimum of two wavefronts (equal addresses broadcast)
+        auto wavefronts = [&](int half) {
+            int worst = 0;
+            for (int r = 0; r < 16; ++r) {
+                std::vector<int> seen;
+                for (int l = 16 * half; l < 16 * half + 16; ++l) {
+                    const int st = std::min(lo[32 * j + l], kPvEntries - nmin);
+                    if ((st & 15) == r && std::find(seen.begin(), seen.end(), st) == seen.end()) seen.push_back(st);
+                }
+                worst = std::max(worst, (int)seen.size());
             }
-        cost[g] = 6 * nmax + 14;
+            return worst;
+        };
+        const bool natural_ok = wavefronts(0) <= 1 && wavefronts(1) <= 1;
+        for (; !natural_ok && n <= nmin; n += 4) {
+            auto start_for = [&](int f, int r) -> int {      // largest admissible start with start % 16 == r, or -1
+                const int m = 32 * j + f;
+                const int hi = len[m] ? std::min(lo[m], kPvEntries - n) : kPvEntries - n;
+                const int lw = len[m] ? std::max(0, lo[m] + len[m] - n) : 0;
+                for (int st = hi; st >= lw; --st)
+                    if ((st & 15) == r) return st;
+                return -1;
+            };
+            std::vector<int> owner(32, -1);                    // position (half*16 + residue) -> filter
+            std::function<bool(int, std::vector<char>&)> try_place = [&](int f, std::vector<char>& seen) -> bool {
+                for (int pos = 0; pos < 32; ++pos) {
+                    if (seen[pos] || start_for(f, pos & 15) < 0) continue;
+                    seen[pos] = 1;
+                    if (owner[pos] < 0 || try_place(owner[pos], seen)) { owner[pos] = f; return true; }
+                }
+                return false;
+            };
+            int placed = 0;
+            for (int f = 0; f < 32; ++f) {
+                std::vector<char> seen(32, 0);
+                if (try_place(f, seen)) ++placed;
+            }
+            if (placed == 32) {
+                for (int pos = 0; pos < 32; ++pos) { pos_of[owner[pos]] = pos; start_of[owner[pos]] = start_for(owner[pos], pos & 15); }
+                break;
+            }
+        }
+        if (pos_of[0] < 0) {                               // natural order, exact starts
+            n = nmin;
+            for (int f = 0; f < 32; ++f) {
+                const int m = 32 * j + f;
+                pos_of[f] = f;
+                start_of[f] = std::min(lo[m], kPvEntries - n);
+                if (len[m] && lo[m] + len[m] > start_of[f] + n)
+                    return fail(MIXFE_EUNSUPPORTED, "mel filter %d (bins %d..%d) overruns the power column", m, lo[m], lo[m] + len[m] - 1);
+            }
+        }
+        pl->slot_len[j] = n;
+        pl->slot_woff[j] = n_wsteps;
+        std::vector<int> filt_at(32, 0);
+        for (int f = 0; f < 32; ++f) filt_at[pos_of[f]] = f;
+        for (int lane = 0; lane < 32; ++lane) flo[32 * j + lane] = (8 * start_of[filt_at[lane]]) | (filt_at[lane] << 16);
+        for (int i = 0; i < n; ++i)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int f = filt_at[lane], m = 32 * j + f, k = start_of[f] + i;
+                wsteps.push_back((len[m] && k >= lo[m] && k < lo[m] + len[m]) ? w(k, m) : 0.0f);
+            }
+        n_wsteps += n;
     }
-    // longest-processing-time-first assignment of groups to the 8 warps
-    std::vector<int> order(ng);
-    std::iota(order.begin(), order.end(), 0);
-    std::sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] != cost[b] ? cost[a] > cost[b] : a < b; });
-    std::vector<unsigned char> wtab(8 * kMaxGroupsPerWarp + 8, 0);
-    int load[8] = {0, 0, 0, 0, 0, 0, 0, 0}, cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int g : order) {
-        int best = -1;
-        for (int wi = 0; wi < 8; ++wi)
-            if (cnt[wi] < kMaxGroupsPerWarp && (best < 0 || load[wi] < load[best])) best = wi;
-        if (best < 0) return fail(MIXFE_EUNSUPPORTED, "too many mel filter groups (%d)", ng);
-        wtab[best * kMaxGroupsPerWarp + cnt[best]++] = (unsigned char)g;
-        load[best] += cost[g];
-    }
-    for (int wi = 0; wi < 8; ++wi) wtab[8 * kMaxGroupsPerWarp + wi] = (unsigned char)cnt[wi];
-    pl->n_groups = ng;
-    pl->nw2 = (int)gw.size();
+    pl->n_slots = n_slots;
+    pl->n_wsteps = n_wsteps;
     int rc;
-    if ((rc = upload(&pl->d_frow0, frow0))) return rc;
-    if ((rc = upload(&pl->d_gdesc, gdesc))) return rc;
-    if ((rc = upload(&pl->d_gw, gw))) return rc;
-    if ((rc = upload(&pl->d_wtab, wtab))) return rc;
+    if ((rc = upload(&pl->d_flo, flo))) return rc;
+    if ((rc = upload(&pl->d_wsteps, wsteps))) return rc;
     // shared-memory map of K1
     pl->nxs = (kTF - 1) * pl->hop + kNfft;
-    const int region0 = std::max(pl->nxs * 8, 2 * nmp * 16 * 4);
-    pl->off_ex = align16(region0);
-    pl->off_tw = pl->off_ex + 8 * 1024 * 8;
-    pl->off_s = pl->off_tw + 1024 * 8;
-    pl->off_frow0 = pl->off_s + 3 * nmp * 8 * 4;
-    pl->off_gdesc = align16(pl->off_frow0 + nmp * 4);
-    pl->off_gw = align16(pl->off_gdesc + ng * 8);
-    pl->off_wtab = align16(pl->off_gw + pl->nw2 * 8);
-    pl->off_red = align16(pl->off_wtab + 8 * kMaxGroupsPerWarp + 8);
+    pl->off_ex = align16(pl->nxs * 8);
+    pl->off_tw = pl->off_ex + 8 * kWarpRegion;
+    pl->off_s = pl->off_tw + 31 * 32 * 8;            // rows k1 = 1..31 of the twiddle table (row 0 is all ones)
+    pl->off_wsteps = pl->off_s + 3 * pl->n_mels_pad * 8 * 4;
+    pl->off_flo = align16(pl->off_wsteps + n_wsteps * 32 * 4);
+    pl->off_red = align16(pl->off_flo + n_slots * 32 * 4);
     pl->smem_k1 = pl->off_red + 8 * 4 * 4;
     if (pl->smem_k1 > 227 * 1024)
-        return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large)", pl->smem_k1);
+        return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
     MIXFE_CUDA(cudaFuncSetAttribute(k1_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_k1));
+    int per_sm = 0;
+    MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_features, kK1Threads, pl->smem_k1));
+    pl->k1_ctas = std::max(1, per_sm) * pl->n_sms;
     return MIXFE_OK;
 }
 
@@ -135,7 +186,6 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     DeviceGuard guard(pl->device);
     const int F = 1 + T / pl->hop;
     const int n_tiles = (F + kTF - 1) / kTF;
-    if (B > 65535) return fail(MIXFE_EINVAL, "B > 65535 clips per call");
     const size_t spec_bytes = (size_t)B * n_tiles * kNumStems * pl->n_mels_pad * sizeof(float2);
     const size_t td_bytes = (size_t)B * n_tiles * kTdN * sizeof(float);
     if (features) {
@@ -146,17 +196,24 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     for (int s = 0; s < 4; ++s) p.stem[s] = stems[s];
     p.stride_b = stride_b; p.stride_c = stride_c;
     p.B = B; p.T = T; p.F = F; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
-    p.n_tiles = n_tiles; p.n_groups = pl->n_groups; p.nxs = pl->nxs;
+    p.n_tiles = n_tiles; p.nxs = pl->nxs; p.total_items = (long long)B * n_tiles;
     p.logmel = logmel; p.lm_stride_b = lm_stride_b; p.melpow = melpow; p.mp_stride_b = mp_stride_b;
     p.part_spec = reinterpret_cast<float2*>(pl->ws);
     p.part_td = reinterpret_cast<float*>(reinterpret_cast<char*>(pl->ws) + spec_bytes);
-    p.tw = pl->d_tw; p.frow0 = pl->d_frow0; p.gdesc = pl->d_gdesc; p.gw = pl->d_gw; p.nw2 = pl->nw2;
-    p.wtab = pl->d_wtab; p.want_stats = features ? 1 : 0;
-    p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_frow0 = pl->off_frow0;
-    p.off_gdesc = pl->off_gdesc; p.off_gw = pl->off_gw; p.off_wtab = pl->off_wtab; p.off_red = pl->off_red;
+    p.tw = pl->d_tw; p.wsteps = pl->d_wsteps; p.flo = pl->d_flo; p.n_slots = pl->n_slots; p.n_wsteps = pl->n_wsteps;
+    for (int j = 0; j < kMaxSlots; ++j) { p.slot_len[j] = pl->slot_len[j]; p.slot_woff[j] = pl->slot_woff[j]; }
+    p.want_stats = features ? 1 : 0;
+    p.sm_ticket = pl->d_sm_ticket;
+    {
+        const char* e = getenv("MIXFE_K1_SKEW_NS");
+        p.skew_ns = e ? atoi(e) : pl->k1_skew_ns;
+    }
+    p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_wsteps = pl->off_wsteps;
+    p.off_flo = pl->off_flo; p.off_red = pl->off_red;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
-        k1_features<<<dim3(n_tiles, B), kK1Threads, pl->smem_k1, stream>>>(p);
+        const int grid = (int)std::min<long long>(p.total_items, pl->k1_ctas);
+        k1_features<<<grid, kK1Threads, pl->smem_k1, stream>>>(p);
     }
     MIXFE_CUDA(cudaGetLastError());
     launch_counter()++;
@@ -207,6 +264,7 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
         return fail(MIXFE_EUNSUPPORTED, "device %d is sm_%d%d; libmixfe is built for sm_100a only", device,
                     prop.major, prop.minor);
     mixfe_plan* pl = new mixfe_plan();
+    pl->n_sms = prop.multiProcessorCount;
     pl->device = device; pl->sr = sample_rate; pl->n_fft = n_fft; pl->hop = hop; pl->n_mels = n_mels;
     pl->n_mels_pad = (n_mels + 15) & ~15; pl->n_bins = n_spectral_bins; pl->n_freq = n_fft / 2 + 1;
     const int sd = n_spectral_bins > 0 ? n_spectral_bins + 2 : 5;
@@ -224,6 +282,8 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
         const double c = -2.0 * M_PI * (double)e / 1024.0;
         twl[e] = make_float2((float)std::cos(c), (float)std::sin(c));
     }
+    MIXFE_CUDA(cudaMalloc((void**)&pl->d_sm_ticket, 1024 * sizeof(unsigned)));
+    MIXFE_CUDA(cudaMemset(pl->d_sm_ticket, 0, 1024 * sizeof(unsigned)));
     int rc = upload(&pl->d_tw, tw);
     if (!rc) rc = upload(&pl->d_twfine, twf);
     if (!rc) rc = upload(&pl->d_twlin, twl);
@@ -236,8 +296,8 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
 int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
-    cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_frow0); cudaFree(pl->d_gdesc);
-    cudaFree(pl->d_gw); cudaFree(pl->d_wtab); cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
+    cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
+    cudaFree(pl->ws); cudaFree(pl->aug_params_dev); cudaFree(pl->d_sm_ticket);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;
@@ -282,6 +342,14 @@ int mixfe_feature_dim(const mixfe_plan* pl) { return pl ? pl->D : fail(MIXFE_EIN
 int mixfe_num_frames(const mixfe_plan* pl, int T) { return pl ? 1 + T / pl->hop : fail(MIXFE_EINVAL, "null plan"); }
 
 size_t mixfe_workspace_bytes(const mixfe_plan* pl) { return pl ? pl->ws_bytes : 0; }
+
+int mixfe_debug_feature_kernel_config(const mixfe_plan* pl, int* ctas_per_sm, int* smem_bytes, int* mel_steps) {
+    if (!pl) return fail(MIXFE_EINVAL, "null plan");
+    if (ctas_per_sm) *ctas_per_sm = pl->n_sms ? pl->k1_ctas / pl->n_sms : 0;
+    if (smem_bytes) *smem_bytes = pl->smem_k1;
+    if (mel_steps) *mel_steps = pl->n_wsteps;
+    return MIXFE_OK;
+}
 
 int mixfe_features_logmel(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,
                           long long stride_c, int B, int T, float* features, float* logmel,

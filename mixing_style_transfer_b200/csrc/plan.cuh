@@ -10,14 +10,14 @@ struct mixfe_plan {
     float2* d_tw = nullptr;
     float2* d_twlin = nullptr;          // exp(-2 pi i j / 1024), j in [0, 1024)
     float2* d_twfine = nullptr;         // exp(-2 pi i e / 2^20), e in [0, 1024): fine twiddles of the long FFT
-    int* d_frow0 = nullptr;
-    int2* d_gdesc = nullptr;
-    float2* d_gw = nullptr;
-    unsigned char* d_wtab = nullptr;
-    int n_groups = 0, nw2 = 0;
-    // K1 shared-memory map
-    int nxs = 0, smem_k1 = 0;
-    int off_ex = 0, off_tw = 0, off_s = 0, off_frow0 = 0, off_gdesc = 0, off_gw = 0, off_wtab = 0, off_red = 0;
+    int* d_flo = nullptr;               // [n_slots][32] byte offset of each filter's first bin in the power column
+    float* d_wsteps = nullptr;          // [n_wsteps][32] filter weights walked by K1's warp-local mel projection
+    int n_slots = 0, n_wsteps = 0, slot_len[4] = {0, 0, 0, 0}, slot_woff[4] = {0, 0, 0, 0};
+    // K1 shared-memory map and persistent grid
+    int nxs = 0, smem_k1 = 0, n_sms = 0, k1_ctas = 0;
+    unsigned* d_sm_ticket = nullptr;    // per-SM arrival counters of K1's persistent CTAs (phase skew)
+    int k1_skew_ns = 0;
+    int off_ex = 0, off_tw = 0, off_s = 0, off_wsteps = 0, off_flo = 0, off_red = 0;
     // plan-owned workspace (grows to the high-water mark, then never reallocates)
     void* ws = nullptr;
     size_t ws_bytes = 0;
