@@ -104,6 +104,16 @@ template <int IMM>
 __device__ __forceinline__ void sts64(unsigned addr, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0+%1], {%2, %3};" ::"r"(addr), "n"(IMM), "f"(x), "f"(y) : "memory");
 }
+template <int IMM>
+__device__ __forceinline__ cplx64 lds_c(unsigned addr) {
+    cplx64 v;
+    asm volatile("ld.shared.b64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(IMM));
+    return v;
+}
+template <int IMM>
+__device__ __forceinline__ void sts_c(unsigned addr, cplx64 v) {
+    asm volatile("st.shared.b64 [%0+%1], %2;" ::"r"(addr), "n"(IMM), "l"(v) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Stage the samples of (clip b, tile, stem s) into xs.  Interior tiles: asynchronous 4-byte copies that
@@ -282,18 +292,14 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             if (s == 0 && p.want_stats) k1_time_stats(p, reinterpret_cast<float*>(ex), b, tile, tid);
 
             // ---- frame t0 + warp -> registers, Hann window on the fly ------------------------
-            float re[32], im[32];
+            cplx64 z[32];                    // (L, R) sample pairs = one complex value each
             const bool active = warp < nvalid;
             if (active) {
                 const float2 wl = tw[lane];             // row k1 = 1: exp(-2 pi i lane/1024)
                 const float cb = wl.x, sb = -wl.y;
                 const unsigned xa = smem_u32(xs + warp * p.hop + lane);
 #pragma unroll
-                for (int n1 = 0; n1 < 32; ++n1) {       // all 32 loads in flight before the first multiply
-                    const float2 v = lds64<0>(xa + n1 * 256);
-                    re[n1] = v.x;
-                    im[n1] = v.y;
-                }
+                for (int n1 = 0; n1 < 32; ++n1) z[n1] = lds_c<0>(xa + n1 * 256);     // all 32 loads in flight
 #pragma unroll
                 for (int n1 = 0; n1 < 32; ++n1) {
                     // 0.5 * hann[32 n1 + lane]; cos(a + b) with a = 2 pi n1/32 (immediate), b per lane.
@@ -301,8 +307,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     const float ca = n1 < 16 ? w32_re(n1) : -w32_re(n1 - 16);
                     const float sa = n1 < 16 ? w32_sin(n1) : -w32_sin(n1 - 16);
                     const float wv = fmaf(0.25f * sa, sb, fmaf(-0.25f * ca, cb, 0.25f));
-                    re[n1] *= wv;
-                    im[n1] *= wv;
+                    float xl, xr;
+                    cunpack(z[n1], xl, xr);
+                    z[n1] = cpack(xl * wv, xr * wv);
                 }
             }
             __syncthreads();                 // B0': xs is dead, the statistics scratch is dead
@@ -316,12 +323,25 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     ns = 0;
                 }
                 if (s + 1 < kNumStems || next_item < p.total_items) k1_stage(p, xs, nb, ntile, ns, tid);
+                if (ns == 0 && next_item < p.total_items && p.want_stats) {
+                    // pull the hop region the next tile owns towards L2 for stems 1..3 (stem 0 comes with its
+                    // staging): the statistics loads at the top of the next tile then hit L2 instead of HBM
+                    const long long own0 = (long long)ntile * kTF * p.hop;
+                    const int lines_per_row = (kTF * p.hop * 4) >> 7;
+                    for (int i = tid; i < 6 * lines_per_row; i += kK1Threads) {
+                        const int row = i / lines_per_row, off = (i - row * lines_per_row) * 32;
+                        if (own0 + off < p.T) {
+                            const float* g = p.stem[1 + (row >> 1)] + (long long)nb * p.stride_b + (row & 1) * p.stride_c + own0 + off;
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g));
+                        }
+                    }
+                }
             }
 
             if (active) {
 #pragma unroll 1
                 for (int pass = 0; pass < 2; ++pass) {          // one copy of the 32-point DFT in the instruction stream
-                    dft32_dif(re, im);
+                    dft32_dif_packed(z);
                     if (pass == 0) {
                         // inter-pass twiddles in batches of 8, the next batch in flight while this one is used;
                         // element (k1, lane) of the exchange goes to k1*32 + (lane ^ k1)  (256-byte rows, XOR swizzle)
@@ -339,10 +359,11 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
 #pragma unroll
                             for (int q = 0; q < 8; ++q) {
                                 const int k1 = 8 * g + q;
-                                const float yr = re[brev5(k1)], yi = im[brev5(k1)];
                                 if (k1 == 0) {
-                                    sts64<0>(wa, yr, yi);
+                                    sts_c<0>(wa, z[0]);
                                 } else {
+                                    float yr, yi;
+                                    cunpack(z[brev5(k1)], yr, yi);
                                     const float2 t = tq[g & 1][q];
                                     sts64<0>((wa ^ (k1 * 8)) + k1 * 256, fmaf(yr, t.x, -yi * t.y), fmaf(yr, t.y, yi * t.x));
                                 }
@@ -351,11 +372,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                         __syncwarp();
                         const unsigned ra = smem_u32(exw) + lane * 264;           // lane*256 + lane*8
 #pragma unroll
-                        for (int n2 = 0; n2 < 32; ++n2) {
-                            const float2 v = lds64<0>(ra ^ (n2 * 8));
-                            re[n2] = v.x;
-                            im[n2] = v.y;
-                        }
+                        for (int n2 = 0; n2 < 32; ++n2) z[n2] = lds_c<0>(ra ^ (n2 * 8));
                         __syncwarp();            // the exchange buffer becomes the power column
                     }
                 }
@@ -364,18 +381,22 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 const int src = (32 - lane) & 31;
 #pragma unroll
                 for (int k2 = 0; k2 < 16; ++k2) {
-                    float qr = __shfl_sync(kFullMask, re[brev5(31 - k2)], src);
-                    float qi = __shfl_sync(kFullMask, im[brev5(31 - k2)], src);
+                    float pr, pi;
+                    cunpack(z[brev5(31 - k2)], pr, pi);
+                    float qr = __shfl_sync(kFullMask, pr, src);
+                    float qi = __shfl_sync(kFullMask, pi, src);
                     if (lane == 0) {                         // N - 32 k2 lives in lane 0 itself, register (32 - k2) & 31
-                        qr = re[brev5((32 - k2) & 31)];
-                        qi = im[brev5((32 - k2) & 31)];
+                        cunpack(z[brev5((32 - k2) & 31)], qr, qi);
                     }
-                    const float xr = re[brev5(k2)], xi = im[brev5(k2)];
-                    const float a = xr + qr, bb = xi - qi, c = xr - qr, d = xi + qi;
+                    const cplx64 x = z[brev5(k2)], q = cpack(qr, -qi);       // conj(X[N-k])
+                    float a, bb, c, d;
+                    cunpack(cadd(x, q), a, bb);                              // 2 L_k
+                    cunpack(csub(x, q), c, d);                               // 2 i R_k
                     pv[lane + 32 * k2] = make_float2(fmaf(a, a, bb * bb), fmaf(c, c, d * d));
                 }
                 if (lane == 0) {
-                    const float xr = re[brev5(16)], xi = im[brev5(16)];      // bin 512 is its own partner
+                    float xr, xi;
+                    cunpack(z[brev5(16)], xr, xi);                           // bin 512 is its own partner
                     pv[512] = make_float2(4.0f * xr * xr, 4.0f * xi * xi);
                 }
                 __syncwarp();
