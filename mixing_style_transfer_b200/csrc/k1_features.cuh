@@ -87,10 +87,6 @@ __device__ __forceinline__ float fast_sigmoid_neg(float x) {     // 1 / (1 + exp
     return __fdividef(1.0f, 1.0f + __expf(x));
 }
 
-__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
-}
 // Shared-memory accesses whose ORDER matters for latency hiding: volatile asm keeps ptxas from sinking a
 // load next to its first use (it does, to save registers, and every load then costs a full LDS latency).
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -104,6 +100,11 @@ template <int IMM>
 __device__ __forceinline__ void sts64(unsigned addr, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0+%1], {%2, %3};" ::"r"(addr), "n"(IMM), "f"(x), "f"(y) : "memory");
 }
+__device__ __forceinline__ float lds32(unsigned addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
 template <int IMM>
 __device__ __forceinline__ cplx64 lds_c(unsigned addr) {
     cplx64 v;
@@ -114,30 +115,72 @@ template <int IMM>
 __device__ __forceinline__ void sts_c(unsigned addr, cplx64 v) {
     asm volatile("st.shared.b64 [%0+%1], %2;" ::"r"(addr), "n"(IMM), "l"(v) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// Stage the samples of (clip b, tile, stem s) into xs.  Interior tiles: asynchronous 4-byte copies that
-// interleave L and R; edge tiles: synchronous loads with torch's 'reflect' indexing.
-__device__ __forceinline__ void k1_stage(const K1Params& p, float2* xs, int b, int tile, int s, int tid) {
-    const float* gL = p.stem[s] + (long long)b * p.stride_b;
-    const float* gR = gL + p.stride_c;
-    const long long base = (long long)tile * kTF * p.hop - kNfft / 2;
-    if (base >= 0 && base + p.nxs <= (long long)p.T) {
-        gL += base;
-        gR += base;
-#pragma unroll 4
-        for (int i = tid; i < p.nxs; i += kK1Threads) {
-            cp_async4(&xs[i].x, gL + i);
-            cp_async4(&xs[i].y, gR + i);
-        }
-    } else {
-        for (int i = tid; i < p.nxs; i += kK1Threads) {
-            long long j = base + i;
-            if (j < 0) j = -j;                               // torch 'reflect': -i -> i
-            if (j >= p.T) j = 2ll * (p.T - 1) - j;           // T-1+i -> T-1-i
-            j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);        // frames past F only; keeps loads in bounds
-            xs[i] = make_float2(__ldg(gL + j), __ldg(gR + j));
-        }
+// ---- staging of one (clip, tile, stem): planar L / R sample rows in shared memory --------------------
+// Interior tiles whose rows are 16-byte aligned in global memory are staged by the TMA engine: ONE thread
+// issues two bulk copies (cp.async.bulk, 11 KB each for hop 256) that complete on an mbarrier; no thread
+// spends instructions on the copy and the data does not pass through registers or L1.  Clip-edge tiles
+// (reflect padding) and unaligned inputs fall back to cooperative loads.
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MIXFE_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MIXFE_DONE_%=;\n"
+        "bra MIXFE_WAIT_%=;\n"
+        "MIXFE_DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+struct K1Stage {                     // where the samples of one (clip, tile, stem) come from
+    const float* gL;
+    const float* gR;
+    long long base;                  // first staged sample (may be negative / run past T at the clip edges)
+    bool tma;
+};
+
+__device__ __forceinline__ K1Stage k1_stage_of(const K1Params& p, int b, int tile, int s) {
+    K1Stage st;
+    st.gL = p.stem[s] + (long long)b * p.stride_b;
+    st.gR = st.gL + p.stride_c;
+    st.base = (long long)tile * kTF * p.hop - kNfft / 2;
+    const bool interior = st.base >= 0 && st.base + p.nxs <= (long long)p.T;
+    st.tma = interior && (p.nxs & 3) == 0 &&
+             ((reinterpret_cast<unsigned long long>(st.gL + st.base) | reinterpret_cast<unsigned long long>(st.gR + st.base)) & 15ull) == 0;
+    return st;
+}
+
+// one thread: arm the barrier and start both row copies
+__device__ __forceinline__ void k1_stage_tma(const K1Params& p, const K1Stage& st, float* xsL, unsigned bar) {
+    const unsigned bytes = (unsigned)p.nxs * 4u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // earlier generic reads of xs vs the async writes
+    mbar_expect_tx(bar, 2u * bytes);
+    tma_bulk_g2s(smem_u32(xsL), st.gL + st.base, bytes, bar);
+    tma_bulk_g2s(smem_u32(xsL + p.nxs), st.gR + st.base, bytes, bar);
+}
+
+// all threads: loads with torch's 'reflect' indexing (clip edges) or plain loads (unaligned rows)
+__device__ __forceinline__ void k1_stage_coop(const K1Params& p, const K1Stage& st, float* xsL, int tid) {
+    float* xsR = xsL + p.nxs;
+    for (int i = tid; i < p.nxs; i += kK1Threads) {
+        long long j = st.base + i;
+        if (j < 0) j = -j;                               // torch 'reflect': -i -> i
+        if (j >= p.T) j = 2ll * (p.T - 1) - j;           // T-1+i -> T-1-i
+        j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);        // frames past F only; keeps loads in bounds
+        xsL[i] = __ldg(st.gL + j);
+        xsR[i] = __ldg(st.gR + j);
     }
 }
 
@@ -235,13 +278,15 @@ __device__ __forceinline__ void k1_time_stats(const K1Params& p, float* scratch,
 
 __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_constant__ K1Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    float2* const xs = reinterpret_cast<float2*>(smem);
+    float* const xsL = reinterpret_cast<float*>(smem);                        // [nxs] left, then [nxs] right
     unsigned char* const ex = smem + p.off_ex;                                // 8 warp regions of 8 KB
     float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);              // [31][32], rows k1 = 1..31
     float* const S = reinterpret_cast<float*>(smem + p.off_s);                // [3][2][n_mels_pad][4]
     float* const wsteps = reinterpret_cast<float*>(smem + p.off_wsteps);      // [n_wsteps][32]
     int* const flo = reinterpret_cast<int*>(smem + p.off_flo);                // [n_slots][32]
     float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
+    const unsigned bar = smem_u32(smem + p.off_red + 128);                    // mbarrier of the TMA staging
+    int* const arrivals = reinterpret_cast<int*>(smem + p.off_red + 136);     // warps done reading xs
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long item = blockIdx.x;
@@ -258,7 +303,22 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     float2* const melw = reinterpret_cast<float2*>(region + kMelOff);
 
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
-    k1_stage(p, xs, b, tile, 0, tid);
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        *arrivals = 0;
+    }
+    __syncthreads();
+    bool cur_tma;                    // how the stage about to be consumed was filled (uniform over the CTA)
+    unsigned tma_parity = 0;
+    {
+        const K1Stage st = k1_stage_of(p, b, tile, 0);
+        cur_tma = st.tma;
+        if (st.tma) {
+            if (tid == 0) k1_stage_tma(p, st, xsL, bar);
+        } else {
+            k1_stage_coop(p, st, xsL, tid);
+        }
+    }
 
     // Persistent CTAs that share an SM start together and, with identical work per tile, would stay in
     // lockstep: both in the FP-bound FFT phase, then both in the shared-memory-bound phases.  Delaying
@@ -287,9 +347,15 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
         float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};                     // masking partial sums of this thread
 
         for (int s = 0; s < kNumStems; ++s) {
-            cp_async_wait_all();
+            if (cur_tma) {
+                mbar_wait(bar, tma_parity);
+                tma_parity ^= 1u;
+            }
             __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
-            if (s == 0 && p.want_stats) k1_time_stats(p, reinterpret_cast<float*>(ex), b, tile, tid);
+            if (s == 0 && p.want_stats) {
+                k1_time_stats(p, reinterpret_cast<float*>(ex), b, tile, tid);
+                __syncthreads();             // the scratch (= exchange regions) is dead
+            }
 
             // ---- frame t0 + warp -> registers, Hann window on the fly ------------------------
             cplx64 z[32];                    // (L, R) sample pairs = one complex value each
@@ -297,9 +363,16 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             if (active) {
                 const float2 wl = tw[lane];             // row k1 = 1: exp(-2 pi i lane/1024)
                 const float cb = wl.x, sb = -wl.y;
-                const unsigned xa = smem_u32(xs + warp * p.hop + lane);
+                const unsigned xa = smem_u32(xsL + warp * p.hop + lane);
+                const unsigned xr_off = (unsigned)p.nxs * 4u;
+                float fl[32], fr[32];
 #pragma unroll
-                for (int n1 = 0; n1 < 32; ++n1) z[n1] = lds_c<0>(xa + n1 * 256);     // all 32 loads in flight
+                for (int n1 = 0; n1 < 32; ++n1) {       // all 64 loads in flight before the first multiply
+                    fl[n1] = lds32(xa + n1 * 128);
+                    fr[n1] = lds32(xa + xr_off + n1 * 128);
+                }
+#pragma unroll
+                for (int n1 = 0; n1 < 32; ++n1) z[n1] = cpack(fl[n1], fr[n1]);
 #pragma unroll
                 for (int n1 = 0; n1 < 32; ++n1) {
                     // 0.5 * hann[32 n1 + lane]; cos(a + b) with a = 2 pi n1/32 (immediate), b per lane.
@@ -312,8 +385,6 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     z[n1] = cpack(xl * wv, xr * wv);
                 }
             }
-            __syncthreads();                 // B0': xs is dead, the statistics scratch is dead
-
             // ---- prefetch the next (tile, stem) while this one is transformed -------------------
             {
                 int nb = b, ntile = tile, ns = s + 1;
@@ -322,7 +393,27 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     ntile = (int)(next_item - (long long)nb * p.n_tiles);
                     ns = 0;
                 }
-                if (s + 1 < kNumStems || next_item < p.total_items) k1_stage(p, xs, nb, ntile, ns, tid);
+                const bool have_next = s + 1 < kNumStems || next_item < p.total_items;
+                bool next_tma = false;
+                if (have_next) {
+                    const K1Stage st = k1_stage_of(p, nb, ntile, ns);
+                    next_tma = st.tma;
+                    if (st.tma) {
+                        // no CTA barrier: the last warp to finish reading xs starts the copy
+                        __syncwarp();
+                        if (lane == 0) {
+                            __threadfence_block();
+                            if (atomicAdd(arrivals, 1) == kK1Threads / 32 - 1) {
+                                *arrivals = 0;
+                                k1_stage_tma(p, st, xsL, bar);
+                            }
+                        }
+                    } else {
+                        __syncthreads();     // B0': every warp has its frame in registers, xs is dead
+                        k1_stage_coop(p, st, xsL, tid);
+                    }
+                }
+                cur_tma = next_tma;
                 if (ns == 0 && next_item < p.total_items && p.want_stats) {
                     // pull the hop region the next tile owns towards L2 for stems 1..3 (stem 0 comes with its
                     // staging): the statistics loads at the top of the next tile then hit L2 instead of HBM
@@ -541,7 +632,6 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
         b = (int)(item / p.n_tiles);
         tile = (int)(item - (long long)b * p.n_tiles);
     }
-    cp_async_wait_all();
 }
 
 // ------------------------------------------------------------------------------------------------

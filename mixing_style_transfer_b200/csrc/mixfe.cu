@@ -160,7 +160,7 @@ int build_mel_tables(mixfe_plan* pl) {
     pl->off_wsteps = pl->off_s + 3 * pl->n_mels_pad * 8 * 4;
     pl->off_flo = align16(pl->off_wsteps + n_wsteps * 32 * 4);
     pl->off_red = align16(pl->off_flo + n_slots * 32 * 4);
-    pl->smem_k1 = pl->off_red + 8 * 4 * 4;
+    pl->smem_k1 = pl->off_red + 8 * 4 * 4 + 32;          // masking scratch, mbarrier, arrival counter
     if (pl->smem_k1 > 227 * 1024)
         return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
     MIXFE_CUDA(cudaFuncSetAttribute(k1_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_k1));
