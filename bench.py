@@ -266,9 +266,7 @@ def run_native(args):
         if with_aug:
             # negatives (clips 48..71) = augment_stems(anchors 0..23), written in place into the batch
             anchors = {n: s[0:N_CLIPS // 3] for n, s in zip(pkg.STEMS, stems)}
-            neg = aug.apply(anchors, decisions)
-            for s, n in zip(stems, pkg.STEMS):
-                s[2 * N_CLIPS // 3:].copy_(neg[n])
+            aug.apply(anchors, decisions, out={n: s[2 * N_CLIPS // 3:] for n, s in zip(pkg.STEMS, stems)})
         plan.features_logmel(stems, True, True, features_out=f_out, logmel_out=lm_out)
 
     sampler = ClockSampler(local_rank)

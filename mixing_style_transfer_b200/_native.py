@@ -223,11 +223,21 @@ class Plan:
                                                _stream(self.device)))
         return out
 
-    def augment(self, stems: Sequence[torch.Tensor], params, impulse: Optional[torch.Tensor]):
-        """stems: 4 CUDA tensors (B,2,T); params: ctypes array of B AugParams; impulse (B,L) or None."""
+    def augment(self, stems: Sequence[torch.Tensor], params, impulse: Optional[torch.Tensor],
+                outs: Optional[Sequence[torch.Tensor]] = None):
+        """stems: 4 CUDA tensors (B,2,T); params: ctypes array of B AugParams; impulse (B,L) or None.
+        outs: optional 4 preallocated CUDA tensors with the inputs' shape AND strides (the C ABI addresses
+        input and output with one pair of strides), not aliasing the inputs."""
         st, sb, sc = unify_stems(stems)
         B, _, T = st[0].shape
-        outs = [torch.empty_strided(s.shape, s.stride(), dtype=torch.float32, device=self.device) for s in st]
+        if outs is None:
+            outs = [torch.empty_strided(s.shape, s.stride(), dtype=torch.float32, device=self.device) for s in st]
+        else:
+            outs = list(outs)
+            for o, s in zip(outs, st):
+                if (o.shape != s.shape or o.stride() != s.stride() or o.dtype != torch.float32
+                        or o.device != s.device):
+                    raise ValueError("augment: `outs` must match the inputs' shape, strides, dtype and device")
         pin = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
         pout = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in outs])
         L = 0

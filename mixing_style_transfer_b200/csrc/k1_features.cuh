@@ -14,13 +14,15 @@
 //
 // Work decomposition.  Persistent CTAs (2 per SM) of 8 warps stride over (clip, frame-tile) items;
 // a tile is TF = 8 consecutive frames and the CTA walks its 4 stems.  Per (tile, stem):
-//   stage   samples [t0*hop - 512, t0*hop + 7*hop + 512) of L and R, reflect-padded at the clip
-//           edges, interleaved as float2 in shared memory.  Interior tiles use cp.async, issued one
-//           (tile, stem) AHEAD -- right after every warp has pulled its frame into registers -- so
-//           the copy overlaps the FFT phase of the current stem.
-//   FFT     one warp per frame: Hann window on the fly, 32 x 32 four-step FFT with the
-//           transposition through a swizzled warp-private shared buffer, L/R untangled with warp
-//           shuffles; the 513 (L, R) powers go to a warp-private column in the same buffer
+//   stage   samples [t0*hop - 512, t0*hop + 7*hop + 512) of L and R as two planar rows in shared memory.
+//           Interior tiles: two TMA bulk copies (cp.async.bulk + mbarrier) issued by ONE thread, one
+//           (tile, stem) AHEAD -- by the last warp that has pulled its frame into registers, without a
+//           CTA barrier -- so the copy overlaps the FFT phase of the current stem.  Clip-edge tiles
+//           (torch 'reflect' padding) and unaligned inputs: cooperative loads.
+//   FFT     one warp per frame: Hann window on the fly, 32 x 32 four-step FFT on packed (re, im) register
+//           pairs (FADD2 butterflies), the transposition through a swizzled warp-private shared buffer
+//           with the twiddle loads software-pipelined, L/R untangled with warp shuffles; the 513 (L, R)
+//           powers go to a warp-private column in the same buffer
 //   mel     WARP-LOCAL: lane l owns filters l, 32+l, 64+l, 96+l of its warp's frame and walks their
 //           contiguous support (weights from a [step][lane] table, powers at lo(filter)+step);
 //           no CTA barrier between FFT and mel.  Result: 128 x (L, R) mel powers per warp.

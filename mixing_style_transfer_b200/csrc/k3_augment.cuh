@@ -27,7 +27,7 @@ namespace mixfe {
 
 constexpr int kAugV = 16;                 // samples per lane per block
 constexpr int kAugBlock = 32 * kAugV;     // 512 samples per warp step
-constexpr int kAugWarps = 4;              // warps per CTA, one chunk each
+constexpr int kAugWarps = kNumStems;      // warps per CTA, one stem each
 
 struct AugClipDev {                        // per-clip decisions in kernel form
     float gain[kNumStems];
@@ -152,20 +152,23 @@ __device__ __forceinline__ float compress_static(float x) {
     return x > 0.0f ? mag : (x < 0.0f ? -mag : (x == 0.0f ? 0.0f * mag : x));     // torch.sign: 0 -> 0, NaN -> NaN
 }
 
-__global__ void __launch_bounds__(kAugWarps * 32) k3_augment(const __grid_constant__ K3Params p) {
+__global__ void __launch_bounds__(kAugWarps * 32, 4) k3_augment(const __grid_constant__ K3Params p) {
     __shared__ SecTables tables[kAugWarps][3];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int chunk = blockIdx.x * kAugWarps + warp;
+    // one warp per (chunk, channel, clip, stem): the four warps of a CTA take the four stems of one chunk
+    // (4x the warps of a stem-sequential walk; the scan is latency-bound and needs them)
+    const int chunk = blockIdx.x;
     const int ch = blockIdx.y, b = blockIdx.z;
-    if (chunk >= p.n_chunks) return;                        // whole warp leaves together
     const AugClipDev& cp = p.clips[b];
     const long long row = (long long)b * p.stride_b + (long long)ch * p.stride_c;
     const long long c0 = (long long)chunk * p.chunk;
     const long long c1 = c0 + p.chunk < p.T ? c0 + p.chunk : p.T;
 
-    for (int s = 0; s < kNumStems; ++s) {
-        const float* __restrict__ src = p.in[s] + row;
-        float* __restrict__ dst = p.out[s] + row;
+    {
+        const int s = warp;
+        // (selects, not p.in[s]: a runtime index into kernel parameters would copy them to local memory)
+        const float* __restrict__ src = (s == 0 ? p.in[0] : s == 1 ? p.in[1] : s == 2 ? p.in[2] : p.in[3]) + row;
+        float* __restrict__ dst = (s == 0 ? p.out[0] : s == 1 ? p.out[1] : s == 2 ? p.out[2] : p.out[3]) + row;
         const int flags = cp.flags[s];
         const float gain = cp.gain[s];
         const bool tilt = flags & 1, comp = flags & 2, bw = flags & 4;
@@ -182,19 +185,29 @@ __global__ void __launch_bounds__(kAugWarps * 32) k3_augment(const __grid_consta
         const bool vec_ok = ((reinterpret_cast<unsigned long long>(src) | reinterpret_cast<unsigned long long>(dst)) & 15ull) == 0;
         double cr[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
         double energy = 0.0;
+        // the next block's samples are requested before this block's (long, serial) arithmetic starts
+        auto fetch = [&](long long blk, float4 (&q)[kAugV / 4]) {
+            const long long i0 = blk + (long long)lane * kAugV;
+            if (blk < c1 && vec_ok && i0 + kAugV <= p.T) {
+#pragma unroll
+                for (int j = 0; j < kAugV / 4; ++j) q[j] = __ldg(reinterpret_cast<const float4*>(src + i0) + j);
+            }
+        };
+        float4 qn[kAugV / 4];
+        fetch(start, qn);
         for (long long blk = start; blk < c1; blk += kAugBlock) {
             const long long i0 = blk + (long long)lane * kAugV;
             float x[kAugV];
             if (vec_ok && i0 + kAugV <= p.T) {
 #pragma unroll
                 for (int j = 0; j < kAugV / 4; ++j) {
-                    const float4 q = __ldg(reinterpret_cast<const float4*>(src + i0) + j);
-                    x[4 * j] = q.x; x[4 * j + 1] = q.y; x[4 * j + 2] = q.z; x[4 * j + 3] = q.w;
+                    x[4 * j] = qn[j].x; x[4 * j + 1] = qn[j].y; x[4 * j + 2] = qn[j].z; x[4 * j + 3] = qn[j].w;
                 }
             } else {
 #pragma unroll
                 for (int n = 0; n < kAugV; ++n) x[n] = i0 + n < p.T ? __ldg(src + i0 + n) : 0.0f;
             }
+            fetch(blk + kAugBlock, qn);
 #pragma unroll
             for (int n = 0; n < kAugV; ++n) x[n] *= gain;
             if (filtered) {

@@ -345,7 +345,7 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     p3.part_energy = reinterpret_cast<double*>(ws + o_energy);
     {
         KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
-        k3_augment<<<dim3((n_chunks + kAugWarps - 1) / kAugWarps, 2, B), kAugWarps * 32, 0, stream>>>(p3);
+        k3_augment<<<dim3(n_chunks, 2, B), kAugWarps * 32, 0, stream>>>(p3);
     }
     MIXFE_CUDA(cudaGetLastError());
     launch_counter()++;

@@ -289,8 +289,10 @@ class AudioAugmenter:
         decisions = [self.draw(tuple(stems_dict.keys()), imp_dev) for _ in range(B)]
         return self.apply(stems_dict, decisions)
 
-    def apply(self, stems_dict, decisions: List[ClipAugmentation]):
-        """Run the augmentation kernels with explicit decisions (one per clip)."""
+    def apply(self, stems_dict, decisions: List[ClipAugmentation], out=None):
+        """Run the augmentation kernels with explicit decisions (one per clip).  `out`: optional dict of
+        preallocated CUDA tensors (same shapes and strides as the inputs, e.g. the negatives' slice of the
+        batch the anchors live in) that receive the augmented stems -- no extra copy."""
         first = stems_dict[STEMS[0]]
         src_device = first.device
         device = _resolve_device(first, self._device)
@@ -308,7 +310,12 @@ class AudioAugmenter:
             for b, d in enumerate(decisions):
                 if d.impulse is not None:
                     impulse[b].copy_(d.impulse.to(device, torch.float32), non_blocking=True)
-        outs = self._plan(device).augment(stems, self._pack(decisions), impulse)
+        pre = None
+        if out is not None:
+            pre = [out[n] if out[n].dim() == 3 else out[n].unsqueeze(0) for n in STEMS]
+        outs = self._plan(device).augment(stems, self._pack(decisions), impulse, pre)
+        if out is not None:
+            return {k: out[k] for k in stems_dict.keys()}
         result = {}
         for name, y in zip(STEMS, outs):
             if not batched:

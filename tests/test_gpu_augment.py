@@ -154,6 +154,29 @@ def test_batched_clips_with_individual_decisions(cuda_device):
         assert err < 5e-6, (i, err)
 
 
+def test_apply_writes_into_a_slice_of_the_batch(cuda_device):
+    """`out=`: the negatives are written straight into their slice of the tensor the anchors live in."""
+    T = 20000
+    clips = [O.musical_clip(s, T) for s in (5, 6)]
+    pars = []
+    for s in (5, 6):
+        torch.manual_seed(200 + s)
+        pars.append(O.draw_clip_aug(prob=1.0))
+    batch = {n: torch.zeros(6, 2, T, device=cuda_device) for n in O.STEMS}
+    for n in O.STEMS:
+        batch[n][0:2] = torch.stack([c[n] for c in clips]).to(cuda_device)
+    aug = pkg.AudioAugmenter()
+    dec = [_decisions_from_oracle(p) for p in pars]
+    ret = aug.apply({n: batch[n][0:2] for n in O.STEMS}, dec, out={n: batch[n][4:6] for n in O.STEMS})
+    fresh = aug.apply({n: batch[n][0:2] for n in O.STEMS}, dec)
+    for n in O.STEMS:
+        assert ret[n].data_ptr() == batch[n][4:6].data_ptr()
+        assert torch.equal(batch[n][4:6], fresh[n])
+        assert float(batch[n][2:4].abs().max()) == 0.0                    # neighbours untouched
+    with pytest.raises(ValueError):
+        aug.apply({n: batch[n][0:2] for n in O.STEMS}, dec, out={n: torch.empty(2, 2, T + 1, device=cuda_device) for n in O.STEMS})
+
+
 def test_augment_stems_draws_like_the_reference(cuda_device):
     """augment_stems consumes the global RNG in the reference's order (checked on CPU in test_host_logic);
     here: same seed twice -> identical output, inputs untouched."""

@@ -161,6 +161,40 @@ def test_strided_views_and_cpu_inputs(fe, cuda_device):
     assert_features_close(out, O.mixing_features(cpu_clip), fe.feature_names(), "cpu input")
 
 
+def test_unaligned_rows_take_the_cooperative_staging_path(fe, cuda_device):
+    """Rows that are not 16-byte aligned cannot be staged by TMA bulk copies nor read with 128-bit loads:
+    interior tiles then go through the cooperative fallback.  Same numbers either way."""
+    g = torch.Generator().manual_seed(12)
+    big = (torch.rand(2, 8, 12000, generator=g) * 2 - 1) * 0.3
+    dev_big = big.to(cuda_device)
+    for off, T in ((501, 9001), (3, 11997), (500, 9000)):
+        views = {n: dev_big[:, 2 * i:2 * i + 2, off:off + T] for i, n in enumerate(O.STEMS)}
+        f, lm = fe.features_and_logmel(views)
+        for b in range(2):
+            clip = {n: big[b, 2 * i:2 * i + 2, off:off + T].contiguous() for i, n in enumerate(O.STEMS)}
+            assert_features_close(f[b], O.mixing_features(clip), fe.feature_names(), f"offset {off} clip {b}")
+            ref = O.log_mel({n: v[None] for n, v in clip.items()})
+            assert float((lm[b].cpu() - ref[0]).abs().max()) < 5e-3
+        # and bit-identical to the aligned (TMA) path on a contiguous copy of the same samples
+        f2, lm2 = fe.features_and_logmel({n: v.contiguous() for n, v in views.items()})
+        assert torch.equal(lm, lm2)
+        assert torch.allclose(f, f2, rtol=1e-5, atol=1e-6)           # statistics sum in a different order
+
+
+def test_thirty_second_clips_of_the_offline_sweep(fe, cuda_device):
+    """BASELINE config 4 shape: 30 s clips (T = 1 323 000, F = 5168); clip 0 against the oracle."""
+    B, T = 3, 1323000
+    g = torch.Generator(device=cuda_device).manual_seed(4096)
+    batch = {n: (torch.rand(B, 2, T, device=cuda_device, generator=g) * 2 - 1) * 0.2 for n in O.STEMS}
+    f, lm = fe.features_and_logmel(batch)
+    assert lm.shape == (B, 8, 128, 5168) and f.shape == (B, 64)
+    clip0 = {n: batch[n][0].cpu() for n in O.STEMS}
+    assert_features_close(f[0], O.mixing_features(clip0), fe.feature_names(), "30 s clip 0")
+    ref = O.log_mel({n: v[None] for n, v in clip0.items()})
+    assert float((lm[0].cpu() - ref[0]).abs().max()) < 5e-3
+    assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 2     # the shared-memory budget keeps 2 CTAs / SM
+
+
 def test_full_size_properties(fe, cuda_device):
     """BASELINE config 2 shape (a slice of it): properties that need no oracle run.
     Gain linearity: scaling every stem by 2 adds ln 4 to the log-mel (where mel >> 1e-10), leaves the
