@@ -10,6 +10,7 @@
 
 #include "common.cuh"
 #include "k1_features.cuh"
+#include "k1g_features.cuh"
 #include "plan.cuh"
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
@@ -170,6 +171,65 @@ int build_mel_tables(mixfe_plan* pl) {
     return MIXFE_OK;
 }
 
+// CSR form of the filterbank + window + twiddles + shared-memory map of the generic kernel K1G.
+int build_generic_tables(mixfe_plan* pl) {
+    const int nf = pl->n_freq, nm = pl->n_mels, n = pl->n_fft;
+    std::vector<int> lo(nm, 0), len(nm, 0), off(nm, 0);
+    std::vector<float> w;
+    for (int m = 0; m < nm; ++m) {
+        int first = -1, last = -1;
+        for (int k = 0; k < nf; ++k)
+            if (pl->fb[(size_t)k * nm + m] != 0.0f) { if (first < 0) first = k; last = k; }
+        off[m] = (int)w.size();
+        if (first >= 0) {
+            lo[m] = first; len[m] = last - first + 1;
+            for (int k = first; k <= last; ++k) w.push_back(pl->fb[(size_t)k * nm + m]);
+        }
+    }
+    if (w.empty()) w.push_back(0.0f);
+    std::vector<float2> tw(n / 2);
+    for (int e = 0; e < n / 2; ++e) {
+        const double a = -2.0 * M_PI * (double)e / (double)n;
+        tw[e] = make_float2((float)std::cos(a), (float)std::sin(a));
+    }
+    // torch.hann_window(n, periodic=True) is evaluated in fp32 by torch; the Python layer hands over the exact
+    // buffer through mixfe_plan_set_window when it matters.  Default: double precision, rounded once.
+    std::vector<float> win(n);
+    for (int i = 0; i < n; ++i) win[i] = (float)(0.5 * (0.5 - 0.5 * std::cos(2.0 * M_PI * (double)i / (double)n)));
+    int rc;
+    if ((rc = upload(&pl->d_mel_lo, lo)) || (rc = upload(&pl->d_mel_len, len)) || (rc = upload(&pl->d_mel_off, off)) ||
+        (rc = upload(&pl->d_mel_w, w)) || (rc = upload(&pl->d_twg, tw)) || (rc = upload(&pl->d_win, win)))
+        return rc;
+    pl->g_log2n = 0;
+    while ((1 << pl->g_log2n) < n) ++pl->g_log2n;
+    pl->g_pw_stride = (n / 2 + 1) | 1;
+    const int per_frame = n * 8 + pl->g_pw_stride * 8;
+    int nfr = kTF;
+    while (nfr > 1 && nfr * per_frame > 160 * 1024) nfr >>= 1;
+    pl->g_nf = nfr;
+    pl->g_off_pw = nfr * n * 8;
+    const int stage = std::max(pl->g_off_pw + nfr * pl->g_pw_stride * 8, 33 * kK1Threads * 4);   // also the statistics scratch
+    pl->g_off_mel = align16(stage);
+    pl->g_off_S = pl->g_off_mel + kTF * pl->n_mels_pad * 8;
+    pl->g_off_red = pl->g_off_S + kNumStems * kTF * pl->n_mels_pad * 4;
+    pl->smem_g = pl->g_off_red + 8 * 4 * 4;
+    if (pl->smem_g > 227 * 1024) return fail(MIXFE_EUNSUPPORTED, "K1G needs %d bytes of shared memory", pl->smem_g);
+    MIXFE_CUDA(cudaFuncSetAttribute(k1g_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_g));
+    return MIXFE_OK;
+}
+
+// Which kernel serves the plan: K1 for n_fft = 1024 when its shared-memory map fits, else K1G.
+int build_tables(mixfe_plan* pl) {
+    int rc = build_generic_tables(pl);
+    if (rc) return rc;
+    const char* force = getenv("MIXFE_FORCE_GENERIC");
+    pl->use_generic = true;
+    if (pl->n_fft == kNfft && !(force && atoi(force))) {
+        if (build_mel_tables(pl) == MIXFE_OK) pl->use_generic = false;
+    }
+    return MIXFE_OK;
+}
+
 int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B,
                  int T, float* features, float* logmel, long long lm_stride_b, float* melpow,
                  long long mp_stride_b, cudaStream_t stream) {
@@ -210,7 +270,18 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     }
     p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_wsteps = pl->off_wsteps;
     p.off_flo = pl->off_flo; p.off_red = pl->off_red;
-    {
+    if (pl->use_generic) {
+        K1GParams g{};
+        g.base = p;
+        g.n_fft = pl->n_fft; g.log2n = pl->g_log2n; g.nf = pl->g_nf;
+        g.twg = pl->d_twg; g.win = pl->d_win;
+        g.mel_lo = pl->d_mel_lo; g.mel_len = pl->d_mel_len; g.mel_off = pl->d_mel_off; g.mel_w = pl->d_mel_w;
+        g.pw_stride = pl->g_pw_stride; g.off_pw = pl->g_off_pw; g.off_mel = pl->g_off_mel; g.off_S = pl->g_off_S;
+        g.off_red = pl->g_off_red;
+        if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "K1G: B=%d > 65535 clips per call", B);
+        KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
+        k1g_features<<<dim3(n_tiles, B), kGThreads, pl->smem_g, stream>>>(g);
+    } else {
         KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
         const int grid = (int)std::min<long long>(p.total_items, pl->k1_ctas);
         k1_features<<<grid, kK1Threads, pl->smem_k1, stream>>>(p);
@@ -248,8 +319,8 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     *out = nullptr;
     if (sample_rate <= 0 || hop <= 0 || n_mels <= 0 || n_spectral_bins < 0)
         return fail(MIXFE_EINVAL, "bad plan arguments");
-    if (n_fft != kNfft)
-        return fail(MIXFE_EUNSUPPORTED, "n_fft=%d: this build's fused STFT kernel covers n_fft=1024 only", n_fft);
+    if (n_fft < 64 || n_fft > 4096 || (n_fft & (n_fft - 1)))
+        return fail(MIXFE_EUNSUPPORTED, "n_fft=%d: the STFT kernels cover powers of two in [64, 4096]", n_fft);
     if (n_mels > kMaxMels) return fail(MIXFE_EUNSUPPORTED, "n_mels=%d > %d", n_mels, kMaxMels);
     if (n_spectral_bins > n_mels)
         return fail(MIXFE_EINVAL, "n_spectral_bins=%d > n_mels=%d (the reference's torch.stack raises)",
@@ -287,7 +358,7 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     int rc = upload(&pl->d_tw, tw);
     if (!rc) rc = upload(&pl->d_twfine, twf);
     if (!rc) rc = upload(&pl->d_twlin, twl);
-    if (!rc) rc = build_mel_tables(pl);
+    if (!rc) rc = build_tables(pl);
     if (rc) { mixfe_plan_destroy(pl); return rc; }
     *out = pl;
     return MIXFE_OK;
@@ -298,6 +369,8 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev); cudaFree(pl->d_sm_ticket);
+    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
+    cudaFree(pl->d_mel_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;
@@ -308,7 +381,7 @@ int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
     DeviceGuard guard(pl->device);
     MIXFE_CUDA(cudaDeviceSynchronize());            // tables may be in use by queued launches
     pl->fb.assign(fb_host, fb_host + (size_t)pl->n_freq * pl->n_mels);
-    return build_mel_tables(pl);
+    return build_tables(pl);
 }
 
 int mixfe_plan_enable_timing(mixfe_plan* pl, int enable) {
@@ -345,6 +418,12 @@ size_t mixfe_workspace_bytes(const mixfe_plan* pl) { return pl ? pl->ws_bytes : 
 
 int mixfe_debug_feature_kernel_config(const mixfe_plan* pl, int* ctas_per_sm, int* smem_bytes, int* mel_steps) {
     if (!pl) return fail(MIXFE_EINVAL, "null plan");
+    if (pl->use_generic) {                      // K1G: one CTA per (clip, tile); ctas_per_sm = 0 marks the generic path
+        if (ctas_per_sm) *ctas_per_sm = 0;
+        if (smem_bytes) *smem_bytes = pl->smem_g;
+        if (mel_steps) *mel_steps = 0;
+        return MIXFE_OK;
+    }
     if (ctas_per_sm) *ctas_per_sm = pl->n_sms ? pl->k1_ctas / pl->n_sms : 0;
     if (smem_bytes) *smem_bytes = pl->smem_k1;
     if (mel_steps) *mel_steps = pl->n_wsteps;

@@ -18,6 +18,15 @@ struct mixfe_plan {
     unsigned* d_sm_ticket = nullptr;    // per-SM arrival counters of K1's persistent CTAs (phase skew)
     int k1_skew_ns = 0;
     int off_ex = 0, off_tw = 0, off_s = 0, off_wsteps = 0, off_flo = 0, off_red = 0;
+    // K1G (k1g_features.cuh): generic power-of-two n_fft path; used when K1 does not cover the configuration
+    bool use_generic = false;
+    float2* d_twg = nullptr;            // [n_fft/2] exp(-2 pi i e / n_fft)
+    float* d_win = nullptr;             // [n_fft] 0.5 * periodic hann
+    int* d_mel_lo = nullptr;            // CSR form of the filterbank: first bin, length, weight offset per filter
+    int* d_mel_len = nullptr;
+    int* d_mel_off = nullptr;
+    float* d_mel_w = nullptr;
+    int g_nf = 0, g_log2n = 0, g_pw_stride = 0, g_off_pw = 0, g_off_mel = 0, g_off_S = 0, g_off_red = 0, smem_g = 0;
     // plan-owned workspace (grows to the high-water mark, then never reallocates)
     void* ws = nullptr;
     size_t ws_bytes = 0;

@@ -1,0 +1,95 @@
+"""GPU parity of the generic STFT kernel K1G (csrc/k1g_features.cuh): the constructor arguments the reference's
+evaluation / style-transfer callers use, MixingFeatureExtractor(44100, 2048, 512, 80)
+(inference/validate_retrieval.py:355, src/train_style_transfer.py:523-533), other power-of-two n_fft, and
+K1G against K1 on the training configuration.  Same tolerances as test_gpu_features.py."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+import mixing_style_transfer_b200 as pkg
+from oracle import mixfe_oracle as O
+from tests._util import assert_features_close, assert_melpower_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _to(clip, dev):
+    return {n: v.to(dev) for n, v in clip.items()}
+
+
+CONFIGS = [(2048, 512, 80), (512, 128, 64), (4096, 1024, 128), (256, 64, 40), (1024, 512, 96), (2048, 256, 128)]
+
+
+@pytest.mark.parametrize("n_fft,hop,n_mels", CONFIGS)
+@pytest.mark.parametrize("T", [44100, 30001])
+def test_features_melpower_logmel_vs_oracle(cuda_device, n_fft, hop, n_mels, T):
+    cfg = O.FrontEndConfig(n_fft=n_fft, hop_length=hop, n_mels=n_mels)
+    clip = O.musical_clip(n_fft + T, T)
+    dclip = _to(clip, cuda_device)
+    fe = pkg.MixingFeatureExtractor(44100, n_fft, hop, n_mels)
+    assert fe.get_feature_dim() == 64
+    got = fe.extract_all_features(dclip)
+    assert_features_close(got, O.mixing_features(clip, cfg), fe.feature_names(), f"{n_fft}/{hop}/{n_mels} T={T}")
+    ofe = O.MelFrontEnd(cfg)
+    ref = torch.cat([ofe.mel_power(clip[n][None]) for n in O.STEMS], dim=1)
+    mp = fe._plan(cuda_device).debug_mel_power([dclip[n][None] for n in O.STEMS])
+    assert mp.shape == ref.shape == (1, 8, n_mels, 1 + T // hop)
+    assert_melpower_close(mp, ref, f"{n_fft}/{hop}/{n_mels} T={T}")
+    pre = pkg.MelSpectrogramPreprocessor(44100, n_fft, hop, n_mels)
+    lm = pre({n: v[None] for n, v in dclip.items()})
+    ref_lm = O.log_mel({n: v[None] for n, v in clip.items()}, cfg)
+    assert lm.shape == ref_lm.shape
+    assert float((lm.cpu() - ref_lm).abs().max()) < 5e-3
+
+
+def test_generic_kernel_serves_non_1024_plans(cuda_device):
+    fe = pkg.MixingFeatureExtractor(44100, 2048, 512, 80)
+    assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 0          # K1G marker
+    assert pkg.MixingFeatureExtractor()._plan(cuda_device).k1_config()["ctas_per_sm"] >= 1
+
+
+def test_batched_2048_matches_per_clip(cuda_device):
+    fe = pkg.MixingFeatureExtractor(44100, 2048, 512, 80)
+    clips = [O.musical_clip(100 + i, 40000) for i in range(3)]
+    batch = {n: torch.stack([c[n] for c in clips]).to(cuda_device) for n in O.STEMS}
+    fb, lb = fe.features_and_logmel(batch)
+    for i, c in enumerate(clips):
+        f1, l1 = fe.features_and_logmel(_to(c, cuda_device))
+        assert torch.equal(fb[i], f1) and torch.equal(lb[i], l1[0] if l1.dim() == 4 else l1)
+
+
+def test_short_clip_raises_for_2048(cuda_device):
+    fe = pkg.MixingFeatureExtractor(44100, 2048, 512, 80)
+    with pytest.raises(RuntimeError, match="[Pp]adding"):
+        fe.extract_all_features({n: torch.zeros(2, 1024, device=cuda_device) for n in O.STEMS})
+
+
+_FORCED = r"""
+import sys, torch
+sys.path.insert(0, %r)
+import mixing_style_transfer_b200 as pkg
+from oracle import mixfe_oracle as O
+from tests._util import assert_features_close, assert_melpower_close
+dev = torch.device("cuda", 0)
+fe = pkg.MixingFeatureExtractor()
+assert fe._plan(dev).k1_config()["ctas_per_sm"] == 0
+for T in (2048, 30001, 66150):
+    clip = O.musical_clip(T, T)
+    d = {n: v.to(dev) for n, v in clip.items()}
+    assert_features_close(fe.extract_all_features(d), O.mixing_features(clip), fe.feature_names(), "forced generic")
+    ofe = O.MelFrontEnd(O.FrontEndConfig())
+    ref = torch.cat([ofe.mel_power(clip[n][None]) for n in O.STEMS], dim=1)
+    assert_melpower_close(fe._plan(dev).debug_mel_power([d[n][None] for n in O.STEMS]), ref, "forced generic")
+print("forced-generic ok")
+"""
+
+
+def test_generic_kernel_on_training_config(cuda_device):
+    """MIXFE_FORCE_GENERIC=1 routes (1024, 256, 128) through K1G: same oracle, same tolerances as K1."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MIXFE_FORCE_GENERIC="1")
+    res = subprocess.run([sys.executable, "-c", _FORCED % root], env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and "forced-generic ok" in res.stdout, res.stdout + res.stderr
