@@ -44,16 +44,18 @@ constexpr int kK1Threads = 256;    // 8 warps, one frame each
 constexpr int kNfft = 1024;
 constexpr int kNfreq = 513;
 constexpr int kTdN = 40;           // floats per tile of time-domain partials
-constexpr int kMaxSlots = 4;       // mel filters per lane (n_mels <= 128)
+constexpr int kMaxMels = 128;
 // warp-private shared region (8 KB): [0, 8192) exchange during the FFT; afterwards
-//   [0, kPvBytes)                 (L, R) power column, bins 0..512 + zero-weight overshoot
-//   [kPvBytes, +1024)             this frame's 128 x (L, R) mel powers
-//   [kLogOff, +1024)              1/8 of the CTA's log tile (16 mel rows x 16 columns)
+//   [skew, skew + 8 * 544)        (L, R) power column of the warp's frame, bins 0..512 + zero-weight overshoot;
+//                                 skew = 64 bytes for frames 2, 3, 6, 7 (the frame pairs that are read in the
+//                                 same half-warp phase of the mel walk then sit 16 banks apart)
+//   [kLogOff + 576 ch + 8 t, +512) row (ch, t = frame) of the CTA's log tile, 128 mel values; word offset
+//                                 = 2 * (8 ch + t) mod 32, so the transposed read of the store phase is conflict-free
 constexpr int kWarpRegion = 8192;
 constexpr int kPvEntries = 544;
-constexpr int kPvBytes = kPvEntries * 8;            // 4352
-constexpr int kMelOff = kPvBytes;                   // 4352
-constexpr int kLogOff = kMelOff + 1024;             // 5376
+constexpr int kPvBytes = (kPvEntries + 8) * 8;      // 4416
+constexpr int kLogOff = kPvBytes;
+constexpr int kLogChStride = 576;
 
 struct K1Params {
     const float* stem[kNumStems];
@@ -68,11 +70,10 @@ struct K1Params {
     float2* part_spec;               // [B][n_tiles][4][n_mels_pad] (sum log, sum mel)
     float* part_td;                  // [B][n_tiles][kTdN]
     const float2* tw;                // [1024] tw[k1*32+n2] = exp(-2 pi i n2 k1 / 1024)
-    const float* wsteps;             // [n_wsteps][32] filter weights, slot-major
-    const int* flo;                  // [n_slots][32] byte offset (8 * first bin) of filter 32*slot + lane
-    int n_slots, n_wsteps;
-    int slot_len[kMaxSlots];         // steps per slot (even)
-    int slot_woff[kMaxSlots];        // first step of the slot in wsteps
+    const float* wsteps;             // per group of 8 filters: [steps][8] weights
+    const int* flo;                  // [kMaxMels] byte offset (8 * first walked bin) of each filter in the power column
+    int n_wt;                        // floats in wsteps
+    int wmeta[8][2][4];              // per warp, per group slot: steps (even), weight offset, group index, 0
     int want_stats;
     unsigned* sm_ticket;             // [n_sms] ever-increasing arrival counters, one per SM
     int skew_ns;                     // start delay of every second CTA that lands on an SM (0 = none)
@@ -283,9 +284,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     float* const xsL = reinterpret_cast<float*>(smem);                        // [nxs] left, then [nxs] right
     unsigned char* const ex = smem + p.off_ex;                                // 8 warp regions of 8 KB
     float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);              // [31][32], rows k1 = 1..31
-    float* const S = reinterpret_cast<float*>(smem + p.off_s);                // [3][2][n_mels_pad][4]
-    float* const wsteps = reinterpret_cast<float*>(smem + p.off_wsteps);      // [n_wsteps][32]
-    int* const flo = reinterpret_cast<int*>(smem + p.off_flo);                // [n_slots][32]
+    float4* const S = reinterpret_cast<float4*>(smem + p.off_s);              // [3][256]: thread-private S values of stems 0..2
+    float* const wsteps = reinterpret_cast<float*>(smem + p.off_wsteps);      // [n_wt]
+    int* const flo = reinterpret_cast<int*>(smem + p.off_flo);                // [kMaxMels]
     float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
     const unsigned bar = smem_u32(smem + p.off_red + 128);                    // mbarrier of the TMA staging
     int* const arrivals = reinterpret_cast<int*>(smem + p.off_red + 136);     // warps done reading xs
@@ -296,13 +297,12 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
 
     // ---- constant tables -> shared memory (once per persistent CTA) ----------------------------
     for (int i = tid; i < 31 * 32; i += kK1Threads) tw[i] = p.tw[32 + i];      // rows k1 = 1..31
-    for (int i = tid; i < p.n_wsteps * 32; i += kK1Threads) wsteps[i] = p.wsteps[i];
-    for (int i = tid; i < p.n_slots * 32; i += kK1Threads) flo[i] = p.flo[i];
+    for (int i = tid; i < p.n_wt; i += kK1Threads) wsteps[i] = p.wsteps[i];
+    for (int i = tid; i < kMaxMels; i += kK1Threads) flo[i] = p.flo[i];
 
     unsigned char* const region = ex + warp * kWarpRegion;
     float2* const exw = reinterpret_cast<float2*>(region);
-    float2* const pv = reinterpret_cast<float2*>(region);
-    float2* const melw = reinterpret_cast<float2*>(region + kMelOff);
+    float2* const pv = reinterpret_cast<float2*>(region + ((warp >> 1) & 1) * 64);
 
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
     if (tid == 0) {
@@ -492,96 +492,88 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     cunpack(z[brev5(16)], xr, xi);                           // bin 512 is its own partner
                     pv[512] = make_float2(4.0f * xr * xr, 4.0f * xi * xi);
                 }
-                __syncwarp();
-
-                // ---- warp-local sparse mel projection --------------------------------------------
-#pragma unroll 1
-                for (int j = 0; j < p.n_slots; ++j) {
-                    {
-                        const int e = flo[j * 32 + lane];          // byte offset of the first bin | filter << 16
-                        const unsigned char* pb = region + (e & 0xffff);
-                        const float* wp = wsteps + p.slot_woff[j] * 32 + lane;
-                        float aL = 0.0f, aR = 0.0f, cL = 0.0f, cR = 0.0f, eL = 0.0f, eR = 0.0f, gL = 0.0f, gR = 0.0f;
-                        const int n = p.slot_len[j];
-#pragma unroll 1
-                        for (int i = 0; i < n; i += 4) {
-                            const float2 v0 = *reinterpret_cast<const float2*>(pb + 8 * i);
-                            const float2 v1 = *reinterpret_cast<const float2*>(pb + 8 * i + 8);
-                            const float2 v2 = *reinterpret_cast<const float2*>(pb + 8 * i + 16);
-                            const float2 v3 = *reinterpret_cast<const float2*>(pb + 8 * i + 24);
-                            const float w0 = wp[32 * i], w1 = wp[32 * i + 32], w2 = wp[32 * i + 64], w3 = wp[32 * i + 96];
-                            aL = fmaf(w0, v0.x, aL);
-                            aR = fmaf(w0, v0.y, aR);
-                            cL = fmaf(w1, v1.x, cL);
-                            cR = fmaf(w1, v1.y, cR);
-                            eL = fmaf(w2, v2.x, eL);
-                            eR = fmaf(w2, v2.y, eR);
-                            gL = fmaf(w3, v3.x, gL);
-                            gR = fmaf(w3, v3.y, gR);
-                        }
-                        melw[32 * j + (e >> 16)] = make_float2((aL + cL) + (eL + gL), (aR + cR) + (eR + gR));
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < kMaxSlots; ++j) melw[32 * j + lane] = make_float2(0.0f, 0.0f);
             }
-            __syncthreads();                 // B1: the 8 mel columns of the tile are complete
+            __syncthreads();                 // B1: the 8 power columns of the tile are complete
 
-            // ---- epilogue A: logs, spectral partial sums, S tiles / masking ----------------------
-            for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
-                const int m = r >> 1, ch = r & 1;
-                const float* src = reinterpret_cast<const float*>(ex + kMelOff) + r;
-                float v[8], lg[8];
+            // ---- tile-level mel projection fused with the epilogue ------------------------------------
+            // lane (q = lane >> 3, i = lane & 7) of warp w walks filter i of the warp's two groups over frames
+            // 2q and 2q + 1: per step one weight (shared by the 4 quarters) and two 64-bit (L, R) powers.
+            {
+                const int q = lane >> 3, fi = lane & 7;
+                const bool ok0 = 2 * q < nvalid, ok1 = 2 * q + 1 < nvalid;
+                const unsigned char* col = ex + 2 * q * kWarpRegion + (q & 1) * 64;
+                const long long tile_id = (long long)b * p.n_tiles + tile;
+                float sc[4];                                  // S = (mel_L + mel_R) / 2 of (group a, b) x (frame 2q, 2q+1)
 #pragma unroll
-                for (int t = 0; t < 8; ++t) v[t] = src[t * (kWarpRegion / 4)];
-#pragma unroll
-                for (int t = 0; t < 8; ++t) lg[t] = ln_fast(v[t] + 1e-10f);
-                float slog = 0.0f, smel = 0.0f;
-                if (nvalid == kTF) {
-                    slog = ((lg[0] + lg[1]) + (lg[2] + lg[3])) + ((lg[4] + lg[5]) + (lg[6] + lg[7]));
-                    smel = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-                } else {
-#pragma unroll
-                    for (int t = 0; t < 8; ++t) {
-                        if (t < nvalid) {
-                            slog += lg[t];
-                            smel += v[t];
+                for (int ab = 0; ab < 2; ++ab) {
+                    const int n = p.wmeta[warp][ab][0];
+                    const int m = 8 * p.wmeta[warp][ab][2] + fi;
+                    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, c3 = 0.0f;
+                    if (n > 0) {
+                        const unsigned char* p0 = col + flo[m];
+                        const float* wp = wsteps + p.wmeta[warp][ab][1] + fi;
+#pragma unroll 2
+                        for (int i = 0; i < n; i += 2) {
+                            const float w0 = wp[8 * i], w1 = wp[8 * i + 8];
+                            const float2 u0 = *reinterpret_cast<const float2*>(p0 + 8 * i);
+                            const float2 u1 = *reinterpret_cast<const float2*>(p0 + 8 * i + 8);
+                            const float2 v0 = *reinterpret_cast<const float2*>(p0 + kWarpRegion + 8 * i);
+                            const float2 v1 = *reinterpret_cast<const float2*>(p0 + kWarpRegion + 8 * i + 8);
+                            a0 = fmaf(w0, u0.x, a0);
+                            a1 = fmaf(w0, u0.y, a1);
+                            a2 = fmaf(w0, v0.x, a2);
+                            a3 = fmaf(w0, v0.y, a3);
+                            c0 = fmaf(w1, u1.x, c0);
+                            c1 = fmaf(w1, u1.y, c1);
+                            c2 = fmaf(w1, v1.x, c2);
+                            c3 = fmaf(w1, v1.y, c3);
                         }
                     }
-                }
-                // log tile chunk of 16 mel rows x 16 columns per warp region; float4 slot q is stored at
-                // q ^ ((q >> 3) & 1) so that the 128-bit stores of a quarter-warp hit distinct banks
-                float4* lt = reinterpret_cast<float4*>(ex + (m >> 4) * kWarpRegion + kLogOff);
-                const int q = (m & 15) * 4 + ch * 2;
-                lt[q ^ ((q >> 3) & 1)] = make_float4(lg[0], lg[1], lg[2], lg[3]);
-                lt[(q + 1) ^ ((q >> 3) & 1)] = make_float4(lg[4], lg[5], lg[6], lg[7]);
-                slog += __shfl_xor_sync(kFullMask, slog, 1);
-                smel += __shfl_xor_sync(kFullMask, smel, 1);
-                if (ch == 0 && p.want_stats)
-                    p.part_spec[(((long long)b * p.n_tiles + tile) * kNumStems + s) * p.n_mels_pad + m] =
-                        make_float2(slog, smel);
-            }
-            if (p.want_stats) {
-                for (int r = tid; r < 2 * p.n_mels_pad; r += kK1Threads) {
-                    const int h = r >= p.n_mels_pad ? 1 : 0, m = r - h * p.n_mels_pad;   // h selects frames 4h .. 4h+3
-                    float sc[4];
+                    const float v[4] = {a0 + c0, a1 + c1, a2 + c2, a3 + c3};     // (frame 2q: L, R), (frame 2q+1: L, R)
+                    float lg[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float2 lr = *reinterpret_cast<const float2*>(ex + (4 * h + i) * kWarpRegion + kMelOff + m * 8);
-                        sc[i] = 0.5f * (lr.x + lr.y);
+                    for (int k = 0; k < 4; ++k) lg[k] = ln_fast(v[k] + 1e-10f);
+                    if (m < p.n_mels_pad) {
+                        // row (ch, t) of the log tile lives in region t
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int t = 2 * q + (k >> 1), ch = k & 1;
+                            *reinterpret_cast<float*>(ex + t * kWarpRegion + kLogOff + ch * kLogChStride + t * 8 + m * 4) = lg[k];
+                        }
                     }
+                    if (p.melpow && m < p.n_mels) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int t = 2 * q + (k >> 1), ch = k & 1;
+                            if (t < nvalid)
+                                p.melpow[(long long)b * p.mp_stride_b + ((long long)(2 * s + ch) * p.n_mels + m) * p.F + t0 + t] = v[k];
+                        }
+                    }
+                    if (p.want_stats) {
+                        float slog = (ok0 ? lg[0] + lg[1] : 0.0f) + (ok1 ? lg[2] + lg[3] : 0.0f);
+                        float smel = (ok0 ? v[0] + v[1] : 0.0f) + (ok1 ? v[2] + v[3] : 0.0f);
+                        slog += __shfl_xor_sync(kFullMask, slog, 8);
+                        smel += __shfl_xor_sync(kFullMask, smel, 8);
+                        slog += __shfl_xor_sync(kFullMask, slog, 16);
+                        smel += __shfl_xor_sync(kFullMask, smel, 16);
+                        if (q == 0 && m < p.n_mels_pad)
+                            p.part_spec[(tile_id * kNumStems + s) * p.n_mels_pad + m] = make_float2(slog, smel);
+                    }
+                    sc[2 * ab] = 0.5f * (v[0] + v[1]);
+                    sc[2 * ab + 1] = 0.5f * (v[2] + v[3]);
+                }
+                if (p.want_stats) {
                     if (s < 3) {
-                        *reinterpret_cast<float4*>(S + ((s * 2 + h) * p.n_mels_pad + m) * 4) = make_float4(sc[0], sc[1], sc[2], sc[3]);
-                    } else if (m < p.n_mels) {
-                        const float4 A0 = *reinterpret_cast<const float4*>(S + ((0 * 2 + h) * p.n_mels_pad + m) * 4);
-                        const float4 A1 = *reinterpret_cast<const float4*>(S + ((1 * 2 + h) * p.n_mels_pad + m) * 4);
-                        const float4 A2 = *reinterpret_cast<const float4*>(S + ((2 * 2 + h) * p.n_mels_pad + m) * 4);
+                        S[s * kK1Threads + tid] = make_float4(sc[0], sc[1], sc[2], sc[3]);
+                    } else {
+                        const float4 A0 = S[tid], A1 = S[kK1Threads + tid], A2 = S[2 * kK1Threads + tid];
                         const float s0[4] = {A0.x, A0.y, A0.z, A0.w}, s1[4] = {A1.x, A1.y, A1.z, A1.w};
                         const float s2[4] = {A2.x, A2.y, A2.z, A2.w};
+                        const bool fa = 8 * p.wmeta[warp][0][2] + fi < p.n_mels, fb = 8 * p.wmeta[warp][1][2] + fi < p.n_mels;
+                        const bool ok[4] = {fa && ok0, fa && ok1, fb && ok0, fb && ok1};
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            if (4 * h + i < nvalid) {
+                            if (ok[i]) {
                                 const float m01 = fmaxf(s0[i], s1[i]), m23 = fmaxf(s2[i], sc[i]);
                                 // sigmoid(max_{j != i} S_j - S_i) = 1 / (1 + exp(S_i - max_others))
                                 msum[0] += fast_sigmoid_neg(s0[i] - fmaxf(s1[i], m23));
@@ -590,14 +582,12 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                                 msum[3] += fast_sigmoid_neg(sc[i] - fmaxf(m01, s2[i]));
                             }
                         }
-                    }
-                }
-                if (s == kNumStems - 1) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
-                    if (lane == 0) {
+                        for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
+                        if (lane == 0) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) red[warp * 4 + i] = msum[i];
+                            for (int i = 0; i < 4; ++i) red[warp * 4 + i] = msum[i];
+                        }
                     }
                 }
             }
@@ -611,15 +601,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     const long long step = 16ll * p.F;
                     if (p.logmel) {
                         float* dst = p.logmel + (long long)b * p.lm_stride_b + o;
-                        const int q = tid >> 2;
-                        const float* src = reinterpret_cast<const float*>(ex + kLogOff) + (((q ^ ((q >> 3) & 1)) << 2) | (tid & 3));
+                        const float* src = reinterpret_cast<const float*>(ex + t * kWarpRegion + kLogOff + ch * kLogChStride + t * 8) + m0;
 #pragma unroll 8
-                        for (int m = m0; m < p.n_mels; m += 16, dst += step, src += kWarpRegion / 4) *dst = *src;
-                    }
-                    if (p.melpow) {
-                        float* dst = p.melpow + (long long)b * p.mp_stride_b + o;
-                        const float* src = reinterpret_cast<const float*>(ex + t * kWarpRegion + kMelOff) + ch;
-                        for (int m = m0; m < p.n_mels; m += 16, dst += step) *dst = src[2 * m];
+                        for (int m = m0; m < p.n_mels; m += 16, dst += step, src += 16) *dst = *src;
                     }
                 }
                 if (s == kNumStems - 1 && p.want_stats && tid < 4) {
@@ -656,7 +640,6 @@ __device__ __forceinline__ void put_feature(float* out, int idx, double v) {
 }
 
 constexpr int kK2Threads = 512;
-constexpr int kMaxMels = 128;
 
 __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
     __shared__ double sE[kNumStems][kMaxMels];       // mean dB per mel band

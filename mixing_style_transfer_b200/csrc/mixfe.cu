@@ -54,113 +54,114 @@ std::vector<float> default_filterbank(int sr, int n_fft, int n_mels) {
     return fb;
 }
 
-// Turn the (n_freq, n_mels) matrix into the per-lane tables of K1's warp-local mel projection:
-// lane l of a warp owns filters l, 32+l, ... (one per slot); a slot is walked for as many steps as its
-// longest filter has bins between its first and last non-zero weight.
+// Turn the (n_freq, n_mels) matrix into the tables of K1's tile-level mel projection.  Filters are taken in
+// groups of 8 consecutive ones; a warp owns two groups (a wide one and a narrow one, paired so that the warps'
+// walks have similar lengths) and lane (q, i) walks filter i of each group over frames 2q, 2q+1 of the tile.
+// All lanes of a warp walk a group for n_g steps = its longest support (rounded up to even), starting at
+// start_m <= lo_m; weights outside the support are zero.
 int build_mel_tables(mixfe_plan* pl) {
     const int nf = pl->n_freq, nm = pl->n_mels;
-    const int n_slots = (nm + 31) / 32;
-    if (n_slots > kMaxSlots) return fail(MIXFE_EUNSUPPORTED, "n_mels=%d needs more than %d filters per lane", nm, kMaxSlots);
-    auto w = [&](int k, int m) -> float { return (k < nf && m < nm) ? pl->fb[(size_t)k * nm + m] : 0.0f; };
-    std::vector<int> lo(n_slots * 32, 0), len(n_slots * 32, 0);
+    const int n_groups = (nm + 7) / 8;
+    if (n_groups > 2 * (kK1Threads / 32)) return fail(MIXFE_EUNSUPPORTED, "n_mels=%d > %d", nm, 16 * (kK1Threads / 32));
+    auto w = [&](int k, int m) -> float { return (k >= 0 && k < nf && m < nm) ? pl->fb[(size_t)k * nm + m] : 0.0f; };
+    std::vector<int> lo(n_groups * 8, 0), len(n_groups * 8, 0);
     for (int m = 0; m < nm; ++m) {
         int first = -1, last = -1;
         for (int k = 0; k < nf; ++k)
             if (w(k, m) != 0.0f) { if (first < 0) first = k; last = k; }
         if (first >= 0) { lo[m] = first; len[m] = last - first + 1; }
     }
-    std::vector<int> flo(n_slots * 32);
-    std::vector<float> wsteps;
-    int n_wsteps = 0;
-    for (int j = 0; j < kMaxSlots; ++j) { pl->slot_len[j] = 0; pl->slot_woff[j] = 0; }
-    for (int j = 0; j < n_slots; ++j) {
+    std::vector<int> fstart(kMaxMels, 0), gn(n_groups, 0), gwoff(n_groups, 0);
+    std::vector<float> wt;
+    int n_steps = 0;
+    for (int g = 0; g < n_groups; ++g) {
         int nmin = 0;
-        for (int l = 0; l < 32; ++l) nmin = std::max(nmin, len[32 * j + l]);
-        nmin = std::max(4, (nmin + 3) & ~3);             // K1 walks four steps per iteration
-        // A lane may start its walk before its filter's first bin (zero weights) as long as the walk still
-        // covers the support.  Use that slack, and the freedom of which lane takes which filter, to give
-        // the 16 lanes of each half-warp start bins with distinct residues mod 16: the 64-bit loads of the
-        // power column are then free of bank conflicts.  Bipartite matching filter -> (half-warp, residue).
+        for (int i = 0; i < 8; ++i) nmin = std::max(nmin, len[8 * g + i]);
+        nmin = std::max(2, (nmin + 1) & ~1);              // K1 walks two steps per iteration
+        // The 64-bit loads of one quarter-pair (16 lanes: 8 filters x 2 frame columns that sit 16 banks apart)
+        // are free of bank conflicts when the 8 start bins have distinct residues mod 8 (equal starts broadcast).
+        // Use the slack of the walk (and up to 4 extra steps) to get there: bipartite matching filter -> residue.
         int n = nmin;
-        std::vector<int> pos_of(32, -1), start_of(32, 0);
-        // natural order first: when the slot's filters are narrow and closely spaced the loads already take the
-        // minimum of two wavefronts (equal addresses broadcast)
-        auto wavefronts = [&](int half) {
-            int worst = 0;
-            for (int r = 0; r < 16; ++r) {
-                std::vector<int> seen;
-                for (int l = 16 * half; l < 16 * half + 16; ++l) {
-                    const int st = std::min(lo[32 * j + l], kPvEntries - nmin);
-                    if ((st & 15) == r && std::find(seen.begin(), seen.end(), st) == seen.end()) seen.push_back(st);
-                }
-                worst = std::max(worst, (int)seen.size());
-            }
-            return worst;
-        };
-        const bool natural_ok = wavefronts(0) <= 1 && wavefronts(1) <= 1;
-        for (; !natural_ok && n <= nmin; n += 4) {
-            auto start_for = [&](int f, int r) -> int {      // largest admissible start with start % 16 == r, or -1
-                const int m = 32 * j + f;
-                const int hi = len[m] ? std::min(lo[m], kPvEntries - n) : kPvEntries - n;
-                const int lw = len[m] ? std::max(0, lo[m] + len[m] - n) : 0;
+        std::vector<int> start(8, 0);
+        bool done = false;
+        for (; n <= nmin + 4 && !done; n += 2) {
+            auto range = [&](int i, int& lw, int& hi) {
+                const int m = 8 * g + i;
+                hi = len[m] ? std::min(lo[m], kPvEntries - n) : kPvEntries - n;
+                lw = len[m] ? std::max(0, lo[m] + len[m] - n) : 0;
+            };
+            auto start_for = [&](int i, int r) -> int {
+                int lw, hi;
+                range(i, lw, hi);
                 for (int st = hi; st >= lw; --st)
-                    if ((st & 15) == r) return st;
+                    if ((st & 7) == r) return st;
                 return -1;
             };
-            std::vector<int> owner(32, -1);                    // position (half*16 + residue) -> filter
-            std::function<bool(int, std::vector<char>&)> try_place = [&](int f, std::vector<char>& seen) -> bool {
-                for (int pos = 0; pos < 32; ++pos) {
-                    if (seen[pos] || start_for(f, pos & 15) < 0) continue;
-                    seen[pos] = 1;
-                    if (owner[pos] < 0 || try_place(owner[pos], seen)) { owner[pos] = f; return true; }
+            std::vector<int> owner(8, -1);
+            std::function<bool(int, std::vector<char>&)> place = [&](int i, std::vector<char>& seen) -> bool {
+                for (int r = 0; r < 8; ++r) {
+                    if (seen[r] || start_for(i, r) < 0) continue;
+                    seen[r] = 1;
+                    if (owner[r] < 0 || place(owner[r], seen)) { owner[r] = i; return true; }
                 }
                 return false;
             };
             int placed = 0;
-            for (int f = 0; f < 32; ++f) {
-                std::vector<char> seen(32, 0);
-                if (try_place(f, seen)) ++placed;
+            for (int i = 0; i < 8; ++i) {
+                std::vector<char> seen(8, 0);
+                if (place(i, seen)) ++placed;
             }
-            if (placed == 32) {
-                for (int pos = 0; pos < 32; ++pos) { pos_of[owner[pos]] = pos; start_of[owner[pos]] = start_for(owner[pos], pos & 15); }
+            if (placed == 8) {
+                for (int r = 0; r < 8; ++r) start[owner[r]] = start_for(owner[r], r);
+                done = true;
                 break;
             }
         }
-        if (pos_of[0] < 0) {                               // natural order, exact starts
+        if (!done) {                                       // exact starts; the loads may take extra wavefronts
             n = nmin;
-            for (int f = 0; f < 32; ++f) {
-                const int m = 32 * j + f;
-                pos_of[f] = f;
-                start_of[f] = std::min(lo[m], kPvEntries - n);
-                if (len[m] && lo[m] + len[m] > start_of[f] + n)
+            for (int i = 0; i < 8; ++i) {
+                const int m = 8 * g + i;
+                start[i] = len[m] ? std::min(lo[m], kPvEntries - n) : 0;
+                if (len[m] && lo[m] + len[m] > start[i] + n)
                     return fail(MIXFE_EUNSUPPORTED, "mel filter %d (bins %d..%d) overruns the power column", m, lo[m], lo[m] + len[m] - 1);
             }
         }
-        pl->slot_len[j] = n;
-        pl->slot_woff[j] = n_wsteps;
-        std::vector<int> filt_at(32, 0);
-        for (int f = 0; f < 32; ++f) filt_at[pos_of[f]] = f;
-        for (int lane = 0; lane < 32; ++lane) flo[32 * j + lane] = (8 * start_of[filt_at[lane]]) | (filt_at[lane] << 16);
-        for (int i = 0; i < n; ++i)
-            for (int lane = 0; lane < 32; ++lane) {
-                const int f = filt_at[lane], m = 32 * j + f, k = start_of[f] + i;
-                wsteps.push_back((len[m] && k >= lo[m] && k < lo[m] + len[m]) ? w(k, m) : 0.0f);
+        gn[g] = n;
+        gwoff[g] = (int)wt.size();
+        for (int i = 0; i < 8; ++i) fstart[8 * g + i] = 8 * start[i];
+        for (int st = 0; st < n; ++st)
+            for (int i = 0; i < 8; ++i) {
+                const int m = 8 * g + i, k = start[i] + st;
+                wt.push_back((len[m] && k >= lo[m] && k < lo[m] + len[m]) ? w(k, m) : 0.0f);
             }
-        n_wsteps += n;
+        n_steps += n;
     }
-    pl->n_slots = n_slots;
-    pl->n_wsteps = n_wsteps;
+    // pair the longest walk with the shortest, the second longest with the second shortest, ...
+    std::vector<int> order(n_groups);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return gn[a] > gn[b]; });
+    const int n_warps = kK1Threads / 32;
+    for (int wv = 0; wv < n_warps; ++wv)
+        for (int ab = 0; ab < 2; ++ab) {
+            const int pos = ab == 0 ? wv : 2 * n_warps - 1 - wv;
+            int* me = pl->wmeta[wv][ab];
+            if (pos < n_groups) { me[0] = gn[order[pos]]; me[1] = gwoff[order[pos]]; me[2] = order[pos]; }
+            else { me[0] = 0; me[1] = 0; me[2] = 2 * n_warps; }          // no group: filters >= n_mels_pad
+            me[3] = 0;
+        }
+    pl->n_wsteps = n_steps;
+    const int n_wt = (int)wt.size();
     int rc;
-    if ((rc = upload(&pl->d_flo, flo))) return rc;
-    if ((rc = upload(&pl->d_wsteps, wsteps))) return rc;
+    if ((rc = upload(&pl->d_flo, fstart))) return rc;
+    if ((rc = upload(&pl->d_wsteps, wt))) return rc;
     // shared-memory map of K1
     pl->nxs = (kTF - 1) * pl->hop + kNfft;
     pl->off_ex = align16(pl->nxs * 8);
     pl->off_tw = pl->off_ex + 8 * kWarpRegion;
     pl->off_s = pl->off_tw + 31 * 32 * 8;            // rows k1 = 1..31 of the twiddle table (row 0 is all ones)
-    pl->off_wsteps = pl->off_s + 3 * pl->n_mels_pad * 8 * 4;
-    pl->off_flo = align16(pl->off_wsteps + n_wsteps * 32 * 4);
-    pl->off_red = align16(pl->off_flo + n_slots * 32 * 4);
+    pl->off_wsteps = pl->off_s + 3 * kK1Threads * 16;   // S: one float4 per thread and stem 0..2
+    pl->off_flo = align16(pl->off_wsteps + n_wt * 4);
+    pl->off_red = align16(pl->off_flo + kMaxMels * 4);
     pl->smem_k1 = pl->off_red + 8 * 4 * 4 + 32;          // masking scratch, mbarrier, arrival counter
     if (pl->smem_k1 > 227 * 1024)
         return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
@@ -260,8 +261,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     p.logmel = logmel; p.lm_stride_b = lm_stride_b; p.melpow = melpow; p.mp_stride_b = mp_stride_b;
     p.part_spec = reinterpret_cast<float2*>(pl->ws);
     p.part_td = reinterpret_cast<float*>(reinterpret_cast<char*>(pl->ws) + spec_bytes);
-    p.tw = pl->d_tw; p.wsteps = pl->d_wsteps; p.flo = pl->d_flo; p.n_slots = pl->n_slots; p.n_wsteps = pl->n_wsteps;
-    for (int j = 0; j < kMaxSlots; ++j) { p.slot_len[j] = pl->slot_len[j]; p.slot_woff[j] = pl->slot_woff[j]; }
+    p.tw = pl->d_tw; p.wsteps = pl->d_wsteps; p.flo = pl->d_flo; p.n_wt = (pl->off_flo - pl->off_wsteps) / 4;
+    memcpy(p.wmeta, pl->wmeta, sizeof(p.wmeta));
     p.want_stats = features ? 1 : 0;
     p.sm_ticket = pl->d_sm_ticket;
     {
