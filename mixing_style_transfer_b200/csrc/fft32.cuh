@@ -97,6 +97,12 @@ __device__ __forceinline__ cplx64 csub(cplx64 a, cplx64 b) {
     return d;
 }
 
+__device__ __forceinline__ cplx64 cfma(cplx64 a, cplx64 b, cplx64 c) {      // lane-wise a * b + c
+    cplx64 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 // In-place forward DFT of 32 packed complex values; X[k] is found at index brev5(k) (as dft32_dif).
 __device__ __forceinline__ void dft32_dif_packed(cplx64 (&z)[32]) {
 #pragma unroll

@@ -43,7 +43,7 @@ constexpr int kTF = 8;             // frames per CTA tile
 constexpr int kK1Threads = 256;    // 8 warps, one frame each
 constexpr int kNfft = 1024;
 constexpr int kNfreq = 513;
-constexpr int kTdN = 40;           // floats per tile of time-domain partials
+constexpr int kTdN = 40;           // floats per record of time-domain partials (two records per tile)
 constexpr int kMaxMels = 128;
 // warp-private shared region (8 KB): [0, 8192) exchange during the FFT; afterwards
 //   [skew, skew + 8 * 544)        (L, R) power column of the warp's frame, bins 0..512 + zero-weight overshoot;
@@ -68,7 +68,7 @@ struct K1Params {
     float* melpow;                   // debug output (mel power before the log) or nullptr
     long long mp_stride_b;
     float2* part_spec;               // [B][n_tiles][4][n_mels_pad] (sum log, sum mel)
-    float* part_td;                  // [B][n_tiles][kTdN]
+    float* part_td;                  // [B][n_tiles][2][kTdN]
     const float2* tw;                // [1024] tw[k1*32+n2] = exp(-2 pi i n2 k1 / 1024)
     const float* wsteps;             // per group of 8 filters: [steps][8] weights
     const int* flo;                  // [kMaxMels] byte offset (8 * first walked bin) of each filter in the power column
@@ -76,6 +76,7 @@ struct K1Params {
     int wmeta[8][2][4];              // per warp, per group slot: steps (even), weight offset, group index, 0
     int want_stats;
     unsigned* sm_ticket;             // [n_sms] ever-increasing arrival counters, one per SM
+    int dbg_skip;                    // timing experiments only (MIXFE_K1_DBG_SKIP): 1 = no time statistics, 2 = no masking
     int skew_ns;                     // start delay of every second CTA that lands on an SM (0 = none)
     int off_ex, off_tw, off_s, off_wsteps, off_flo, off_red;
 };
@@ -187,95 +188,192 @@ __device__ __forceinline__ void k1_stage_coop(const K1Params& p, const K1Stage& 
     }
 }
 
-// Time-domain partials of the hop region a tile owns: per stem sum L, sum R, sum L^2, sum R^2,
-// sum (L-R)^2, sum (L+R)^2, max|L|, max|R| (slots 8s..8s+7) and the mixture energy (slot 32).
-__device__ __forceinline__ void k1_accumulate(float (&acc)[33], const float (&L)[kNumStems], const float (&R)[kNumStems]) {
-    float mL = 0.0f, mR = 0.0f;
-#pragma unroll
-    for (int s = 0; s < kNumStems; ++s) {
-        acc[s * 8 + 0] += L[s];
-        acc[s * 8 + 1] += R[s];
-        acc[s * 8 + 2] = fmaf(L[s], L[s], acc[s * 8 + 2]);
-        acc[s * 8 + 3] = fmaf(R[s], R[s], acc[s * 8 + 3]);
-        const float d = L[s] - R[s], m = L[s] + R[s];
-        acc[s * 8 + 4] = fmaf(d, d, acc[s * 8 + 4]);
-        acc[s * 8 + 5] = fmaf(m, m, acc[s * 8 + 5]);
-        acc[s * 8 + 6] = fmaxf(acc[s * 8 + 6], fabsf(L[s]));
-        acc[s * 8 + 7] = fmaxf(acc[s * 8 + 7], fabsf(R[s]));
-        mL += L[s];                                  // ((0 + v) + b) + d) + o, as sum(stems.values())
-        mR += R[s];
-    }
-    acc[32] = fmaf(mL, mL, fmaf(mR, mR, acc[32]));
+// Time-domain partials of the hop region a tile owns.  A tile writes TWO records of kTdN floats, one per half
+// of its region: per stem (slots 8s..8s+7) sum L, sum R, sum L^2, sum R^2, sum (L-R)^2, sum (L+R)^2, max|L|,
+// max|R|; the mixture energy of the half in four pieces (slots 32, 37, 38, 39); the masking sums of the whole
+// tile in slots 33..36 of record 0.
+//
+// Roles instead of a CTA-wide reduction: warp w sums stem (w & 3) over half (w >> 2) of the region -- two rows,
+// 14 running values, one warp-shuffle reduction, no shared memory and no barrier -- and then the mixture energy
+// of eighth w (all 8 rows).  Sums run on pairs of consecutive samples (packed f32x2 adds / FMAs).
+struct K1StemAcc {
+    cplx64 sL, sR, sLL, sRR, sDD, sSS;
+    float mxL, mxR;
+};
+
+__device__ __forceinline__ void k1_stem_acc(K1StemAcc& a, float l0, float l1, float r0, float r1) {
+    const cplx64 L = cpack(l0, l1), R = cpack(r0, r1);
+    a.sL = cadd(a.sL, L);
+    a.sR = cadd(a.sR, R);
+    a.sLL = cfma(L, L, a.sLL);
+    a.sRR = cfma(R, R, a.sRR);
+    const cplx64 d = csub(L, R), m = cadd(L, R);
+    a.sDD = cfma(d, d, a.sDD);
+    a.sSS = cfma(m, m, a.sSS);
+    a.mxL = fmaxf(fmaxf(a.mxL, fabsf(l0)), fabsf(l1));
+    a.mxR = fmaxf(fmaxf(a.mxR, fabsf(r0)), fabsf(r1));
 }
 
-// `scratch` is the (idle) 64 KB exchange region.  Contains one __syncthreads; the caller provides
-// the barrier that separates the reduce from the next writer of `scratch`.
-__device__ __forceinline__ void k1_time_stats(const K1Params& p, float* scratch, int b, int tile, int tid) {
+__device__ __forceinline__ float cfold(cplx64 v) {
+    float x, y;
+    cunpack(v, x, y);
+    return x + y;
+}
+
+__device__ __forceinline__ void k1_time_stats(const K1Params& p, int b, int tile, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
-    float acc[33];
-#pragma unroll
-    for (int i = 0; i < 33; ++i) acc[i] = 0.0f;
     const long long own0 = (long long)tile * kTF * p.hop;
     const long long rem = (long long)p.T - own0;
     const int own_n = rem < 0 ? 0 : (rem > (long long)kTF * p.hop ? kTF * p.hop : (int)rem);
     const long long cb = (long long)b * p.stride_b + own0;
-    unsigned long long amask = (unsigned long long)own_n;
+    unsigned long long amask = (unsigned long long)(p.hop & 3);
 #pragma unroll
     for (int s = 0; s < kNumStems; ++s)
         amask |= reinterpret_cast<unsigned long long>(p.stem[s] + cb) |
                  reinterpret_cast<unsigned long long>(p.stem[s] + cb + p.stride_c);
-    if ((amask & 15ull) == 0) {
-        // 128-bit path: every row start is 16-byte aligned and the region is a whole number of float4
-        // (own_n is part of the mask: a multiple of 16 samples)
-        for (int i = tid; i < (own_n >> 2); i += kK1Threads) {
+    const bool vec = (amask & 15ull) == 0;       // every row start 16-byte aligned, role ranges start on float4 boundaries
+    float* rec = p.part_td + ((long long)b * p.n_tiles + tile) * (2 * kTdN) + (warp >> 2) * kTdN;
+
+    // ---- role A: stem (warp & 3), half (warp >> 2) -------------------------------------------------
+    {
+        const int s = warp & 3;
+        const int r0 = (warp >> 2) * (kTF / 2) * p.hop;
+        const int r1 = min(own_n, r0 + (kTF / 2) * p.hop);
+        const float* gL = p.stem[s] + cb;
+        const float* gR = gL + p.stride_c;
+        K1StemAcc a;
+        a.sL = a.sR = a.sLL = a.sRR = a.sDD = a.sSS = 0ull;
+        a.mxL = a.mxR = 0.0f;
+        int i = r0;
+        if (vec) {
+            const int r1v = r0 + ((r1 - r0) > 0 ? ((r1 - r0) & ~3) : 0);
+#pragma unroll 1
+            for (int i4 = r0 + 4 * lane; i4 < r1v; i4 += 8 * 128) {
+                float4 vL[8], vR[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {                // up to 16 x 128-bit loads in flight per lane
+                    const bool in = i4 + 128 * u < r1v;
+                    vL[u] = in ? __ldg(reinterpret_cast<const float4*>(gL + i4 + 128 * u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    vR[u] = in ? __ldg(reinterpret_cast<const float4*>(gR + i4 + 128 * u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    k1_stem_acc(a, vL[u].x, vL[u].y, vR[u].x, vR[u].y);
+                    k1_stem_acc(a, vL[u].z, vL[u].w, vR[u].z, vR[u].w);
+                }
+            }
+            i = r1v;
+        }
+        for (int j = i + lane; j < r1; j += 32) k1_stem_acc(a, __ldg(gL + j), 0.0f, __ldg(gR + j), 0.0f);
+        float v[6] = {cfold(a.sL), cfold(a.sR), cfold(a.sLL), cfold(a.sRR), cfold(a.sDD), cfold(a.sSS)};
+#pragma unroll
+        for (int q = 0; q < 6; ++q) v[q] = warp_sum(v[q]);
+        const float mL = warp_max(a.mxL), mR = warp_max(a.mxR);
+        if (lane == 0) {
+            float4* dst = reinterpret_cast<float4*>(rec + s * 8);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], mL, mR);
+        }
+    }
+    // ---- role M: mixture energy of eighth `warp` ----------------------------------------------------
+    {
+        const int r0 = warp * p.hop;
+        const int r1 = min(own_n, r0 + p.hop);
+        cplx64 e = 0ull;
+        int i = r0;
+        if (vec) {
+            const int r1v = r0 + ((r1 - r0) > 0 ? ((r1 - r0) & ~3) : 0);
+#pragma unroll 1
+            for (int i4 = r0 + 4 * lane; i4 < r1v; i4 += 2 * 128) {
+                float4 vL[2][kNumStems], vR[2][kNumStems];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const bool in = i4 + 128 * u < r1v;
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {
+                        vL[u][s] = in ? __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb + i4 + 128 * u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        vR[u][s] = in ? __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb + p.stride_c + i4 + 128 * u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    // ((0 + v) + b) + d) + o, as sum(stems.values())
+                    const cplx64 l01 = cadd(cadd(cadd(cpack(vL[u][0].x, vL[u][0].y), cpack(vL[u][1].x, vL[u][1].y)), cpack(vL[u][2].x, vL[u][2].y)), cpack(vL[u][3].x, vL[u][3].y));
+                    const cplx64 l23 = cadd(cadd(cadd(cpack(vL[u][0].z, vL[u][0].w), cpack(vL[u][1].z, vL[u][1].w)), cpack(vL[u][2].z, vL[u][2].w)), cpack(vL[u][3].z, vL[u][3].w));
+                    const cplx64 q01 = cadd(cadd(cadd(cpack(vR[u][0].x, vR[u][0].y), cpack(vR[u][1].x, vR[u][1].y)), cpack(vR[u][2].x, vR[u][2].y)), cpack(vR[u][3].x, vR[u][3].y));
+                    const cplx64 q23 = cadd(cadd(cadd(cpack(vR[u][0].z, vR[u][0].w), cpack(vR[u][1].z, vR[u][1].w)), cpack(vR[u][2].z, vR[u][2].w)), cpack(vR[u][3].z, vR[u][3].w));
+                    e = cfma(l01, l01, cfma(q01, q01, e));
+                    e = cfma(l23, l23, cfma(q23, q23, e));
+                }
+            }
+            i = r1v;
+        }
+        float es = cfold(e);
+        for (int j = i + lane; j < r1; j += 32) {
+            float mL = 0.0f, mR = 0.0f;
+#pragma unroll
+            for (int s = 0; s < kNumStems; ++s) {
+                mL += __ldg(p.stem[s] + cb + j);
+                mR += __ldg(p.stem[s] + cb + p.stride_c + j);
+            }
+            es = fmaf(mL, mL, fmaf(mR, mR, es));
+        }
+        es = warp_sum(es);
+        if (lane == 0) rec[(warp & 3) == 0 ? 32 : 36 + (warp & 3)] = es;
+    }
+}
+
+// The same roles on rows the TMA engine has put into shared memory: row (2 stem + channel) holds the tile's own
+// region (kTF * hop <= 2048 samples, all of them inside the clip) at rows + 8 KB * row.
+__device__ __forceinline__ void k1_time_stats_smem(const K1Params& p, const unsigned char* rows, int b, int tile, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    float* rec = p.part_td + ((long long)b * p.n_tiles + tile) * (2 * kTdN) + (warp >> 2) * kTdN;
+    {
+        const int s = warp & 3;
+        const int n4 = (kTF / 2) * p.hop / 4;                    // float4 per row of this half
+        const float4* rL = reinterpret_cast<const float4*>(rows + (2 * s) * kWarpRegion) + (warp >> 2) * n4;
+        const float4* rR = rL + kWarpRegion / 16;
+        K1StemAcc a;
+        a.sL = a.sR = a.sLL = a.sRR = a.sDD = a.sSS = 0ull;
+        a.mxL = a.mxR = 0.0f;
+#pragma unroll 4
+        for (int i = lane; i < n4; i += 32) {
+            const float4 vL = rL[i], vR = rR[i];
+            k1_stem_acc(a, vL.x, vL.y, vR.x, vR.y);
+            k1_stem_acc(a, vL.z, vL.w, vR.z, vR.w);
+        }
+        float v[6] = {cfold(a.sL), cfold(a.sR), cfold(a.sLL), cfold(a.sRR), cfold(a.sDD), cfold(a.sSS)};
+#pragma unroll
+        for (int q = 0; q < 6; ++q) v[q] = warp_sum(v[q]);
+        const float mL = warp_max(a.mxL), mR = warp_max(a.mxR);
+        if (lane == 0) {
+            float4* dst = reinterpret_cast<float4*>(rec + s * 8);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], mL, mR);
+        }
+    }
+    {
+        const int n4 = p.hop / 4;                                // float4 per row of this eighth
+        const float4* r0 = reinterpret_cast<const float4*>(rows) + warp * n4;
+        cplx64 e = 0ull;
+#pragma unroll 2
+        for (int i = lane; i < n4; i += 32) {
             float4 vL[kNumStems], vR[kNumStems];
 #pragma unroll
             for (int s = 0; s < kNumStems; ++s) {
-                vL[s] = __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb) + i);
-                vR[s] = __ldg(reinterpret_cast<const float4*>(p.stem[s] + cb + p.stride_c) + i);
+                vL[s] = r0[(2 * s) * (kWarpRegion / 16) + i];
+                vR[s] = r0[(2 * s + 1) * (kWarpRegion / 16) + i];
             }
-            {
-                const float L[4] = {vL[0].x, vL[1].x, vL[2].x, vL[3].x}, R[4] = {vR[0].x, vR[1].x, vR[2].x, vR[3].x};
-                k1_accumulate(acc, L, R);
-            }
-            {
-                const float L[4] = {vL[0].y, vL[1].y, vL[2].y, vL[3].y}, R[4] = {vR[0].y, vR[1].y, vR[2].y, vR[3].y};
-                k1_accumulate(acc, L, R);
-            }
-            {
-                const float L[4] = {vL[0].z, vL[1].z, vL[2].z, vL[3].z}, R[4] = {vR[0].z, vR[1].z, vR[2].z, vR[3].z};
-                k1_accumulate(acc, L, R);
-            }
-            {
-                const float L[4] = {vL[0].w, vL[1].w, vL[2].w, vL[3].w}, R[4] = {vR[0].w, vR[1].w, vR[2].w, vR[3].w};
-                k1_accumulate(acc, L, R);
-            }
+            // ((0 + v) + b) + d) + o, as sum(stems.values())
+            const cplx64 l01 = cadd(cadd(cadd(cpack(vL[0].x, vL[0].y), cpack(vL[1].x, vL[1].y)), cpack(vL[2].x, vL[2].y)), cpack(vL[3].x, vL[3].y));
+            const cplx64 l23 = cadd(cadd(cadd(cpack(vL[0].z, vL[0].w), cpack(vL[1].z, vL[1].w)), cpack(vL[2].z, vL[2].w)), cpack(vL[3].z, vL[3].w));
+            const cplx64 q01 = cadd(cadd(cadd(cpack(vR[0].x, vR[0].y), cpack(vR[1].x, vR[1].y)), cpack(vR[2].x, vR[2].y)), cpack(vR[3].x, vR[3].y));
+            const cplx64 q23 = cadd(cadd(cadd(cpack(vR[0].z, vR[0].w), cpack(vR[1].z, vR[1].w)), cpack(vR[2].z, vR[2].w)), cpack(vR[3].z, vR[3].w));
+            e = cfma(l01, l01, cfma(q01, q01, e));
+            e = cfma(l23, l23, cfma(q23, q23, e));
         }
-    } else {
-        for (int i = tid; i < own_n; i += kK1Threads) {
-            float L[kNumStems], R[kNumStems];
-#pragma unroll
-            for (int s = 0; s < kNumStems; ++s) {
-                const float* g = p.stem[s] + cb + i;
-                L[s] = __ldg(g);
-                R[s] = __ldg(g + p.stride_c);
-            }
-            k1_accumulate(acc, L, R);
-        }
-    }
-#pragma unroll
-    for (int q = 0; q < 33; ++q) scratch[q * kK1Threads + tid] = acc[q];
-    __syncthreads();
-    for (int q = warp; q < 33; q += 8) {
-        const bool is_max = q < 32 && (q & 7) >= 6;
-        float v = 0.0f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float u = scratch[q * kK1Threads + lane + 32 * j];
-            v = is_max ? fmaxf(v, u) : v + u;
-        }
-        v = is_max ? warp_max(v) : warp_sum(v);
-        if (lane == 0) p.part_td[((long long)b * p.n_tiles + tile) * kTdN + q] = v;
+        const float es = warp_sum(cfold(e));
+        if (lane == 0) rec[(warp & 3) == 0 ? 32 : 36 + (warp & 3)] = es;
     }
 }
 
@@ -290,6 +388,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
     const unsigned bar = smem_u32(smem + p.off_red + 128);                    // mbarrier of the TMA staging
     int* const arrivals = reinterpret_cast<int*>(smem + p.off_red + 136);     // warps done reading xs
+    const unsigned bar2 = smem_u32(smem + p.off_red + 144);                   // mbarrier of the statistics rows
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long item = blockIdx.x;
@@ -307,11 +406,12 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
     if (tid == 0) {
         mbar_init(bar, 1);
+        mbar_init(bar2, 1);
         *arrivals = 0;
     }
     __syncthreads();
     bool cur_tma;                    // how the stage about to be consumed was filled (uniform over the CTA)
-    unsigned tma_parity = 0;
+    unsigned tma_parity = 0, stats_parity = 0;
     {
         const K1Stage st = k1_stage_of(p, b, tile, 0);
         cur_tma = st.tma;
@@ -354,9 +454,34 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 tma_parity ^= 1u;
             }
             __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
-            if (s == 0 && p.want_stats) {
-                k1_time_stats(p, reinterpret_cast<float*>(ex), b, tile, tid);
-                __syncthreads();             // the scratch (= exchange regions) is dead
+            if (s == 0 && p.want_stats && !(p.dbg_skip & 1)) {
+                // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
+                // the clip and every row is 16-byte aligned; else role loads straight from global memory.
+                const long long own0 = (long long)tile * kTF * p.hop;
+                const long long cb = (long long)b * p.stride_b + own0;
+                unsigned long long amask = (unsigned long long)(p.hop & 127);
+#pragma unroll
+                for (int q = 0; q < kNumStems; ++q)
+                    amask |= reinterpret_cast<unsigned long long>(p.stem[q] + cb) |
+                             reinterpret_cast<unsigned long long>(p.stem[q] + cb + p.stride_c);
+                if ((amask & 15ull) == 0 && kTF * p.hop * 4 <= kWarpRegion && own0 + kTF * p.hop <= (long long)p.T) {
+                    if (tid == 0) {
+                        const unsigned bytes = (unsigned)(kTF * p.hop) * 4u;
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_expect_tx(bar2, 8u * bytes);
+#pragma unroll
+                        for (int q = 0; q < kNumStems; ++q) {
+                            tma_bulk_g2s(smem_u32(ex + (2 * q) * kWarpRegion), p.stem[q] + cb, bytes, bar2);
+                            tma_bulk_g2s(smem_u32(ex + (2 * q + 1) * kWarpRegion), p.stem[q] + cb + p.stride_c, bytes, bar2);
+                        }
+                    }
+                    mbar_wait(bar2, stats_parity);
+                    stats_parity ^= 1u;
+                    k1_time_stats_smem(p, ex, b, tile, tid);
+                    __syncthreads();         // the rows are dead: the exchange regions go back to their warps
+                } else {
+                    k1_time_stats(p, b, tile, tid);
+                }
             }
 
             // ---- frame t0 + warp -> registers, Hann window on the fly ------------------------
@@ -563,7 +688,8 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     sc[2 * ab + 1] = 0.5f * (v[2] + v[3]);
                 }
                 if (p.want_stats) {
-                    if (s < 3) {
+                    if (p.dbg_skip & 2) {
+                    } else if (s < 3) {
                         S[s * kK1Threads + tid] = make_float4(sc[0], sc[1], sc[2], sc[3]);
                     } else {
                         const float4 A0 = S[tid], A1 = S[kK1Threads + tid], A2 = S[2 * kK1Threads + tid];
@@ -609,7 +735,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 if (s == kNumStems - 1 && p.want_stats && tid < 4) {
                     float v = 0.0f;
                     for (int w = 0; w < 8; ++w) v += red[w * 4 + tid];
-                    p.part_td[((long long)b * p.n_tiles + tile) * kTdN + 33 + tid] = v;
+                    p.part_td[((long long)b * p.n_tiles + tile) * (2 * kTdN) + 33 + tid] = v;
                 }
             }
         }
@@ -674,14 +800,20 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
             sMelTot[s][warp & 3] = c;
         }
     }
-    // 2. time-domain partials: 8 threads per quantity
+    // 2. time-domain partials: 8 threads per quantity, two records per tile
     if (tid < kTdN * 8) {
         const int q = tid >> 3, sub = tid & 7;
         const bool is_max = q < 32 && (q & 7) >= 6;
         double v = 0.0;
-        for (int t = sub; t < p.n_tiles; t += 8) {
-            const double u = (double)__ldg(p.part_td + ((long long)b * p.n_tiles + t) * kTdN + q);
-            v = is_max ? fmax(v, u) : v + u;
+        if (q < 37) {
+            const float* src = p.part_td + (long long)b * p.n_tiles * (2 * kTdN);
+            const int n_rec = 2 * p.n_tiles, step = (q >= 33) ? 2 : 1;          // masking sums live in record 0 only
+            for (int t = sub * step; t < n_rec; t += 8 * step) {
+                const float* r = src + (long long)t * kTdN;
+                double u = (double)__ldg(r + q);
+                if (q == 32) u += (double)__ldg(r + 37) + (double)__ldg(r + 38) + (double)__ldg(r + 39);
+                v = is_max ? fmax(v, u) : v + u;
+            }
         }
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) {

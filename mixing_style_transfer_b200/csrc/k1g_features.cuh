@@ -72,7 +72,7 @@ __device__ __forceinline__ void k1g_pass2_last(float2* z, int n, int frames, int
 }
 
 __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant__ K1GParams g) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(1024) unsigned char smem[];
     const K1Params& p = g.base;
     float2* const z = reinterpret_cast<float2*>(smem);                         // [nf][n_fft]
     float2* const pw = reinterpret_cast<float2*>(smem + g.off_pw);             // [nf][pw_stride]
@@ -87,8 +87,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
 
     if (p.want_stats) {
-        k1_time_stats(p, reinterpret_cast<float*>(smem), b, tile, tid);
-        __syncthreads();
+        k1_time_stats(p, b, tile, tid);
     }
 
     for (int s = 0; s < kNumStems; ++s) {
@@ -198,7 +197,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
         if (tid < 4) {
             float v = 0.0f;
             for (int w = 0; w < kGThreads / 32; ++w) v += red[w * 4 + tid];
-            p.part_td[((long long)b * p.n_tiles + tile) * kTdN + 33 + tid] = v;
+            p.part_td[((long long)b * p.n_tiles + tile) * (2 * kTdN) + 33 + tid] = v;
         }
     }
 }

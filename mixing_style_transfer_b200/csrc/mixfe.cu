@@ -209,7 +209,7 @@ int build_generic_tables(mixfe_plan* pl) {
     while (nfr > 1 && nfr * per_frame > 160 * 1024) nfr >>= 1;
     pl->g_nf = nfr;
     pl->g_off_pw = nfr * n * 8;
-    const int stage = std::max(pl->g_off_pw + nfr * pl->g_pw_stride * 8, 33 * kK1Threads * 4);   // also the statistics scratch
+    const int stage = pl->g_off_pw + nfr * pl->g_pw_stride * 8;
     pl->g_off_mel = align16(stage);
     pl->g_off_S = pl->g_off_mel + kTF * pl->n_mels_pad * 8;
     pl->g_off_red = pl->g_off_S + kNumStems * kTF * pl->n_mels_pad * 4;
@@ -248,7 +248,7 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     const int F = 1 + T / pl->hop;
     const int n_tiles = (F + kTF - 1) / kTF;
     const size_t spec_bytes = (size_t)B * n_tiles * kNumStems * pl->n_mels_pad * sizeof(float2);
-    const size_t td_bytes = (size_t)B * n_tiles * kTdN * sizeof(float);
+    const size_t td_bytes = (size_t)B * n_tiles * 2 * kTdN * sizeof(float);
     if (features) {
         int rc = ensure_workspace(pl, spec_bytes + td_bytes, stream);
         if (rc) return rc;
@@ -268,6 +268,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     {
         const char* e = getenv("MIXFE_K1_SKEW_NS");
         p.skew_ns = e ? atoi(e) : pl->k1_skew_ns;
+        const char* d = getenv("MIXFE_K1_DBG_SKIP");
+        p.dbg_skip = d ? atoi(d) : 0;
     }
     p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_wsteps = pl->off_wsteps;
     p.off_flo = pl->off_flo; p.off_red = pl->off_red;
