@@ -454,6 +454,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 tma_parity ^= 1u;
             }
             __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
+            bool stats_rows = false;
             if (s == 0 && p.want_stats && !(p.dbg_skip & 1)) {
                 // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
                 // the clip and every row is 16-byte aligned; else role loads straight from global memory.
@@ -475,10 +476,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                             tma_bulk_g2s(smem_u32(ex + (2 * q + 1) * kWarpRegion), p.stem[q] + cb + p.stride_c, bytes, bar2);
                         }
                     }
-                    mbar_wait(bar2, stats_parity);
-                    stats_parity ^= 1u;
-                    k1_time_stats_smem(p, ex, b, tile, tid);
-                    __syncthreads();         // the rows are dead: the exchange regions go back to their warps
+                    stats_rows = true;       // consumed below, after this warp's frame is in registers
                 } else {
                     k1_time_stats(p, b, tile, tid);
                 }
@@ -554,6 +552,13 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                         }
                     }
                 }
+            }
+
+            if (stats_rows) {                // the copy had the frame load to land
+                mbar_wait(bar2, stats_parity);
+                stats_parity ^= 1u;
+                k1_time_stats_smem(p, ex, b, tile, tid);
+                __syncthreads();             // the rows are dead: the exchange regions go back to their warps
             }
 
             if (active) {
