@@ -86,6 +86,18 @@ int mixfe_augment(mixfe_plan* plan, const float* const in[MIXFE_NUM_STEMS],
                   int B, int T, const mixfe_aug_params* params, const float* impulse, int L,
                   void* cuda_stream);
 
+/* Replaces autograd through MelSpectrogramPreprocessor.forward (src/model.py:41-67), the path the style-transfer
+ * loop differentiates (src/train_style_transfer.py:206-215): given d loss / d logmel, ADDS d loss / d stems into
+ * grad_stems (which the caller zero-initialises).  stems: the forward inputs, addressed as in
+ * mixfe_features_logmel; grad_logmel: device, same addressing as `logmel` there; grad_stems[s]: device, element
+ * (b, c, t) at grad_stems[s][b*grad_stride_b + c*grad_stride_c + t].  The spectrum is recomputed; nothing is
+ * saved by the forward.  Returns MIXFE_ESHORT when T <= n_fft/2. */
+int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
+                          long long stride_b, long long stride_c, int B, int T,
+                          const float* grad_logmel, long long grad_logmel_stride_b,
+                          float* const grad_stems[MIXFE_NUM_STEMS], long long grad_stride_b,
+                          long long grad_stride_c, void* cuda_stream);
+
 /* Test hook: mel POWER (before the log) for every channel, same addressing as logmel. */
 int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                           long long stride_b, long long stride_c, int B, int T,
@@ -105,7 +117,8 @@ long long mixfe_launch_count(void);
 #define MIXFE_KERNEL_FINALIZE 1   /* K2: per-clip feature finalize */
 #define MIXFE_KERNEL_AUGMENT 2    /* K3: gain/biquad/compressor scan */
 #define MIXFE_KERNEL_REVERB 3     /* K4/K5: FFT-domain reverb + redistribution (all its launches) */
-#define MIXFE_NUM_KERNELS 4
+#define MIXFE_KERNEL_LOGMEL_BWD 4 /* K6: backward of the log-mel */
+#define MIXFE_NUM_KERNELS 5
 int mixfe_plan_enable_timing(mixfe_plan* plan, int enable);
 int mixfe_plan_kernel_time(mixfe_plan* plan, int which, double* total_ms, long long* launches);
 

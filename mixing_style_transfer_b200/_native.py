@@ -9,7 +9,7 @@ import ctypes
 import os
 import subprocess
 import threading
-from typing import Optional, Sequence
+from typing import List, Optional, Sequence
 
 import torch
 
@@ -71,7 +71,7 @@ _lock = threading.Lock()
 # every symbol include/mixfe.h declares (tests check the library exports all of them)
 EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_plan_destroy",
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
-           "mixfe_features_logmel", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
+           "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config")
 
 
@@ -100,6 +100,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_workspace_bytes.restype = ctypes.c_size_t
         L.mixfe_features_logmel.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp, ll, vp]
         L.mixfe_debug_mel_power.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, vp]
+        L.mixfe_logmel_backward.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, ctypes.POINTER(vp), ll, ll, vp]
         L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
                                     ctypes.POINTER(AugParams), vp, ci, vp]
         L.mixfe_launch_count.restype = ll
@@ -213,6 +214,27 @@ class Plan:
                                                0 if lm is None else lm.stride(0), _stream(self.device)))
         return feats, lm
 
+    def logmel_backward(self, stems: Sequence[torch.Tensor], grad_logmel: torch.Tensor) -> List[torch.Tensor]:
+        """d loss / d stems (4 new (B,2,T) tensors) from d loss / d logmel (B,8,n_mels,F); the adjoint of the
+        log-mel half of features_logmel (kernel K6)."""
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        F = self.num_frames(T)
+        g = grad_logmel
+        if g.dtype != torch.float32 or g.device != self.device:
+            g = g.to(device=self.device, dtype=torch.float32)
+        if tuple(g.shape) != (B, 8, self.n_mels, F):
+            raise ValueError(f"grad_logmel shape {tuple(g.shape)}, expected {(B, 8, self.n_mels, F)}")
+        if g.stride(3) != 1 or g.stride(2) != F or g.stride(1) != self.n_mels * F:
+            g = g.contiguous()
+        outs = [torch.zeros((B, 2, T), dtype=torch.float32, device=self.device) for _ in range(4)]
+        ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        optrs = (ctypes.c_void_p * 4)(*[o.data_ptr() for o in outs])
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_logmel_backward(self._h, ptrs, sb, sc, B, T, _ptr(g), g.stride(0), optrs,
+                                               outs[0].stride(0), outs[0].stride(1), _stream(self.device)))
+        return outs
+
     def debug_mel_power(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
         st, sb, sc = unify_stems(stems)
         B, _, T = st[0].shape
@@ -249,7 +271,7 @@ class Plan:
                                        _stream(self.device)))
         return outs
 
-    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3}
+    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4}
 
     def enable_timing(self, on: bool = True) -> None:
         _check(lib().mixfe_plan_enable_timing(self._h, 1 if on else 0))

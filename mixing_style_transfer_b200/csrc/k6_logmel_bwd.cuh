@@ -1,0 +1,188 @@
+// K6: backward of the log-mel front end, d loss / d audio from d loss / d logmel.
+//
+// Reference behaviour: autograd through MelSpectrogramPreprocessor.forward (src/model.py:41-67), which the
+// style-transfer loop relies on -- the TCN output flows through the frozen encoder's log-mel
+// (src/train_style_transfer.py:206-215, inference/test_tcn_style_transfer.py:44-57): log -> mel matmul ->
+// |X|^2 -> rfft -> Hann window -> framing with hop -> 'reflect' padding.
+//
+//   logmel = log(mel + 1e-10)                     dmel  = g / (mel + 1e-10)
+//   mel[m] = sum_k fb[k][m] P[k]                  dP[k] = sum_m fb[k][m] dmel[m]
+//   P[k]   = |X[k]|^2, k = 0..n/2                 G[k]  = 2 X[k] dP[k]
+//   X      = rfft(w * frame)                      dframe[i] = w[i] * Re sum_k G[k] exp(+2 pi i k i / n)
+//   frame  = xpad[t hop + i]                      overlap-add, then the adjoint of the reflect padding
+//
+// One CTA per (tile of 8 frames, clip, stem).  The forward spectrum is recomputed (no activations are saved: the
+// forward writes only the log-mel), with K1G's shared-memory radix-4 FFT.  L and R share both transforms: forward as
+// one complex FFT of L + iR; backward as one complex FFT of conj(Y), Y = Hermitian extension of G_L plus i times that
+// of G_R, whose inverse transform is dframe_L + i dframe_R.  Frames are overlap-added in shared memory; the tile's
+// span goes to global memory with atomicAdd (a sample receives at most two tiles' values when n_fft <= 9 hop, so
+// the sum is order-independent there; within n_fft/2 samples of the clip edges the reflected terms add a third).
+#pragma once
+
+#include "k1g_features.cuh"
+
+namespace mixfe {
+
+struct K6Params {
+    const float* stem[kNumStems];    // forward inputs
+    long long stride_b, stride_c;
+    float* out[kNumStems];           // gradients, zero-initialised by the caller
+    long long ostride_b, ostride_c;
+    const float* g;                  // d loss / d logmel: (b, ch, m, f) at g[b * g_stride_b + (ch * n_mels + m) * F + f]
+    long long g_stride_b;
+    int B, T, F, hop, n_mels, n_mels_pad, n_fft, log2n, nf, span;
+    const float2* twg;               // [n_fft/2]
+    const float* win;                // [n_fft] 0.5 * periodic hann
+    const int* mel_lo;               // filterbank by filter (CSR): first bin, bins, weight offset
+    const int* mel_len;
+    const int* mel_off;
+    const float* mel_w;
+    const int* bin_lo;               // filterbank by bin (CSR of the transpose): first filter, filters, weight offset
+    const int* bin_len;
+    const int* bin_off;
+    const float* bin_w;
+    int pw_stride;
+    int off_U, off_pw, off_mel, off_ola;
+};
+
+__global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant__ K6Params p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
+    float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][n/2+1] (L.re, L.im, R.re, R.im)
+    float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power, then dP
+    float2* const melb = reinterpret_cast<float2*>(smem + p.off_mel);        // [nf][n_mels_pad] dmel
+    float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [2][span]
+
+    const int tid = threadIdx.x;
+    const int tile = blockIdx.x, b = blockIdx.y, s = blockIdx.z;
+    const int n = p.n_fft, half = n >> 1, nb = half + 1;
+    const int t0 = tile * kTF;
+    const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
+    const int sh = 32 - p.log2n;
+    const float* gL = p.stem[s] + (long long)b * p.stride_b;
+    const float* gR = gL + p.stride_c;
+
+    for (int i = tid; i < 2 * p.span; i += kGThreads) ola[i] = 0.0f;
+
+    for (int f0 = 0; f0 < nvalid; f0 += p.nf) {
+        const int frames = nvalid - f0 < p.nf ? nvalid - f0 : p.nf;
+        // ---- forward: load + window, FFT, untangle ------------------------------------------------
+        for (int idx = tid; idx < frames * n; idx += kGThreads) {
+            const int f = idx / n, i = idx - f * n;
+            long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
+            if (j < 0) j = -j;
+            if (j >= p.T) j = 2ll * (p.T - 1) - j;
+            const float w = __ldg(p.win + i);
+            z[idx] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
+        }
+        __syncthreads();
+        int h = half;
+        for (; h >= 2; h >>= 2) {
+            k1g_pass4(z, p.twg, n, frames, h, tid);
+            __syncthreads();
+        }
+        if (h == 1) {
+            k1g_pass2_last(z, n, frames, tid);
+            __syncthreads();
+        }
+        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
+            const int f = idx / nb, k = idx - f * nb;
+            const float2 x = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
+            const float2 y = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
+            const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
+            U[(size_t)f * nb + k] = make_float4(a, bb, d, -c);               // L = a + i bb, R = d - i c
+            pw[(size_t)f * p.pw_stride + k] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
+        }
+        __syncthreads();
+        // ---- mel, then dmel = g / (mel + 1e-10) ---------------------------------------------------
+        for (int idx = tid; idx < frames * p.n_mels_pad; idx += kGThreads) {
+            const int f = idx / p.n_mels_pad, m = idx - f * p.n_mels_pad;
+            float dL = 0.0f, dR = 0.0f;
+            if (m < p.n_mels) {
+                const int lo = __ldg(p.mel_lo + m), len = __ldg(p.mel_len + m);
+                const float* w = p.mel_w + __ldg(p.mel_off + m);
+                const float2* src = pw + (size_t)f * p.pw_stride + lo;
+                float aL = 0.0f, aR = 0.0f;
+                for (int i = 0; i < len; ++i) {
+                    const float wi = __ldg(w + i);
+                    const float2 v = src[i];
+                    aL = fmaf(wi, v.x, aL);
+                    aR = fmaf(wi, v.y, aR);
+                }
+                const long long o = (long long)b * p.g_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + t0 + f0 + f;
+                dL = __ldg(p.g + o) / (aL + 1e-10f);
+                dR = __ldg(p.g + o + (long long)p.n_mels * p.F) / (aR + 1e-10f);
+            }
+            melb[idx] = make_float2(dL, dR);
+        }
+        __syncthreads();
+        // ---- dP[k] = sum_m fb[k][m] dmel[m] (overwrites the power column) ----------------------------
+        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
+            const int f = idx / nb, k = idx - f * nb;
+            const int lo = __ldg(p.bin_lo + k), len = __ldg(p.bin_len + k);
+            const float* w = p.bin_w + __ldg(p.bin_off + k);
+            const float2* src = melb + (size_t)f * p.n_mels_pad + lo;
+            float aL = 0.0f, aR = 0.0f;
+            for (int i = 0; i < len; ++i) {
+                const float wi = __ldg(w + i);
+                const float2 v = src[i];
+                aL = fmaf(wi, v.x, aL);
+                aR = fmaf(wi, v.y, aR);
+            }
+            pw[(size_t)f * p.pw_stride + k] = make_float2(aL, aR);
+        }
+        __syncthreads();
+        // ---- conj(Y) in natural order: G = 2 X dP, Hermitian extension, L + iR packing ------------------
+        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
+            const int f = idx / nb, k = idx - f * nb;
+            const float4 u = U[(size_t)f * nb + k];
+            const float2 dp = pw[(size_t)f * p.pw_stride + k];
+            const float a = 2.0f * u.x * dp.x, bi = 2.0f * u.y * dp.x;       // G_L = a + i bi
+            const float c = 2.0f * u.z * dp.y, di = 2.0f * u.w * dp.y;       // G_R = c + i di
+            float2* zf = z + (size_t)f * n;
+            if (k == 0 || k == half) {
+                zf[k] = make_float2(a, -c);
+            } else {
+                zf[k] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
+                zf[n - k] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
+            }
+        }
+        __syncthreads();
+        // ---- inverse transform = conj(FFT(conj Y)) ------------------------------------------------------
+        h = half;
+        for (; h >= 2; h >>= 2) {
+            k1g_pass4(z, p.twg, n, frames, h, tid);
+            __syncthreads();
+        }
+        if (h == 1) {
+            k1g_pass2_last(z, n, frames, tid);
+            __syncthreads();
+        }
+        // ---- window and overlap-add, one frame after the other (frames overlap) ------------------------
+        for (int f = 0; f < frames; ++f) {
+            float* oL = ola + (f0 + f) * p.hop;
+            float* oR = oL + p.span;
+            for (int i = tid; i < n; i += kGThreads) {
+                const float2 r = z[(size_t)f * n + (__brev((unsigned)i) >> sh)];
+                const float w = 2.0f * __ldg(p.win + i);
+                oL[i] = fmaf(w, r.x, oL[i]);
+                oR[i] = fmaf(-w, r.y, oR[i]);
+            }
+            __syncthreads();
+        }
+    }
+    __syncthreads();
+    // ---- the tile's span -> gradient, through the adjoint of the reflect padding ------------------------
+    float* dLp = p.out[s] + (long long)b * p.ostride_b;
+    float* dRp = dLp + p.ostride_c;
+    const int used = nvalid > 0 ? (nvalid - 1) * p.hop + n : 0;
+    for (int i = tid; i < used; i += kGThreads) {
+        long long j = (long long)t0 * p.hop - half + i;
+        if (j < 0) j = -j;
+        if (j >= p.T) j = 2ll * (p.T - 1) - j;
+        atomicAdd(dLp + j, ola[i]);
+        atomicAdd(dRp + j, ola[p.span + i]);
+    }
+}
+
+}  // namespace mixfe

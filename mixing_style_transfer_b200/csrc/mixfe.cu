@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "k1_features.cuh"
 #include "k1g_features.cuh"
+#include "k6_logmel_bwd.cuh"
 #include "plan.cuh"
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
@@ -216,6 +217,38 @@ int build_generic_tables(mixfe_plan* pl) {
     pl->smem_g = pl->g_off_red + 8 * 4 * 4;
     if (pl->smem_g > 227 * 1024) return fail(MIXFE_EUNSUPPORTED, "K1G needs %d bytes of shared memory", pl->smem_g);
     MIXFE_CUDA(cudaFuncSetAttribute(k1g_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_g));
+    // K6 (log-mel backward): filterbank by bin + its shared-memory map
+    {
+        std::vector<int> blo(nf, 0), blen(nf, 0), boff(nf, 0);
+        std::vector<float> bw;
+        for (int k = 0; k < nf; ++k) {
+            int first = -1, last = -1;
+            for (int m = 0; m < nm; ++m)
+                if (pl->fb[(size_t)k * nm + m] != 0.0f) { if (first < 0) first = m; last = m; }
+            boff[k] = (int)bw.size();
+            if (first >= 0) {
+                blo[k] = first; blen[k] = last - first + 1;
+                for (int m = first; m <= last; ++m) bw.push_back(pl->fb[(size_t)k * nm + m]);
+            }
+        }
+        if (bw.empty()) bw.push_back(0.0f);
+        if ((rc = upload(&pl->d_bin_lo, blo)) || (rc = upload(&pl->d_bin_len, blen)) || (rc = upload(&pl->d_bin_off, boff)) ||
+            (rc = upload(&pl->d_bin_w, bw)))
+            return rc;
+        pl->b_span = (kTF - 1) * pl->hop + n;
+        const int per = n * 8 + (n / 2 + 1) * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
+        const int ola = align16(2 * pl->b_span * 4);
+        int bn = kTF;
+        while (bn > 1 && bn * per + ola + 64 > 220 * 1024) bn >>= 1;
+        pl->b_nf = bn;
+        pl->b_off_U = bn * n * 8;
+        pl->b_off_pw = pl->b_off_U + bn * (n / 2 + 1) * 16;
+        pl->b_off_mel = pl->b_off_pw + bn * pl->g_pw_stride * 8;
+        pl->b_off_ola = align16(pl->b_off_mel + bn * pl->n_mels_pad * 8);
+        pl->smem_b = pl->b_off_ola + ola;
+        if (pl->smem_b > 227 * 1024) pl->smem_b = 0;          // hop too large for the overlap-add buffer: backward unsupported
+        else MIXFE_CUDA(cudaFuncSetAttribute(k6_logmel_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_b));
+    }
     return MIXFE_OK;
 }
 
@@ -306,6 +339,44 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     return MIXFE_OK;
 }
 
+int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B, int T,
+                        const float* grad_logmel, long long g_stride_b, float* const grad_stems[4], long long ostride_b,
+                        long long ostride_c, cudaStream_t stream) {
+    if (!pl || !stems || !grad_stems || !grad_logmel) return fail(MIXFE_EINVAL, "null plan, stems or gradients");
+    for (int s = 0; s < 4; ++s)
+        if (!stems[s] || !grad_stems[s]) return fail(MIXFE_EINVAL, "stems[%d] or grad_stems[%d] is NULL", s, s);
+    if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
+    if (B == 0) return MIXFE_OK;
+    if (T <= pl->n_fft / 2)
+        return fail(MIXFE_ESHORT, "Argument #4: Padding size should be less than the corresponding input dimension, "
+                                  "but got: padding (%d, %d) at dimension 2 of input of length %d",
+                    pl->n_fft / 2, pl->n_fft / 2, T);
+    if (stride_c < T || (B > 1 && stride_b < T) || ostride_c < T || (B > 1 && ostride_b < T))
+        return fail(MIXFE_EINVAL, "strides smaller than T");
+    if (!pl->smem_b) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: hop=%d needs more shared memory than an SM has", pl->hop);
+    if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: B=%d > 65535 clips per call", B);
+    DeviceGuard guard(pl->device);
+    K6Params p{};
+    for (int s = 0; s < 4; ++s) { p.stem[s] = stems[s]; p.out[s] = grad_stems[s]; }
+    p.stride_b = stride_b; p.stride_c = stride_c; p.ostride_b = ostride_b; p.ostride_c = ostride_c;
+    p.g = grad_logmel; p.g_stride_b = g_stride_b;
+    p.B = B; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
+    p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span;
+    p.twg = pl->d_twg; p.win = pl->d_win;
+    p.mel_lo = pl->d_mel_lo; p.mel_len = pl->d_mel_len; p.mel_off = pl->d_mel_off; p.mel_w = pl->d_mel_w;
+    p.bin_lo = pl->d_bin_lo; p.bin_len = pl->d_bin_len; p.bin_off = pl->d_bin_off; p.bin_w = pl->d_bin_w;
+    p.pw_stride = pl->g_pw_stride;
+    p.off_U = pl->b_off_U; p.off_pw = pl->b_off_pw; p.off_mel = pl->b_off_mel; p.off_ola = pl->b_off_ola;
+    const int n_tiles = (p.F + kTF - 1) / kTF;
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_LOGMEL_BWD, stream);
+        k6_logmel_bwd<<<dim3(n_tiles, B, kNumStems), kGThreads, pl->smem_b, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter()++;
+    return MIXFE_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -373,7 +444,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev); cudaFree(pl->d_sm_ticket);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
-    cudaFree(pl->d_mel_w);
+    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_lo); cudaFree(pl->d_bin_len); cudaFree(pl->d_bin_off); cudaFree(pl->d_bin_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;
@@ -438,6 +509,14 @@ int mixfe_features_logmel(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STE
                           long long logmel_stride_b, void* cuda_stream) {
     return run_features(pl, stems, stride_b, stride_c, B, T, features, logmel, logmel_stride_b, nullptr, 0,
                         static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_logmel_backward(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,
+                          long long stride_c, int B, int T, const float* grad_logmel, long long grad_logmel_stride_b,
+                          float* const grad_stems[MIXFE_NUM_STEMS], long long grad_stride_b, long long grad_stride_c,
+                          void* cuda_stream) {
+    return run_logmel_backward(pl, stems, stride_b, stride_c, B, T, grad_logmel, grad_logmel_stride_b, grad_stems,
+                               grad_stride_b, grad_stride_c, static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_debug_mel_power(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,

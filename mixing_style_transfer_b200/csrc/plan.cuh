@@ -27,6 +27,11 @@ struct mixfe_plan {
     int* d_mel_len = nullptr;
     int* d_mel_off = nullptr;
     float* d_mel_w = nullptr;
+    int* d_bin_lo = nullptr;            // CSR of the transposed filterbank (K6): first filter, count, weight offset per bin
+    int* d_bin_len = nullptr;
+    int* d_bin_off = nullptr;
+    float* d_bin_w = nullptr;
+    int b_nf = 0, b_span = 0, b_off_U = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)
     int g_nf = 0, g_log2n = 0, g_pw_stride = 0, g_off_pw = 0, g_off_mel = 0, g_off_S = 0, g_off_red = 0, smem_g = 0;
     // plan-owned workspace (grows to the high-water mark, then never reallocates)
     void* ws = nullptr;

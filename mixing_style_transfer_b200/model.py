@@ -66,12 +66,39 @@ class MelSpectrogramPreprocessor(nn.Module):
 
     def forward(self, stems_dict):
         first = stems_dict[STEMS[0]]
-        if any(stems_dict[n].requires_grad for n in STEMS) and torch.is_grad_enabled():
-            raise NotImplementedError(
-                "MelSpectrogramPreprocessor (libmixfe): backward through the log-mel is not built yet "
-                "(SURVEY.md section 8f row 1); detach the stems or run under torch.no_grad()")
         src_device = first.device
         device = _resolve_device(first, None)
-        stems, batched = _gather_stems(stems_dict, device)
-        _, lm = self._plan(device).features_logmel(stems, want_features=False, want_logmel=True)
+        plan = self._plan(device)
+        if torch.is_grad_enabled() and any(stems_dict[n].requires_grad for n in STEMS):
+            # the style-transfer loop differentiates through the encoder's log-mel (src/train_style_transfer.py:206-215)
+            lm = _LogMelFunction.apply(plan, device, *[stems_dict[n] for n in STEMS])
+        else:
+            stems, _ = _gather_stems(stems_dict, device)
+            _, lm = plan.features_logmel(stems, want_features=False, want_logmel=True)
         return lm if lm.device == src_device else lm.to(src_device)
+
+
+class _LogMelFunction(torch.autograd.Function):
+    """log-mel with a hand-written backward (kernel K6); the forward saves only its inputs."""
+
+    @staticmethod
+    def forward(ctx, plan, device, *stems):
+        gathered, _ = _gather_stems(dict(zip(STEMS, stems)), device)
+        _, lm = plan.features_logmel(gathered, want_features=False, want_logmel=True)
+        ctx.plan = plan
+        ctx.meta = [(x.dim(), x.device, x.dtype) for x in stems]
+        ctx.save_for_backward(*gathered)
+        return lm
+
+    @staticmethod
+    def backward(ctx, grad_logmel):
+        grads = ctx.plan.logmel_backward(list(ctx.saved_tensors), grad_logmel)
+        out = []
+        for g, (dim, dev, dt), need in zip(grads, ctx.meta, ctx.needs_input_grad[2:]):
+            if not need:
+                out.append(None)
+                continue
+            if dim == 2:
+                g = g[0]
+            out.append(g.to(device=dev, dtype=dt))
+        return (None, None, *out)
