@@ -25,7 +25,8 @@
 
 namespace mixfe {
 
-constexpr int kAugV = 16;                 // samples per lane per block
+constexpr int kAugLogV = 4;
+constexpr int kAugV = 1 << kAugLogV;       // samples per lane per block
 constexpr int kAugBlock = 32 * kAugV;     // 512 samples per warp step
 constexpr int kAugWarps = kNumStems;      // warps per CTA, one stem each
 
@@ -50,6 +51,7 @@ struct SecTables {                         // per warp, per section, in shared m
     double mp[6][4];                       // M^(2^d), d = 0..5, row-major 2x2
     double h[kAugV][2];                    // C A^n
     double ml[4][32];                      // M^(lane+1), component-major
+    double carry[2];                       // state at the start of the block being processed (warp-uniform)
 };
 
 __device__ __forceinline__ void mat2_mul(const double (&a)[4], const double (&b)[4], double (&c)[4]) {
@@ -61,13 +63,13 @@ __device__ __forceinline__ void mat2_mul(const double (&a)[4], const double (&b)
 
 // Every lane computes the (tiny) tables redundantly in registers; lanes then store their share.
 __device__ __forceinline__ void build_tables(SecTables& tb, double a1, double a2, int lane) {
-    double ap[5][4];                        // A^(2^d), d = 0..4  (A^16 = M)
+    double ap[kAugLogV + 1][4];             // A^(2^d), d = 0..log2 V  (A^V = M)
     ap[0][0] = -a1; ap[0][1] = 1.0; ap[0][2] = -a2; ap[0][3] = 0.0;
 #pragma unroll
-    for (int d = 1; d < 5; ++d) mat2_mul(ap[d - 1], ap[d - 1], ap[d]);
+    for (int d = 1; d <= kAugLogV; ++d) mat2_mul(ap[d - 1], ap[d - 1], ap[d]);
     double mp[6][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) mp[0][i] = ap[4][i];
+    for (int i = 0; i < 4; ++i) mp[0][i] = ap[kAugLogV][i];
 #pragma unroll
     for (int d = 1; d < 6; ++d) mat2_mul(mp[d - 1], mp[d - 1], mp[d]);
     if (lane < 6) {
@@ -93,11 +95,11 @@ __device__ __forceinline__ void build_tables(SecTables& tb, double a1, double a2
 #pragma unroll
         for (int i = 0; i < 4; ++i) tb.ml[i][lane] = r[i];
     }
-    // h[n] = first row of A^n, n = lane < 16
+    // h[n] = first row of A^n, n = lane < V
     if (lane < kAugV) {
         double r0 = 1.0, r1 = 0.0;
 #pragma unroll
-        for (int d = 0; d < 4; ++d) {
+        for (int d = 0; d < kAugLogV; ++d) {
             if ((lane >> d) & 1) {
                 const double n0 = r0 * ap[d][0] + r1 * ap[d][2];
                 const double n1 = r0 * ap[d][1] + r1 * ap[d][3];
@@ -111,18 +113,26 @@ __device__ __forceinline__ void build_tables(SecTables& tb, double a1, double a2
 }
 
 // One biquad over the lane's 16 samples (in place) with the warp-wide state scan.
+// Zero-state response in direct form, w[n] = b0 x[n] + b1 x[n-1] + b2 x[n-2] (no dependences) and
+// y[n] = (w[n] - a2 y[n-2]) - a1 y[n-1]: ONE dependent DFMA per sample instead of the two of the DF2T update; the
+// DF2T state the scan works on is rebuilt from the last two inputs and outputs.
 __device__ __forceinline__ void biquad_block(double (&v)[kAugV], const double* c /*b0 b1 b2 a1 a2*/,
-                                             const SecTables& tb, double& carry1, double& carry2, int lane) {
+                                             SecTables& tb, int lane) {
     const double b0 = c[0], b1 = c[1], b2 = c[2], a1 = c[3], a2 = c[4];
-    double z1 = 0.0, z2 = 0.0;
+    const double carry1 = tb.carry[0], carry2 = tb.carry[1];
+    double xm1 = 0.0, xm2 = 0.0, ym1 = 0.0, ym2 = 0.0;
 #pragma unroll
     for (int n = 0; n < kAugV; ++n) {
         const double x = v[n];
-        const double y = fma(b0, x, z1);
-        z1 = fma(b1, x, fma(-a1, y, z2));
-        z2 = fma(b2, x, -a2 * y);
+        const double w = fma(b0, x, fma(b1, xm1, b2 * xm2));
+        const double y = fma(-a1, ym1, fma(-a2, ym2, w));
+        xm2 = xm1; xm1 = x;
+        ym2 = ym1; ym1 = y;
         v[n] = y;
     }
+    // DF2T state after the last sample: z1 = b1 x[N-1] - a1 y[N-1] + (b2 x[N-2] - a2 y[N-2]), z2 = b2 x[N-1] - a2 y[N-1]
+    double z1 = fma(b1, xm1, fma(-a1, ym1, fma(b2, xm2, -a2 * ym2)));
+    double z2 = fma(b2, xm1, -a2 * ym1);
     // inclusive scan of end states: e_l <- sum_{j<=l} M^(l-j) e_j
 #pragma unroll
     for (int d = 0; d < 5; ++d) {
@@ -138,8 +148,9 @@ __device__ __forceinline__ void biquad_block(double (&v)[kAugV], const double* c
     double s1 = __shfl_up_sync(kFullMask, z1, 1);
     double s2 = __shfl_up_sync(kFullMask, z2, 1);
     if (lane == 0) { s1 = carry1; s2 = carry2; }
-    carry1 = __shfl_sync(kFullMask, z1, 31);
-    carry2 = __shfl_sync(kFullMask, z2, 31);
+    __syncwarp();                                        // every lane has read the old carry
+    if (lane == 31) { tb.carry[0] = z1; tb.carry[1] = z2; }
+    __syncwarp();
 #pragma unroll
     for (int n = 0; n < kAugV; ++n) v[n] = fma(tb.h[n][0], s1, fma(tb.h[n][1], s2, v[n]));
 }
@@ -183,7 +194,8 @@ __global__ void __launch_bounds__(kAugWarps * 32, 4) k3_augment(const __grid_con
         long long start = filtered ? c0 - p.warm : c0;      // c0 and warm are multiples of the block
         if (start < 0) start = 0;
         const bool vec_ok = ((reinterpret_cast<unsigned long long>(src) | reinterpret_cast<unsigned long long>(dst)) & 15ull) == 0;
-        double cr[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+        if (lane < 3) { tables[warp][lane].carry[0] = 0.0; tables[warp][lane].carry[1] = 0.0; }
+        __syncwarp();
         double energy = 0.0;
         // the next block's samples are requested before this block's (long, serial) arithmetic starts
         auto fetch = [&](long long blk, float4 (&q)[kAugV / 4]) {
@@ -211,26 +223,27 @@ __global__ void __launch_bounds__(kAugWarps * 32, 4) k3_augment(const __grid_con
 #pragma unroll
             for (int n = 0; n < kAugV; ++n) x[n] *= gain;
             if (filtered) {
+                // one copy of the biquad in the instruction stream: sections 0 (tilt), 1 and 2 (band-limit), the
+                // compressor between 0 and 1; fp32 rounding where the reference's .float() sits (:433, :456)
                 double v[kAugV];
-                if (tilt) {
 #pragma unroll
-                    for (int n = 0; n < kAugV; ++n) v[n] = (double)x[n];
-                    biquad_block(v, cp.sos[s][0], tables[warp][0], cr[0][0], cr[0][1], lane);
+                for (int n = 0; n < kAugV; ++n) v[n] = (double)x[n];
+#pragma unroll 1
+                for (int sec = 0; sec < 3; ++sec) {
+                    if (sec == 1 && comp) {
 #pragma unroll
-                    for (int n = 0; n < kAugV; ++n) x[n] = (float)v[n];
+                        for (int n = 0; n < kAugV; ++n) v[n] = (double)compress_static((float)v[n]);
+                    }
+                    if (sec == 0 ? tilt : bw) {
+                        biquad_block(v, cp.sos[s][sec], tables[warp][sec], lane);
+                        if (sec == 0) {
+#pragma unroll
+                            for (int n = 0; n < kAugV; ++n) v[n] = (double)(float)v[n];
+                        }
+                    }
                 }
-                if (comp) {
 #pragma unroll
-                    for (int n = 0; n < kAugV; ++n) x[n] = compress_static(x[n]);
-                }
-                if (bw) {
-#pragma unroll
-                    for (int n = 0; n < kAugV; ++n) v[n] = (double)x[n];
-                    biquad_block(v, cp.sos[s][1], tables[warp][1], cr[1][0], cr[1][1], lane);
-                    biquad_block(v, cp.sos[s][2], tables[warp][2], cr[2][0], cr[2][1], lane);
-#pragma unroll
-                    for (int n = 0; n < kAugV; ++n) x[n] = (float)v[n];
-                }
+                for (int n = 0; n < kAugV; ++n) x[n] = (float)v[n];
             } else if (comp) {
 #pragma unroll
                 for (int n = 0; n < kAugV; ++n) x[n] = compress_static(x[n]);
