@@ -202,7 +202,10 @@ __global__ void __launch_bounds__(kAugWarps * 32, 4) k3_augment(const __grid_con
             const long long i0 = blk + (long long)lane * kAugV;
             if (blk < c1 && vec_ok && i0 + kAugV <= p.T) {
 #pragma unroll
-                for (int j = 0; j < kAugV / 4; ++j) q[j] = __ldg(reinterpret_cast<const float4*>(src + i0) + j);
+                for (int j = 0; j < kAugV / 4; ++j)          // volatile: ptxas must not sink the loads to their first use
+                    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(q[j].x), "=f"(q[j].y), "=f"(q[j].z), "=f"(q[j].w)
+                                 : "l"(reinterpret_cast<const float4*>(src + i0) + j));
             }
         };
         float4 qn[kAugV / 4];
@@ -219,9 +222,14 @@ __global__ void __launch_bounds__(kAugWarps * 32, 4) k3_augment(const __grid_con
 #pragma unroll
                 for (int n = 0; n < kAugV; ++n) x[n] = i0 + n < p.T ? __ldg(src + i0 + n) : 0.0f;
             }
-            fetch(blk + kAugBlock, qn);
+            // consume this block's loads BEFORE the next block's are issued: a wait on the loads' scoreboard would
+            // otherwise also wait for the new ones and expose the full memory latency every block
 #pragma unroll
             for (int n = 0; n < kAugV; ++n) x[n] *= gain;
+#pragma unroll
+            for (int n = 0; n < kAugV; n += 4)
+                asm volatile("" : "+f"(x[n]), "+f"(x[n + 1]), "+f"(x[n + 2]), "+f"(x[n + 3]));
+            fetch(blk + kAugBlock, qn);
             if (filtered) {
                 // one copy of the biquad in the instruction stream: sections 0 (tilt), 1 and 2 (band-limit), the
                 // compressor between 0 and 1; fp32 rounding where the reference's .float() sits (:433, :456)
