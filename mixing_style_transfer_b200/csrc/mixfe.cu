@@ -207,7 +207,11 @@ int build_generic_tables(mixfe_plan* pl) {
     pl->g_pw_stride = (n / 2 + 1) | 1;
     const int per_frame = n * 8 + pl->g_pw_stride * 8;
     int nfr = kTF;
-    while (nfr > 1 && nfr * per_frame > 160 * 1024) nfr >>= 1;
+    {
+        const char* e = getenv("MIXFE_K1G_SMEM_KB");            // tuning knob: frame-buffer budget per CTA
+        const int budget = (e ? atoi(e) : 72) * 1024;       // 72 KB: 2-3 CTAs per SM beat one CTA with all 8 frames in flight (profiles/README.md)
+        while (nfr > 1 && nfr * per_frame > budget) nfr >>= 1;
+    }
     pl->g_nf = nfr;
     pl->g_off_pw = nfr * n * 8;
     const int stage = pl->g_off_pw + nfr * pl->g_pw_stride * 8;
@@ -239,7 +243,9 @@ int build_generic_tables(mixfe_plan* pl) {
         const int per = n * 8 + (n / 2 + 1) * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
         const int ola = align16(2 * pl->b_span * 4);
         int bn = kTF;
-        while (bn > 1 && bn * per + ola + 64 > 220 * 1024) bn >>= 1;
+        const char* e6 = getenv("MIXFE_K6_SMEM_KB");
+        const int budget6 = (e6 ? atoi(e6) : 50) * 1024;
+        while (bn > 1 && bn * per + ola + 64 > budget6) bn >>= 1;
         pl->b_nf = bn;
         pl->b_off_U = bn * n * 8;
         pl->b_off_pw = pl->b_off_U + bn * (n / 2 + 1) * 16;
