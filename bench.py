@@ -331,6 +331,34 @@ def run_native(args):
                      "note": "in-place all_gather_into_tensor of (72,64) features + (72,8,128,1723) fp32 log-mels per rank; "
                              "not part of value (extraction is collective-free)"}
         del ggb
+        # config 5 (global contrastive batch): extraction followed by the gather (NCCL), the two pipelined in 4 chunks
+        # (gather of chunk c on a side stream under the kernels of chunk c + 1), and the same with copy-engine pushes
+        # into symmetric (NVLink-mapped) buffers, which need no SMs and therefore do overlap the persistent kernel
+        from mixing_style_transfer_b200.distributed import extract_global_batch
+        stems_d = dict(zip(pkg.STEMS, stems))
+        comm = torch.cuda.Stream(device=dev)
+        both = {}
+        ref_gb = extract_global_batch(fe, stems_d, n_chunks=4, comm_stream=comm)
+        torch.cuda.synchronize()
+        for label, nch, sym in (("nccl_serial_ms", 1, False), ("nccl_pipelined_4_chunks_ms", 4, False),
+                                ("symmetric_ce_serial_ms", 1, True), ("symmetric_ce_pipelined_4_chunks_ms", 4, True)):
+            gbx = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True, n_chunks=nch, symmetric=sym)
+            for _ in range(2):
+                extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
+            torch.cuda.synchronize(); barrier()
+            a0.record()
+            for _ in range(reps):
+                extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
+            a1.record(); torch.cuda.synchronize(); barrier()
+            t = torch.tensor([a0.elapsed_time(a1) / reps], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            both[label] = float(t.item())
+            if nch == 4:
+                both[label.replace("_ms", "_equals_nccl")] = bool(torch.equal(gbx.logmel, ref_gb.logmel)
+                                                                  and torch.equal(gbx.features, ref_gb.features))
+            del gbx
+        del ref_gb
+        allgather["extract_plus_gather"] = both
 
     # ---- end to end from pinned host memory through the public pipeline ---------------------------
     e2e = None

@@ -72,7 +72,8 @@ _lock = threading.Lock()
 EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_plan_destroy",
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
-           "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config")
+           "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
+           "mixfe_plan_reserve_sms")
 
 
 def lib() -> ctypes.CDLL:
@@ -105,6 +106,7 @@ def lib() -> ctypes.CDLL:
                                     ctypes.POINTER(AugParams), vp, ci, vp]
         L.mixfe_launch_count.restype = ll
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
+        L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
@@ -272,6 +274,10 @@ class Plan:
         return outs
 
     KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4}
+
+    def reserve_sms(self, n: int) -> None:
+        """Leave n SMs out of K1's persistent grid (so a collective can run beside it); 0 = full grid."""
+        _check(lib().mixfe_plan_reserve_sms(self._h, int(n)))
 
     def enable_timing(self, on: bool = True) -> None:
         _check(lib().mixfe_plan_enable_timing(self._h, 1 if on else 0))

@@ -325,7 +325,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         k1g_features<<<dim3(n_tiles, B), kGThreads, pl->smem_g, stream>>>(g);
     } else {
         KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
-        const int grid = (int)std::min<long long>(p.total_items, pl->k1_ctas);
+        const int per_sm = pl->n_sms ? pl->k1_ctas / pl->n_sms : 1;
+        const int grid = (int)std::min<long long>(p.total_items, (long long)per_sm * (pl->n_sms - pl->reserved_sms));
         k1_features<<<grid, kK1Threads, pl->smem_k1, stream>>>(p);
     }
     MIXFE_CUDA(cudaGetLastError());
@@ -462,6 +463,12 @@ int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
     MIXFE_CUDA(cudaDeviceSynchronize());            // tables may be in use by queued launches
     pl->fb.assign(fb_host, fb_host + (size_t)pl->n_freq * pl->n_mels);
     return build_tables(pl);
+}
+
+int mixfe_plan_reserve_sms(mixfe_plan* pl, int n_sms) {
+    if (!pl || n_sms < 0) return fail(MIXFE_EINVAL, "bad plan or SM count");
+    pl->reserved_sms = std::min(n_sms, std::max(0, pl->n_sms - 1));
+    return MIXFE_OK;
 }
 
 int mixfe_plan_enable_timing(mixfe_plan* pl, int enable) {

@@ -49,6 +49,19 @@ def _worker(rank, world, port, q):
             ok &= bool((gb.features[3 * r:3 * r + 3] == r + 1).all())
             ok &= bool(gb.logmel[3 * r, 0, 0, 0] == 1000 * r)
         ok &= gb.payload_bytes_received() == 4 * 3 * (64 + 8 * 4 * 5) * (world - 1)
+        # chunk-major layout: chunk c of every rank is contiguous, gathered chunk by chunk
+        gc = GlobalBatch(n_local=6, feature_dim=4, n_mels=2, n_frames=3, device="cpu", n_chunks=3)
+        for c in range(3):
+            f, lm = gc.local_views(c)
+            for i in range(gc.cs):
+                f[i].fill_(100.0 * rank + c * gc.cs + i)          # value encodes (rank, local clip)
+                lm[i].fill_(100.0 * rank + c * gc.cs + i)
+            gc.all_gather(chunk=c)
+        for r in range(world):
+            for j in range(6):
+                row = gc.global_index(r, j)
+                ok &= bool((gc.features[row] == 100.0 * r + j).all()) and bool((gc.logmel[row] == 100.0 * r + j).all())
+        ok &= sorted(gc.global_index(r, j) for r in range(world) for j in range(6)) == list(range(6 * world))
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
