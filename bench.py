@@ -368,7 +368,7 @@ def run_native(args):
             host[n].copy_(s)
         hf = HostPipeline.pinned_like((N_CLIPS, plan.feature_dim))
         hl = HostPipeline.pinned_like((N_CLIPS, 8, N_MELS, F))
-        pipe = HostPipeline(fe, N_CLIPS, T, chunk=6, device=dev, with_logmel=True)
+        pipe = HostPipeline(fe, N_CLIPS, T, chunk=12, device=dev, with_logmel=True)
         pipe.run(host, hf, hl)
         torch.cuda.synchronize(); barrier()
         t0 = time.perf_counter()

@@ -21,6 +21,23 @@ class HostPipeline:
         self.plan = extractor._plan(self.device)
         self.n, self.T, self.chunk = n_clips, T, max(1, min(chunk, n_clips))
         self.with_logmel = with_logmel
+        # chunk boundaries: short chunks at both ends (the first upload and the last download are the only legs
+        # that nothing overlaps), full ones in between
+        sizes, left, ramp = [], n_clips, [max(1, self.chunk // 4), max(1, self.chunk // 2)]
+        head = [r for r in ramp if r < self.chunk]
+        for r in head:
+            if left > 2 * sum(head):
+                sizes.append(r); left -= r
+        tail = list(reversed(sizes))
+        left -= sum(tail)
+        while left > 0:
+            m = min(self.chunk, left)
+            sizes.append(m); left -= m
+        sizes += tail
+        self.bounds, lo = [], 0
+        for m in sizes:
+            self.bounds.append((lo, lo + m)); lo += m
+        assert lo == n_clips
         F = self.plan.num_frames(T)
         # two device slots so that chunk i+1 uploads while chunk i computes
         self.slots = []
@@ -48,9 +65,7 @@ class HostPipeline:
         cur = torch.cuda.current_stream(self.device)
         for s in (self.s_up, self.s_run, self.s_down):
             s.wait_stream(cur)
-        n_chunks = (self.n + self.chunk - 1) // self.chunk
-        for i in range(n_chunks):
-            lo, hi = i * self.chunk, min(self.n, (i + 1) * self.chunk)
+        for i, (lo, hi) in enumerate(self.bounds):
             m = hi - lo
             slot = self.slots[i & 1]
             with torch.cuda.stream(self.s_up):
