@@ -341,7 +341,8 @@ def run_native(args):
         ref_gb = extract_global_batch(fe, stems_d, n_chunks=4, comm_stream=comm)
         torch.cuda.synchronize()
         for label, nch, sym in (("nccl_serial_ms", 1, False), ("nccl_pipelined_4_chunks_ms", 4, False),
-                                ("symmetric_ce_serial_ms", 1, True), ("symmetric_ce_pipelined_4_chunks_ms", 4, True)):
+                                ("symmetric_ce_serial_ms", 1, True), ("symmetric_ce_pipelined_4_chunks_ms", 4, True),
+                                ("multicast_ce_serial_ms", 1, "multicast"), ("multicast_ce_pipelined_4_chunks_ms", 4, "multicast")):
             gbx = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True, n_chunks=nch, symmetric=sym)
             for _ in range(2):
                 extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)

@@ -107,6 +107,11 @@ int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
  * reference configuration), its dynamic shared memory, and the steps of the warp-local mel walk. */
 int mixfe_debug_feature_kernel_config(const mixfe_plan* plan, int* ctas_per_sm, int* smem_bytes, int* mel_steps);
 
+/* Device-to-device copy by a copy engine, stream-ordered on `cuda_stream`.  dst may be the NVSwitch multicast
+ * mapping of a symmetric allocation: one copy then lands in every rank's buffer (distributed.GlobalBatch,
+ * the all-gather of BASELINE config 5 without kernels). */
+int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream);
+
 /* K1 runs as a persistent grid that fills every SM; a collective launched beside it (the all-gather of the
  * previous chunk, distributed.extract_global_batch) cannot start until CTAs retire.  Leaving n_sms SMs out
  * of K1's grid lets it run concurrently.  0 restores the full grid. */

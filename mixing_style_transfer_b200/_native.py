@@ -73,7 +73,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
-           "mixfe_plan_reserve_sms")
+           "mixfe_plan_reserve_sms", "mixfe_copy_async")
 
 
 def lib() -> ctypes.CDLL:
@@ -107,6 +107,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_launch_count.restype = ll
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
+        L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
@@ -151,6 +152,12 @@ def unify_stems(stems: Sequence[torch.Tensor]):
     if not ok:
         st = [s.contiguous() for s in st]
     return st, st[0].stride(0), st[0].stride(1)
+
+
+def copy_async(dst_ptr: int, src: torch.Tensor, nbytes: int) -> None:
+    """Copy-engine D2D copy of `nbytes` from the (contiguous) tensor `src` to the raw device address `dst_ptr` on the
+    current stream of src's device; dst_ptr may be an NVSwitch multicast address."""
+    _check(lib().mixfe_copy_async(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src.data_ptr()), nbytes, _stream(src.device)))
 
 
 class Plan:

@@ -465,6 +465,12 @@ int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
     return build_tables(pl);
 }
 
+int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream) {
+    if (!dst || !src) return fail(MIXFE_EINVAL, "null dst or src");
+    MIXFE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(cuda_stream)));
+    return MIXFE_OK;
+}
+
 int mixfe_plan_reserve_sms(mixfe_plan* pl, int n_sms) {
     if (!pl || n_sms < 0) return fail(MIXFE_EINVAL, "bad plan or SM count");
     pl->reserved_sms = std::min(n_sms, std::max(0, pl->n_sms - 1));

@@ -46,7 +46,7 @@ class GlobalBatch:
 
     def __init__(self, n_local: int, feature_dim: int, n_mels: int, n_frames: int, device,
                  group: Optional[dist.ProcessGroup] = None, with_logmel: bool = True, n_chunks: int = 1,
-                 symmetric: bool = False):
+                 symmetric=False):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -58,6 +58,8 @@ class GlobalBatch:
         n = n_local * self.world                    # all_gather_into_tensor needs equal shards
         self._peers = None                          # symmetric mode: (features, logmel) views of every rank's buffers
         self._handle = None
+        self._mc = None                             # multicast mode: (address of features, address of logmel) in the multicast mapping
+        self._stage = None                          # multicast mode: this rank's results before they are multicast
         if symmetric and self.world > 1:
             # One NVLink-mapped allocation per rank (torch symmetric memory); the gather is then a set of
             # copy-engine pushes into the peers' buffers: no SMs, so it runs under the persistent feature kernel.
@@ -72,6 +74,14 @@ class GlobalBatch:
                 return f, (t[nf:].view(n, 8, n_mels, n_frames) if with_logmel else None)
             self.features, self.logmel = views(flat)
             self._peers = [views(self._handle.get_buffer(r, (nf + nl,), torch.float32)) for r in range(self.world)]
+            if symmetric == "multicast":
+                # One copy to the NVSwitch multicast mapping lands in EVERY rank's buffer (this one included), so the
+                # kernels write a local staging slice and 2 copies per chunk replace the 2 (world - 1) pushes.
+                if not self._handle.multicast_ptr:
+                    raise RuntimeError("symmetric='multicast': this allocation has no NVSwitch multicast mapping")
+                self._mc = (self._handle.multicast_ptr, self._handle.multicast_ptr + 4 * nf)
+                self._stage = (torch.empty((n_local, feature_dim), dtype=torch.float32, device=device),
+                               torch.empty((n_local, 8, n_mels, n_frames), dtype=torch.float32, device=device) if with_logmel else None)
             return
         self.features = torch.empty((n, feature_dim), dtype=torch.float32, device=device)
         self.logmel = torch.empty((n, 8, n_mels, n_frames), dtype=torch.float32, device=device) if with_logmel else None
@@ -90,6 +100,9 @@ class GlobalBatch:
             if self.n_chunks != 1:
                 raise ValueError("chunk-major layout: ask for one chunk's views")
             chunk = 0
+        if self._stage is not None:
+            a = chunk * self.cs
+            return self._stage[0][a:a + self.cs], (self._stage[1][a:a + self.cs] if self._stage[1] is not None else None)
         lo = self._chunk_span(chunk)[0] + self.rank * self.cs
         f = self.features[lo:lo + self.cs]
         lm = self.logmel[lo:lo + self.cs] if self.logmel is not None else None
@@ -106,6 +119,12 @@ class GlobalBatch:
         for c in (range(self.n_chunks) if chunk is None else [chunk]):
             lo = self._chunk_span(c)[0] + self.rank * self.cs
             f, lm = self.local_views(c)
+            if self._mc is not None:
+                from ._native import copy_async
+                if lm is not None:
+                    copy_async(self._mc[1] + 4 * lo * self.logmel[0].numel(), lm, 4 * lm.numel())
+                copy_async(self._mc[0] + 4 * lo * self.features.shape[1], f, 4 * f.numel())
+                continue
             for k in range(1, self.world):
                 pf, plm = self._peers[(self.rank + k) % self.world]
                 if lm is not None:
@@ -138,7 +157,7 @@ class GlobalBatch:
 
 def extract_global_batch(extractor, local_stems: Dict[str, torch.Tensor], group=None, with_logmel: bool = True,
                          gather: bool = True, n_chunks: int = 1, comm_stream=None,
-                         out: Optional[GlobalBatch] = None, symmetric: bool = False) -> GlobalBatch:
+                         out: Optional[GlobalBatch] = None, symmetric=False) -> GlobalBatch:
     """features + log-mel of this rank's clips written into the global buffers, then all-gathered.
 
     n_chunks > 1 pipelines the two: the clips are processed in n_chunks launches and the gather of chunk c runs on
@@ -146,7 +165,8 @@ def extract_global_batch(extractor, local_stems: Dict[str, torch.Tensor], group=
     for the last gather before returning.  The global order is then chunk-major (GlobalBatch.global_index).
     With NCCL the overlap is small -- its kernels need whole SMs and the persistent feature kernel holds every
     register of every SM -- so `symmetric=True` (copy-engine pushes into NVLink-mapped peer buffers, GlobalBatch.push)
-    is the mode that pipelines.  `out` reuses a GlobalBatch (symmetric buffers cost a rendezvous to create); the
+    is the mode that pipelines; `symmetric="multicast"` sends each chunk ONCE, to the NVSwitch multicast mapping.
+    `out` reuses a GlobalBatch (symmetric buffers cost a rendezvous to create); the
     caller then makes sure the peers are done reading the previous contents."""
     from ._native import STEMS
     first = local_stems[STEMS[0]]
