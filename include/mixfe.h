@@ -98,6 +98,14 @@ int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
                           float* const grad_stems[MIXFE_NUM_STEMS], long long grad_stride_b,
                           long long grad_stride_c, void* cuda_stream);
 
+/* EXTENSION (no counterpart in the reference, whose compute_loudness is un-weighted and un-gated,
+ * src/mixing_utils.py:311-318): integrated loudness after ITU-R BS.1770-4 --
+ * K-weighting, 400 ms blocks with 75 % overlap, absolute gate -70 LUFS, relative gate -10 LU -- of each stem and
+ * of the mixture.  lufs: device [B][5] fp32 = vocals, bass, drums, other, mixture (-inf when no block passes the
+ * gates).  Needs sample_rate % 10 == 0 and T >= 0.4 s (MIXFE_EINVAL otherwise).  Not part of the feature vector. */
+int mixfe_gated_loudness(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
+                         long long stride_b, long long stride_c, int B, int T, float* lufs, void* cuda_stream);
+
 /* Test hook: mel POWER (before the log) for every channel, same addressing as logmel. */
 int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                           long long stride_b, long long stride_c, int B, int T,
@@ -128,7 +136,8 @@ long long mixfe_launch_count(void);
 #define MIXFE_KERNEL_AUGMENT 2    /* K3: gain/biquad/compressor scan */
 #define MIXFE_KERNEL_REVERB 3     /* K4/K5: FFT-domain reverb + redistribution (all its launches) */
 #define MIXFE_KERNEL_LOGMEL_BWD 4 /* K6: backward of the log-mel */
-#define MIXFE_NUM_KERNELS 5
+#define MIXFE_KERNEL_LOUDNESS 5   /* K7: K-weighting scan + sub-block energies + gating */
+#define MIXFE_NUM_KERNELS 6
 int mixfe_plan_enable_timing(mixfe_plan* plan, int enable);
 int mixfe_plan_kernel_time(mixfe_plan* plan, int which, double* total_ms, long long* launches);
 

@@ -73,7 +73,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
-           "mixfe_plan_reserve_sms", "mixfe_copy_async")
+           "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness")
 
 
 def lib() -> ctypes.CDLL:
@@ -108,6 +108,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
+        L.mixfe_gated_loudness.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
@@ -244,6 +245,16 @@ class Plan:
                                                outs[0].stride(0), outs[0].stride(1), _stream(self.device)))
         return outs
 
+    def gated_loudness(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
+        """(B,5) BS.1770-4 integrated loudness [vocals, bass, drums, other, mixture] in LUFS (kernel K7; extension)."""
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        out = torch.empty((B, 5), dtype=torch.float32, device=self.device)
+        ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_gated_loudness(self._h, ptrs, sb, sc, B, T, _ptr(out), _stream(self.device)))
+        return out
+
     def debug_mel_power(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
         st, sb, sc = unify_stems(stems)
         B, _, T = st[0].shape
@@ -280,7 +291,7 @@ class Plan:
                                        _stream(self.device)))
         return outs
 
-    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4}
+    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5}
 
     def reserve_sms(self, n: int) -> None:
         """Leave n SMs out of K1's persistent grid (so a collective can run beside it); 0 = full grid."""

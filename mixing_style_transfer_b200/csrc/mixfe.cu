@@ -15,6 +15,7 @@
 #include "plan.cuh"
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
+#include "k7_loudness.cuh"
 
 using namespace mixfe;
 
@@ -384,6 +385,65 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
     return MIXFE_OK;
 }
 
+// BS.1770-4 K-weighting for an arbitrary sample rate: bilinear transform (with pre-warping) of the analog prototype
+// behind the Recommendation's 48 kHz table; at 48 kHz this gives the table's coefficients (oracle/bs1770.py checks).
+void k_weighting(double fs, double (&sos)[2][5]) {
+    {
+        const double f0 = 1681.974450955533, G = 3.999843853973347, Q = 0.7071752369554196;
+        const double K = std::tan(M_PI * f0 / fs), Vh = std::pow(10.0, G / 20.0), Vb = std::pow(Vh, 0.4996667741545416);
+        const double a0 = 1.0 + K / Q + K * K;
+        sos[0][0] = (Vh + Vb * K / Q + K * K) / a0; sos[0][1] = 2.0 * (K * K - Vh) / a0; sos[0][2] = (Vh - Vb * K / Q + K * K) / a0;
+        sos[0][3] = 2.0 * (K * K - 1.0) / a0; sos[0][4] = (1.0 - K / Q + K * K) / a0;
+    }
+    {
+        const double f0 = 38.13547087602444, Q = 0.5003270373238773;
+        const double K = std::tan(M_PI * f0 / fs), a0 = 1.0 + K / Q + K * K;
+        sos[1][0] = 1.0; sos[1][1] = -2.0; sos[1][2] = 1.0;
+        sos[1][3] = 2.0 * (K * K - 1.0) / a0; sos[1][4] = (1.0 - K / Q + K * K) / a0;
+    }
+}
+
+int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B, int T,
+                       float* out, cudaStream_t stream) {
+    if (!pl || !stems || !out) return fail(MIXFE_EINVAL, "null plan, stems or output");
+    for (int s = 0; s < 4; ++s)
+        if (!stems[s]) return fail(MIXFE_EINVAL, "stems[%d] is NULL", s);
+    if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
+    if (pl->sr % 10) return fail(MIXFE_EUNSUPPORTED, "gated loudness: sample rate %d is not a multiple of 10 Hz", pl->sr);
+    const int sub = pl->sr / 10;
+    if (T < 4 * sub) return fail(MIXFE_EINVAL, "Audio must have length greater than the block size (%d samples)", 4 * sub);
+    if (B == 0) return MIXFE_OK;
+    if (stride_c < T || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
+    if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "gated loudness: B=%d > 65535 clips per call", B);
+    DeviceGuard guard(pl->device);
+    K7Params p{};
+    for (int s = 0; s < 4; ++s) p.stem[s] = stems[s];
+    p.stride_b = stride_b; p.stride_c = stride_c; p.B = B; p.T = T; p.sub = sub; p.n_sub = T / sub;
+    p.spc = kLoudMaxSubs; p.n_chunks = (p.n_sub + p.spc - 1) / p.spc;
+    k_weighting((double)pl->sr, p.sos);
+    // warm-up: slowest pole of the two sections (the high-pass has a near-double real pole: n r^n, hence the margin)
+    double r = 0.0;
+    for (int i = 0; i < 2; ++i) {
+        const double a1 = p.sos[i][3], a2 = p.sos[i][4], disc = a1 * a1 - 4.0 * a2;
+        r = std::max(r, disc < 0.0 ? std::sqrt(a2) : (std::fabs(a1) + std::sqrt(disc)) / 2.0);
+    }
+    const double need = 1.25 * std::log(1e-13) / std::log(std::min(r, 0.999999));
+    p.warm = ((int)std::ceil(need) + kAugBlock - 1) / kAugBlock * kAugBlock;
+    const size_t bytes = sizeof(double) * (size_t)B * kLoudSignals * 2 * p.n_sub;
+    int rc = ensure_workspace(pl, bytes, stream);
+    if (rc) return rc;
+    p.sub_energy = reinterpret_cast<double*>(pl->ws);
+    p.out = out;
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_LOUDNESS, stream);
+        k7_kweight_energy<<<dim3(p.n_chunks, 2, B), kLoudSignals * 32, 0, stream>>>(p);
+        k7_gate<<<B, kLoudSignals * 32, 0, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 2;
+    return MIXFE_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -536,6 +596,11 @@ int mixfe_logmel_backward(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STE
                           void* cuda_stream) {
     return run_logmel_backward(pl, stems, stride_b, stride_c, B, T, grad_logmel, grad_logmel_stride_b, grad_stems,
                                grad_stride_b, grad_stride_c, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_gated_loudness(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,
+                         int B, int T, float* lufs, void* cuda_stream) {
+    return run_gated_loudness(pl, stems, stride_b, stride_c, B, T, lufs, static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_debug_mel_power(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,

@@ -114,6 +114,20 @@ class MixingFeatureExtractor:
         MelSpectrogramPreprocessor output (src/model.py:41-67) for the same (n_fft, hop, n_mels)."""
         return self._run(stems_dict, True, True)
 
+    def gated_loudness(self, stems_dict):
+        """EXTENSION (not in the reference): ITU-R BS.1770-4 integrated loudness --
+        K-weighted, gated -- of the four stems and of their mixture, (5,) or (B,5) in LUFS, order vocals, bass,
+        drums, other, mixture.  The reference's own loudness (un-weighted, un-gated, src/mixing_utils.py:311-318)
+        stays what the feature vector holds."""
+        first = stems_dict[STEMS[0]]
+        src_device = first.device
+        device = _resolve_device(first, None)
+        stems, batched = _gather_stems(stems_dict, device)
+        out = self._plan(device).gated_loudness(stems)
+        if not batched:
+            out = out[0]
+        return out if out.device == src_device else out.to(src_device)
+
     def feature_names(self) -> List[str]:
         """Names of the D entries in the reference's sorted-key order (src/mixing_utils.py:320-357)."""
         if self.use_detailed_spectral:

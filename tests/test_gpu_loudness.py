@@ -1,0 +1,57 @@
+"""GPU: K7 (K-weighted, gated loudness; extension, parity unpinned by the reference) against the BS.1770-4 oracle.
+Tolerance 1e-3 LU (fp32 output of an fp64 pipeline; the oracle's scipy sosfilt is the same DF2T arithmetic)."""
+import numpy as np
+import pytest
+import torch
+
+import mixing_style_transfer_b200 as pkg
+from oracle import bs1770 as B
+from oracle import mixfe_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("T", [17640, 44100, 100001, 441000])
+def test_gated_loudness_vs_oracle(cuda_device, T):
+    clip = O.musical_clip(T % 97, T)
+    clip["bass"] = clip["bass"] * 0.05                       # spread the levels
+    half = T // 2
+    clip["drums"] = torch.cat([clip["drums"][:, :half], clip["drums"][:, half:] * 1e-3], dim=1)   # relative gate bites
+    fe = pkg.MixingFeatureExtractor()
+    n0 = pkg.launch_count()
+    got = fe.gated_loudness({n: v.to(cuda_device) for n, v in clip.items()})
+    assert pkg.launch_count() == n0 + 2
+    assert got.shape == (5,) and got.dtype == torch.float32
+    ref = B.stems_gated_loudness({n: v.numpy() for n, v in clip.items()}, 44100)
+    assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 1e-3, (got.cpu().numpy(), ref)
+
+
+def test_batched_equals_per_clip_and_silence_is_minus_inf(cuda_device):
+    fe = pkg.MixingFeatureExtractor()
+    T = 60000
+    clips = [O.musical_clip(30 + i, T) for i in range(3)]
+    clips[1]["other"] = torch.zeros(2, T)
+    batch = {n: torch.stack([c[n] for c in clips]).to(cuda_device) for n in O.STEMS}
+    got = fe.gated_loudness(batch)
+    assert got.shape == (3, 5)
+    assert got[1, 3] == float("-inf")
+    for i, c in enumerate(clips):
+        one = fe.gated_loudness({n: v.to(cuda_device) for n, v in c.items()})
+        assert torch.equal(one, got[i])
+    again = fe.gated_loudness(batch)
+    assert torch.equal(again, got)                            # fixed-order reductions
+
+
+def test_too_short_raises(cuda_device):
+    fe = pkg.MixingFeatureExtractor()
+    with pytest.raises(ValueError, match="block size"):
+        fe.gated_loudness({n: torch.zeros(2, 17639, device=cuda_device) for n in O.STEMS})
+
+
+def test_other_sample_rate(cuda_device):
+    fs, T = 48000, 96000
+    fe = pkg.MixingFeatureExtractor(sample_rate=fs)
+    clip = O.musical_clip(3, T, sample_rate=fs)
+    got = fe.gated_loudness({n: v.to(cuda_device) for n, v in clip.items()})
+    ref = B.stems_gated_loudness({n: v.numpy() for n, v in clip.items()}, fs)
+    assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 1e-3
