@@ -106,6 +106,23 @@ int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
 int mixfe_gated_loudness(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                          long long stride_b, long long stride_c, int B, int T, float* lufs, void* cuda_stream);
 
+/* Replaces ONE resolution of MultiResolutionSTFTLoss.forward (src/loss.py:332-448; the cycle loss of
+ * src/train_style_transfer.py:239) and its autograd.  The plan's (n_fft, hop) is the resolution (win = n_fft, periodic
+ * Hann, center=True, reflect).  x (prediction), y (target): device fp32, element (b, c, t) at
+ * x[b*x_stride_b + c*x_stride_c + t].
+ *   forward : state (device, 8 doubles) <- { sum (|Y|-|X|)^2, sum |Y|^2, sum |log(|X|+1e-5) - log(|Y|+1e-5)|,
+ *             spectral convergence (:395), log-magnitude L1 (:408), and the two gradient factors, element count }.
+ *             The resolution's loss is state[3] + state[4]; the module averages over resolutions (:444).
+ *   backward: ADDS grad_scale[0] * d(state[3] + state[4]) / dx into grad_x (zero-initialised by the caller);
+ *             grad_scale is a device scalar = upstream gradient / number of resolutions; `state` is the forward's. */
+int mixfe_stft_loss_forward(mixfe_plan* plan, const float* x, const float* y, int B, int C, int T,
+                            long long x_stride_b, long long x_stride_c, long long y_stride_b, long long y_stride_c,
+                            double* state, void* cuda_stream);
+int mixfe_stft_loss_backward(mixfe_plan* plan, const float* x, const float* y, int B, int C, int T,
+                             long long x_stride_b, long long x_stride_c, long long y_stride_b, long long y_stride_c,
+                             const double* state, const float* grad_scale, float* grad_x,
+                             long long g_stride_b, long long g_stride_c, void* cuda_stream);
+
 /* Test hook: mel POWER (before the log) for every channel, same addressing as logmel. */
 int mixfe_debug_mel_power(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                           long long stride_b, long long stride_c, int B, int T,
@@ -137,7 +154,8 @@ long long mixfe_launch_count(void);
 #define MIXFE_KERNEL_REVERB 3     /* K4/K5: FFT-domain reverb + redistribution (all its launches) */
 #define MIXFE_KERNEL_LOGMEL_BWD 4 /* K6: backward of the log-mel */
 #define MIXFE_KERNEL_LOUDNESS 5   /* K7: K-weighting scan + sub-block energies + gating */
-#define MIXFE_NUM_KERNELS 6
+#define MIXFE_KERNEL_STFT_LOSS 6  /* K8: STFT-loss partials / finish / backward */
+#define MIXFE_NUM_KERNELS 7
 int mixfe_plan_enable_timing(mixfe_plan* plan, int enable);
 int mixfe_plan_kernel_time(mixfe_plan* plan, int which, double* total_ms, long long* launches);
 

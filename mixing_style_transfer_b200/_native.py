@@ -73,7 +73,8 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
-           "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness")
+           "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness",
+           "mixfe_stft_loss_forward", "mixfe_stft_loss_backward")
 
 
 def lib() -> ctypes.CDLL:
@@ -109,6 +110,8 @@ def lib() -> ctypes.CDLL:
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
         L.mixfe_gated_loudness.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
+        L.mixfe_stft_loss_forward.argtypes = [vp, vp, vp, ci, ci, ci, ll, ll, ll, ll, vp, vp]
+        L.mixfe_stft_loss_backward.argtypes = [vp, vp, vp, ci, ci, ci, ll, ll, ll, ll, vp, vp, vp, ll, ll, vp]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
@@ -245,6 +248,33 @@ class Plan:
                                                outs[0].stride(0), outs[0].stride(1), _stream(self.device)))
         return outs
 
+    @staticmethod
+    def _bct(t: torch.Tensor) -> torch.Tensor:
+        if t.dtype != torch.float32:
+            t = t.float()
+        return t if t.stride(2) == 1 else t.contiguous()
+
+    def stft_loss_forward(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One resolution (this plan's n_fft, hop) of the STFT loss on (B,C,T) CUDA tensors -> state (8 doubles on the
+        device): [3] spectral convergence, [4] log-magnitude L1 (kernel K8)."""
+        x, y = self._bct(x), self._bct(y)
+        B, C, T = x.shape
+        state = torch.empty(8, dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_stft_loss_forward(self._h, _ptr(x), _ptr(y), B, C, T, x.stride(0), x.stride(1), y.stride(0),
+                                                 y.stride(1), _ptr(state), _stream(self.device)))
+        return state
+
+    def stft_loss_backward(self, x: torch.Tensor, y: torch.Tensor, state: torch.Tensor, grad_scale: torch.Tensor,
+                           grad_x: torch.Tensor) -> None:
+        """Adds grad_scale * d(sc + lm)/dx of this resolution into grad_x ((B,C,T) fp32, contiguous in T)."""
+        x, y = self._bct(x), self._bct(y)
+        B, C, T = x.shape
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_stft_loss_backward(self._h, _ptr(x), _ptr(y), B, C, T, x.stride(0), x.stride(1), y.stride(0),
+                                                  y.stride(1), _ptr(state), _ptr(grad_scale), _ptr(grad_x), grad_x.stride(0),
+                                                  grad_x.stride(1), _stream(self.device)))
+
     def gated_loudness(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
         """(B,5) BS.1770-4 integrated loudness [vocals, bass, drums, other, mixture] in LUFS (kernel K7; extension)."""
         st, sb, sc = unify_stems(stems)
@@ -291,7 +321,7 @@ class Plan:
                                        _stream(self.device)))
         return outs
 
-    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5}
+    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5, "stft_loss": 6}
 
     def reserve_sms(self, n: int) -> None:
         """Leave n SMs out of K1's persistent grid (so a collective can run beside it); 0 = full grid."""

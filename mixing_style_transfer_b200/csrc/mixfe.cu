@@ -16,6 +16,7 @@
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
 #include "k7_loudness.cuh"
+#include "k8_mrstft.cuh"
 
 using namespace mixfe;
 
@@ -444,6 +445,89 @@ int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long st
     return MIXFE_OK;
 }
 
+int stft_loss_common(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long xs_b, long long xs_c,
+                     long long ys_b, long long ys_c, K8Params& p) {
+    if (!pl || !x || !y) return fail(MIXFE_EINVAL, "null plan, x or y");
+    if (B < 0 || C <= 0 || T < 0) return fail(MIXFE_EINVAL, "bad B, C or T");
+    if (T <= pl->n_fft / 2)
+        return fail(MIXFE_ESHORT, "Argument #4: Padding size should be less than the corresponding input dimension, "
+                                  "but got: padding (%d, %d) at dimension 2 of input of length %d",
+                    pl->n_fft / 2, pl->n_fft / 2, T);
+    if (xs_c < T || ys_c < T) return fail(MIXFE_EINVAL, "channel strides smaller than T");
+    if ((long long)B * C > 65535) return fail(MIXFE_EUNSUPPORTED, "STFT loss: B*C=%lld > 65535 rows per call", (long long)B * C);
+    p = K8Params{};
+    p.x = x; p.y = y; p.xs_b = xs_b; p.xs_c = xs_c; p.ys_b = ys_b; p.ys_c = ys_c;
+    p.rows = B * C; p.C = C; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_fft = pl->n_fft; p.log2n = pl->g_log2n;
+    p.n_tiles = (p.F + kTF - 1) / kTF; p.span = (kTF - 1) * pl->hop + pl->n_fft;
+    p.twg = pl->d_twg; p.win = pl->d_win;
+    return MIXFE_OK;
+}
+
+int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long xs_b, long long xs_c,
+                          long long ys_b, long long ys_c, double* state, cudaStream_t stream) {
+    K8Params p;
+    int rc = stft_loss_common(pl, x, y, B, C, T, xs_b, xs_c, ys_b, ys_c, p);
+    if (rc) return rc;
+    if (!state) return fail(MIXFE_EINVAL, "state is NULL");
+    if (B == 0) return fail(MIXFE_EINVAL, "empty batch");
+    DeviceGuard guard(pl->device);
+    int nf = kTF;
+    while (nf > 1 && nf * pl->n_fft * 8 > 72 * 1024) nf >>= 1;
+    p.nf = nf;
+    p.off_red = nf * pl->n_fft * 8;
+    const int smem = p.off_red + 8 * 3 * 4;
+    if (!pl->k8_attr_done) {
+        MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        MIXFE_CUDA(cudaFuncSetAttribute(k8_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        pl->k8_attr_done = true;
+    }
+    rc = ensure_workspace(pl, sizeof(float) * 3 * (size_t)p.rows * p.n_tiles, stream);
+    if (rc) return rc;
+    p.part = reinterpret_cast<float*>(pl->ws);
+    p.state = state;
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+        k8_partials<<<dim3(p.n_tiles, p.rows), kGThreads, smem, stream>>>(p);
+        k8_finish<<<1, 256, 0, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 2;
+    return MIXFE_OK;
+}
+
+int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long xs_b, long long xs_c,
+                           long long ys_b, long long ys_c, const double* state, const float* gscale, float* gx,
+                           long long gs_b, long long gs_c, cudaStream_t stream) {
+    K8Params p;
+    int rc = stft_loss_common(pl, x, y, B, C, T, xs_b, xs_c, ys_b, ys_c, p);
+    if (rc) return rc;
+    if (!state || !gscale || !gx) return fail(MIXFE_EINVAL, "state, gscale or gx is NULL");
+    if (gs_c < T) return fail(MIXFE_EINVAL, "gradient channel stride smaller than T");
+    if (B == 0) return MIXFE_OK;
+    DeviceGuard guard(pl->device);
+    const int nb = pl->n_fft / 2 + 1, per = pl->n_fft * 8 + nb * 8, ola = align16(p.span * 4);
+    if (per + ola > 200 * 1024) return fail(MIXFE_EUNSUPPORTED, "STFT loss backward: hop=%d needs too much shared memory", pl->hop);
+    int nf = kTF;
+    while (nf > 1 && nf * per + ola > 64 * 1024) nf >>= 1;
+    p.nf = nf;
+    p.off_U = nf * pl->n_fft * 8;
+    p.off_ola = align16(p.off_U + nf * nb * 8);
+    const int smem = p.off_ola + ola;
+    if (!pl->k8_attr_done) {
+        MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        MIXFE_CUDA(cudaFuncSetAttribute(k8_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        pl->k8_attr_done = true;
+    }
+    p.state = const_cast<double*>(state); p.gscale = gscale; p.gx = gx; p.gs_b = gs_b; p.gs_c = gs_c;
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+        k8_backward<<<dim3(p.n_tiles, p.rows), kGThreads, smem, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter()++;
+    return MIXFE_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -601,6 +685,20 @@ int mixfe_logmel_backward(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STE
 int mixfe_gated_loudness(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,
                          int B, int T, float* lufs, void* cuda_stream) {
     return run_gated_loudness(pl, stems, stride_b, stride_c, B, T, lufs, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long x_stride_b,
+                            long long x_stride_c, long long y_stride_b, long long y_stride_c, double* state, void* cuda_stream) {
+    return run_stft_loss_forward(pl, x, y, B, C, T, x_stride_b, x_stride_c, y_stride_b, y_stride_c, state,
+                                 static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long x_stride_b,
+                             long long x_stride_c, long long y_stride_b, long long y_stride_c, const double* state,
+                             const float* grad_scale, float* grad_x, long long g_stride_b, long long g_stride_c,
+                             void* cuda_stream) {
+    return run_stft_loss_backward(pl, x, y, B, C, T, x_stride_b, x_stride_c, y_stride_b, y_stride_c, state, grad_scale, grad_x,
+                                  g_stride_b, g_stride_c, static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_debug_mel_power(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,

@@ -41,6 +41,7 @@ struct mixfe_plan {
     void* aug_params_host = nullptr;    // pinned staging buffer for them
     size_t aug_params_cap = 0;
     // optional per-kernel timing (bench.py): event pairs recorded around launches, drained on query
+    bool k8_attr_done = false;          // dynamic shared-memory opt-in of the STFT-loss kernels
     bool k4_attr_done = false;          // dynamic shared-memory opt-in of the reverb kernels
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[MIXFE_NUM_KERNELS];
