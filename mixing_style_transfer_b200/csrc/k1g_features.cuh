@@ -33,23 +33,30 @@ struct K1GParams {
     const int* mel_len;              // [n_mels] bins in the support
     const int* mel_off;              // [n_mels] offset of the filter's weights in mel_w
     const float* mel_w;
-    int pw_stride;                   // float2 entries per frame of the power column (n_fft/2 + 1, padded to odd)
+    int pw_stride;                   // float2 entries per frame of the padded power column (odd)
     int off_pw, off_mel, off_S, off_red;
 };
+
+// idx / d for 0 <= idx and idx * d < 2^32, d >= 2, with magic = 0xFFFFFFFF / d + 1 (one multiply-high instead of the
+// ~20-instruction runtime division).
+__device__ __forceinline__ unsigned k1g_magic(int d) { return 0xFFFFFFFFu / (unsigned)d + 1u; }
+__device__ __forceinline__ int k1g_div(int idx, unsigned magic) { return (int)__umulhi((unsigned)idx, magic); }
 
 __device__ __forceinline__ float2 cmulf(float2 a, float2 w) {
     return make_float2(fmaf(a.x, w.x, -a.y * w.y), fmaf(a.x, w.y, a.y * w.x));
 }
 
 // One radix-4 DIF pass = the two radix-2 stages with half-sizes h and h/2, on `frames` rows of n points.
+// n and h are powers of two: all index arithmetic is shifts and masks.
 __device__ __forceinline__ void k1g_pass4(float2* z, const float2* __restrict__ tw, int n, int frames, int h, int tid) {
-    const int hh = h >> 1, s = n / (2 * h), quarter = n >> 2;
-    for (int idx = tid; idx < frames * quarter; idx += kGThreads) {
-        const int f = idx / quarter, q = idx - f * quarter;
-        const int g = q / hh, j = q - g * hh;
-        float2* r = z + (size_t)f * n + g * 2 * h + j;
+    const int hh = h >> 1, lq = 31 - __clz(n) - 2, lhh = 31 - __clz(hh), ls = lq + 1 - lhh - 1;   // s = n / (2 h) = 2^ls
+    const int total = frames << lq;
+    for (int idx = tid; idx < total; idx += kGThreads) {
+        const int f = idx >> lq, q = idx & ((1 << lq) - 1);
+        const int g = q >> lhh, j = q & (hh - 1);
+        float2* r = z + ((size_t)f << (lq + 2)) + ((g << lhh) << 2) + j;         // f * n + g * 2h + j, 2h = 4 hh
         const float2 a = r[0], b = r[hh], c = r[h], d = r[h + hh];
-        const float2 w1 = __ldg(tw + j * s), w2 = __ldg(tw + 2 * j * s);
+        const float2 w1 = __ldg(tw + (j << ls)), w2 = __ldg(tw + (j << (ls + 1)));
         const float2 a1 = make_float2(a.x + c.x, a.y + c.y);
         const float2 b1 = make_float2(b.x + d.x, b.y + d.y);
         const float2 c1 = cmulf(make_float2(a.x - c.x, a.y - c.y), w1);
@@ -85,6 +92,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
     const int n = g.n_fft, half = n >> 1;
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
+    const unsigned mg_nb = k1g_magic(half + 1), mg_mp = k1g_magic(p.n_mels_pad);
 
     if (p.want_stats) {
         k1_time_stats(p, b, tile, tid);
@@ -97,7 +105,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
             const int frames = nvalid - f0 < g.nf ? (nvalid - f0 > 0 ? nvalid - f0 : 0) : g.nf;
             // ---- load + window ------------------------------------------------------------------
             for (int idx = tid; idx < frames * n; idx += kGThreads) {
-                const int f = idx / n, i = idx - f * n;
+                const int f = idx >> g.log2n, i = idx & (n - 1);
                 long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
                 if (j < 0) j = -j;                               // torch 'reflect'
                 if (j >= p.T) j = 2ll * (p.T - 1) - j;
@@ -116,26 +124,30 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
                 __syncthreads();
             }
             // ---- untangle L / R, power ------------------------------------------------------------
-            const int sh = 32 - g.log2n;
+            // Lane i takes bin k = bitrev_{log2n-1}(i): X[k] then sits at position 2 i and X[n-k] at an odd position
+            // walking the other way, so a warp reads neighbouring words instead of 32 words of one bank.  The power
+            // column is padded (k + (k >> pad_sh)) so that the scattered k of a warp fall into different banks.
+            const int sh = 32 - g.log2n, pad_sh = g.log2n > 6 ? g.log2n - 6 : 31;
             for (int idx = tid; idx < frames * (half + 1); idx += kGThreads) {
-                const int f = idx / (half + 1), k = idx - f * (half + 1);
+                const int f = k1g_div(idx, mg_nb), i = idx - f * (half + 1);
+                const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
                 const float2 x = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
                 const float2 y = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
                 const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
-                pw[(size_t)f * g.pw_stride + k] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
+                pw[(size_t)f * g.pw_stride + k + (k >> pad_sh)] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
             }
             __syncthreads();
             // ---- mel projection -------------------------------------------------------------------
             for (int idx = tid; idx < g.nf * p.n_mels_pad; idx += kGThreads) {
-                const int f = idx / p.n_mels_pad, m = idx - f * p.n_mels_pad;
+                const int f = k1g_div(idx, mg_mp), m = idx - f * p.n_mels_pad;
                 float aL = 0.0f, aR = 0.0f;
                 if (f < frames && m < p.n_mels) {
                     const int lo = __ldg(g.mel_lo + m), len = __ldg(g.mel_len + m);
                     const float* w = g.mel_w + __ldg(g.mel_off + m);
-                    const float2* src = pw + (size_t)f * g.pw_stride + lo;
+                    const float2* src = pw + (size_t)f * g.pw_stride;
                     for (int i = 0; i < len; ++i) {
                         const float wi = __ldg(w + i);
-                        const float2 v = src[i];
+                        const float2 v = src[lo + i + ((lo + i) >> pad_sh)];
                         aL = fmaf(wi, v.x, aL);
                         aR = fmaf(wi, v.y, aR);
                     }
@@ -176,7 +188,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
     if (p.want_stats) {
         float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};
         for (int idx = tid; idx < kTF * p.n_mels_pad; idx += kGThreads) {
-            const int t = idx / p.n_mels_pad, m = idx - t * p.n_mels_pad;
+            const int t = k1g_div(idx, mg_mp), m = idx - t * p.n_mels_pad;
             if (t < nvalid && m < p.n_mels) {
                 const float s0 = S[idx], s1 = S[kTF * p.n_mels_pad + idx], s2 = S[2 * kTF * p.n_mels_pad + idx],
                             s3 = S[3 * kTF * p.n_mels_pad + idx];

@@ -31,8 +31,10 @@ struct K6Params {
     const float* g;                  // d loss / d logmel: (b, ch, m, f) at g[b * g_stride_b + (ch * n_mels + m) * F + f]
     long long g_stride_b;
     int B, T, F, hop, n_mels, n_mels_pad, n_fft, log2n, nf, span;
+    int span_pad;                    // floats per channel of the padded overlap-add span
     const float2* twg;               // [n_fft/2]
     const float* win;                // [n_fft] 0.5 * periodic hann
+    const float* win_br;             // the same, bit-reversed: win_br[p] = win[bitrev(p)]
     const int* mel_lo;               // filterbank by filter (CSR): first bin, bins, weight offset
     const int* mel_len;
     const int* mel_off;
@@ -41,17 +43,17 @@ struct K6Params {
     const int* bin_len;
     const int* bin_off;
     const float* bin_w;
-    int pw_stride;
+    int pw_stride;                   // entries per frame of U and of the power column (both padded: k + (k >> pad_sh))
     int off_U, off_pw, off_mel, off_ola;
 };
 
 __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant__ K6Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
-    float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][n/2+1] (L.re, L.im, R.re, R.im)
+    float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][pw_stride] (L.re, L.im, R.re, R.im)
     float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power, then dP
     float2* const melb = reinterpret_cast<float2*>(smem + p.off_mel);        // [nf][n_mels_pad] dmel
-    float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [2][span]
+    float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [2][span_pad]
 
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, b = blockIdx.y, s = blockIdx.z;
@@ -59,16 +61,18 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const int sh = 32 - p.log2n;
+    const unsigned mg_nb = k1g_magic(nb), mg_mp = k1g_magic(p.n_mels_pad);
+    const int pad_sh = p.log2n > 6 ? p.log2n - 6 : 31, ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
     const float* gL = p.stem[s] + (long long)b * p.stride_b;
     const float* gR = gL + p.stride_c;
 
-    for (int i = tid; i < 2 * p.span; i += kGThreads) ola[i] = 0.0f;
+    for (int i = tid; i < 2 * p.span_pad; i += kGThreads) ola[i] = 0.0f;
 
     for (int f0 = 0; f0 < nvalid; f0 += p.nf) {
         const int frames = nvalid - f0 < p.nf ? nvalid - f0 : p.nf;
         // ---- forward: load + window, FFT, untangle ------------------------------------------------
         for (int idx = tid; idx < frames * n; idx += kGThreads) {
-            const int f = idx / n, i = idx - f * n;
+            const int f = idx >> p.log2n, i = idx & (n - 1);
             long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
             if (j < 0) j = -j;
             if (j >= p.T) j = 2ll * (p.T - 1) - j;
@@ -86,26 +90,29 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
             __syncthreads();
         }
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
+            // lane i takes bin k = bitrev_{log2n-1}(i) (k1g_features' untangle); U and the power column are padded
+            const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
+            const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
             const float2 x = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
             const float2 y = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
             const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
-            U[(size_t)f * nb + k] = make_float4(a, bb, d, -c);               // L = a + i bb, R = d - i c
-            pw[(size_t)f * p.pw_stride + k] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
+            const size_t o = (size_t)f * p.pw_stride + k + (k >> pad_sh);
+            U[o] = make_float4(a, bb, d, -c);                                // L = a + i bb, R = d - i c
+            pw[o] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
         }
         __syncthreads();
         // ---- mel, then dmel = g / (mel + 1e-10) ---------------------------------------------------
         for (int idx = tid; idx < frames * p.n_mels_pad; idx += kGThreads) {
-            const int f = idx / p.n_mels_pad, m = idx - f * p.n_mels_pad;
+            const int f = k1g_div(idx, mg_mp), m = idx - f * p.n_mels_pad;
             float dL = 0.0f, dR = 0.0f;
             if (m < p.n_mels) {
                 const int lo = __ldg(p.mel_lo + m), len = __ldg(p.mel_len + m);
                 const float* w = p.mel_w + __ldg(p.mel_off + m);
-                const float2* src = pw + (size_t)f * p.pw_stride + lo;
+                const float2* src = pw + (size_t)f * p.pw_stride;
                 float aL = 0.0f, aR = 0.0f;
                 for (int i = 0; i < len; ++i) {
                     const float wi = __ldg(w + i);
-                    const float2 v = src[i];
+                    const float2 v = src[lo + i + ((lo + i) >> pad_sh)];
                     aL = fmaf(wi, v.x, aL);
                     aR = fmaf(wi, v.y, aR);
                 }
@@ -118,7 +125,7 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
         __syncthreads();
         // ---- dP[k] = sum_m fb[k][m] dmel[m] (overwrites the power column) ----------------------------
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
+            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
             const int lo = __ldg(p.bin_lo + k), len = __ldg(p.bin_len + k);
             const float* w = p.bin_w + __ldg(p.bin_off + k);
             const float2* src = melb + (size_t)f * p.n_mels_pad + lo;
@@ -129,14 +136,14 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
                 aL = fmaf(wi, v.x, aL);
                 aR = fmaf(wi, v.y, aR);
             }
-            pw[(size_t)f * p.pw_stride + k] = make_float2(aL, aR);
+            pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)] = make_float2(aL, aR);
         }
         __syncthreads();
         // ---- conj(Y) in natural order: G = 2 X dP, Hermitian extension, L + iR packing ------------------
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
-            const float4 u = U[(size_t)f * nb + k];
-            const float2 dp = pw[(size_t)f * p.pw_stride + k];
+            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
+            const float4 u = U[(size_t)f * p.pw_stride + k + (k >> pad_sh)];
+            const float2 dp = pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)];
             const float a = 2.0f * u.x * dp.x, bi = 2.0f * u.y * dp.x;       // G_L = a + i bi
             const float c = 2.0f * u.z * dp.y, di = 2.0f * u.w * dp.y;       // G_R = c + i di
             float2* zf = z + (size_t)f * n;
@@ -159,14 +166,18 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
             __syncthreads();
         }
         // ---- window and overlap-add, one frame after the other (frames overlap) ------------------------
+        // A thread walks the positions of the bit-reversed result (neighbouring words of z, the window read from its
+        // bit-reversed copy) and adds at sample i = bitrev(position); the span is padded (q + (q >> ola_sh)) so that
+        // the 32 samples of a warp, n/32 apart, fall into 32 banks.
         for (int f = 0; f < frames; ++f) {
-            float* oL = ola + (f0 + f) * p.hop;
-            float* oR = oL + p.span;
-            for (int i = tid; i < n; i += kGThreads) {
-                const float2 r = z[(size_t)f * n + (__brev((unsigned)i) >> sh)];
-                const float w = 2.0f * __ldg(p.win + i);
-                oL[i] = fmaf(w, r.x, oL[i]);
-                oR[i] = fmaf(-w, r.y, oR[i]);
+            const int q0 = (f0 + f) * p.hop;
+            for (int pos = tid; pos < n; pos += kGThreads) {
+                const float2 r = z[(size_t)f * n + pos];
+                const float w = 2.0f * __ldg(p.win_br + pos);
+                const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
+                const int o = q + (q >> ola_sh);
+                ola[o] = fmaf(w, r.x, ola[o]);
+                ola[p.span_pad + o] = fmaf(-w, r.y, ola[p.span_pad + o]);
             }
             __syncthreads();
         }
@@ -180,8 +191,9 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
         long long j = (long long)t0 * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
-        atomicAdd(dLp + j, ola[i]);
-        atomicAdd(dRp + j, ola[p.span + i]);
+        const int o = i + (i >> ola_sh);
+        atomicAdd(dLp + j, ola[o]);
+        atomicAdd(dRp + j, ola[p.span_pad + o]);
     }
 }
 

@@ -35,6 +35,8 @@ struct K8Params {
     const float* gscale;             // device scalar: upstream gradient / n_resolutions   (backward)
     float* gx;                       // gradient of x, zero-initialised by the caller, addressing gs_b, gs_c (backward)
     long long gs_b, gs_c;
+    int u_stride, span_pad;          // padded row of U (k + (k >> pad_sh)), padded overlap-add span (q + (q >> ola_sh))
+    const float* win_br;             // window in bit-reversed order
     int off_U, off_ola, off_red;
 };
 
@@ -42,7 +44,7 @@ __device__ __forceinline__ void k8_load_fft(const K8Params& p, float2* z, const 
                                             int frames, int tid) {
     const int n = p.n_fft, half = n >> 1;
     for (int idx = tid; idx < frames * n; idx += kGThreads) {
-        const int f = idx / n, i = idx - f * n;
+        const int f = idx >> p.log2n, i = idx & (n - 1);
         long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
@@ -68,6 +70,7 @@ __global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x, row = blockIdx.y;
     const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n;
+    const unsigned mg_nb = k1g_magic(nb);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const float* xr = p.x + (long long)(row / p.C) * p.xs_b + (long long)(row % p.C) * p.xs_c;
@@ -77,7 +80,9 @@ __global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__
         const int frames = nvalid - f0 < p.nf ? nvalid - f0 : p.nf;
         k8_load_fft(p, z, xr, yr, t0, f0, frames, tid);
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
+            // lane i takes bin k = bitrev_{log2n-1}(i): neighbouring words of z instead of one bank (k1g_features)
+            const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
+            const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
             const float2 u = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
             const float2 v = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
             const float a = u.x + v.x, bb = u.y - v.y, c = u.x - v.x, d = u.y + v.y;   // X = a + i bb, Y = d - i c
@@ -134,24 +139,27 @@ __global__ void __launch_bounds__(256) k8_finish(const K8Params p) {
 __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__ K8Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
-    float2* const U = reinterpret_cast<float2*>(smem + p.off_U);             // [nf][n/2+1] G = d loss / d X
-    float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [span]
+    float2* const U = reinterpret_cast<float2*>(smem + p.off_U);             // [nf][u_stride] G = d loss / d X
+    float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [span_pad]
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, row = blockIdx.y;
     const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n;
+    const unsigned mg_nb = k1g_magic(nb);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const float* xr = p.x + (long long)(row / p.C) * p.xs_b + (long long)(row % p.C) * p.xs_c;
     const float* yr = p.y + (long long)(row / p.C) * p.ys_b + (long long)(row % p.C) * p.ys_c;
+    const int pad_sh = p.log2n > 6 ? p.log2n - 6 : 31, ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
     const float gs = __ldg(p.gscale);
     const float alpha = (float)p.state[5] * gs, beta = (float)p.state[6] * gs;
 
-    for (int i = tid; i < p.span; i += kGThreads) ola[i] = 0.0f;
+    for (int i = tid; i < p.span_pad; i += kGThreads) ola[i] = 0.0f;
     for (int f0 = 0; f0 < nvalid; f0 += p.nf) {
         const int frames = nvalid - f0 < p.nf ? nvalid - f0 : p.nf;
         k8_load_fft(p, z, xr, yr, t0, f0, frames, tid);
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
+            const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
+            const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
             const float2 u = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
             const float2 v = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
             const float a = u.x + v.x, bb = u.y - v.y, c = u.x - v.x, d = u.y + v.y;   // X = a + i bb, Y = d - i c
@@ -160,13 +168,13 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
             const float sg = dl > 0.0f ? 1.0f : (dl < 0.0f ? -1.0f : 0.0f);
             const float gm = fmaf(alpha, mx - my, beta * sg / (mx + 1e-5f));            // d loss / d |X|
             const float inv = mx > 0.0f ? gm / mx : 0.0f;
-            U[(size_t)f * nb + k] = make_float2(inv * a, inv * bb);
+            U[(size_t)f * p.u_stride + k + (k >> pad_sh)] = make_float2(inv * a, inv * bb);
         }
         __syncthreads();
         // conj of the Hermitian extension of G, natural order (the imaginary slot of the packed transform stays empty)
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = idx / nb, k = idx - f * nb;
-            const float2 g = U[(size_t)f * nb + k];
+            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
+            const float2 g = U[(size_t)f * p.u_stride + k + (k >> pad_sh)];
             float2* zf = z + (size_t)f * n;
             if (k == 0 || k == half) {
                 zf[k] = make_float2(g.x, 0.0f);
@@ -185,11 +193,14 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
             k1g_pass2_last(z, n, frames, tid);
             __syncthreads();
         }
+        // positions of the bit-reversed result in order, padded span (k6_logmel_bwd's overlap-add)
         for (int f = 0; f < frames; ++f) {
-            float* o = ola + (f0 + f) * p.hop;
-            for (int i = tid; i < n; i += kGThreads) {
-                const float2 r = z[(size_t)f * n + (__brev((unsigned)i) >> sh)];
-                o[i] = fmaf(2.0f * __ldg(p.win + i), r.x, o[i]);
+            const int q0 = (f0 + f) * p.hop;
+            for (int pos = tid; pos < n; pos += kGThreads) {
+                const float2 r = z[(size_t)f * n + pos];
+                const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
+                const int o = q + (q >> ola_sh);
+                ola[o] = fmaf(2.0f * __ldg(p.win_br + pos), r.x, ola[o]);
             }
             __syncthreads();
         }
@@ -201,7 +212,7 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
         long long j = (long long)t0 * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
-        atomicAdd(gr + j, ola[i]);
+        atomicAdd(gr + j, ola[i + (i >> ola_sh)]);
     }
 }
 

@@ -206,7 +206,16 @@ int build_generic_tables(mixfe_plan* pl) {
         return rc;
     pl->g_log2n = 0;
     while ((1 << pl->g_log2n) < n) ++pl->g_log2n;
-    pl->g_pw_stride = (n / 2 + 1) | 1;
+    {
+        std::vector<float> win_br(n);                 // window in the FFT's output order, for the overlap-add loops
+        for (int q = 0; q < n; ++q) {
+            int r = 0;
+            for (int bit = 0; bit < pl->g_log2n; ++bit) r |= ((q >> bit) & 1) << (pl->g_log2n - 1 - bit);
+            win_br[q] = win[r];
+        }
+        if ((rc = upload(&pl->d_win_br, win_br))) return rc;
+    }
+    pl->g_pw_stride = (n / 2 + 1 + (pl->g_log2n > 6 ? (n / 2) >> (pl->g_log2n - 6) : 0)) | 1;   // k + (k >> pad_sh), k <= n/2
     const int per_frame = n * 8 + pl->g_pw_stride * 8;
     int nfr = kTF;
     {
@@ -242,15 +251,16 @@ int build_generic_tables(mixfe_plan* pl) {
             (rc = upload(&pl->d_bin_w, bw)))
             return rc;
         pl->b_span = (kTF - 1) * pl->hop + n;
-        const int per = n * 8 + (n / 2 + 1) * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
-        const int ola = align16(2 * pl->b_span * 4);
+        pl->b_span_pad = pl->b_span + (pl->g_log2n > 5 ? pl->b_span >> (pl->g_log2n - 5) : 0) + 1;
+        const int per = n * 8 + pl->g_pw_stride * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
+        const int ola = align16(2 * pl->b_span_pad * 4);
         int bn = kTF;
         const char* e6 = getenv("MIXFE_K6_SMEM_KB");
         const int budget6 = (e6 ? atoi(e6) : 50) * 1024;
         while (bn > 1 && bn * per + ola + 64 > budget6) bn >>= 1;
         pl->b_nf = bn;
         pl->b_off_U = bn * n * 8;
-        pl->b_off_pw = pl->b_off_U + bn * (n / 2 + 1) * 16;
+        pl->b_off_pw = pl->b_off_U + bn * pl->g_pw_stride * 16;
         pl->b_off_mel = pl->b_off_pw + bn * pl->g_pw_stride * 8;
         pl->b_off_ola = align16(pl->b_off_mel + bn * pl->n_mels_pad * 8);
         pl->smem_b = pl->b_off_ola + ola;
@@ -370,8 +380,8 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
     p.stride_b = stride_b; p.stride_c = stride_c; p.ostride_b = ostride_b; p.ostride_c = ostride_c;
     p.g = grad_logmel; p.g_stride_b = g_stride_b;
     p.B = B; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
-    p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span;
-    p.twg = pl->d_twg; p.win = pl->d_win;
+    p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span; p.span_pad = pl->b_span_pad;
+    p.twg = pl->d_twg; p.win = pl->d_win; p.win_br = pl->d_win_br;
     p.mel_lo = pl->d_mel_lo; p.mel_len = pl->d_mel_len; p.mel_off = pl->d_mel_off; p.mel_w = pl->d_mel_w;
     p.bin_lo = pl->d_bin_lo; p.bin_len = pl->d_bin_len; p.bin_off = pl->d_bin_off; p.bin_w = pl->d_bin_w;
     p.pw_stride = pl->g_pw_stride;
@@ -459,7 +469,9 @@ int stft_loss_common(mixfe_plan* pl, const float* x, const float* y, int B, int 
     p.x = x; p.y = y; p.xs_b = xs_b; p.xs_c = xs_c; p.ys_b = ys_b; p.ys_c = ys_c;
     p.rows = B * C; p.C = C; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_fft = pl->n_fft; p.log2n = pl->g_log2n;
     p.n_tiles = (p.F + kTF - 1) / kTF; p.span = (kTF - 1) * pl->hop + pl->n_fft;
-    p.twg = pl->d_twg; p.win = pl->d_win;
+    p.span_pad = p.span + (pl->g_log2n > 5 ? p.span >> (pl->g_log2n - 5) : 0) + 1;
+    p.u_stride = pl->g_pw_stride;
+    p.twg = pl->d_twg; p.win = pl->d_win; p.win_br = pl->d_win_br;
     return MIXFE_OK;
 }
 
@@ -505,13 +517,13 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     if (gs_c < T) return fail(MIXFE_EINVAL, "gradient channel stride smaller than T");
     if (B == 0) return MIXFE_OK;
     DeviceGuard guard(pl->device);
-    const int nb = pl->n_fft / 2 + 1, per = pl->n_fft * 8 + nb * 8, ola = align16(p.span * 4);
+    const int per = pl->n_fft * 8 + p.u_stride * 8, ola = align16(p.span_pad * 4);
     if (per + ola > 200 * 1024) return fail(MIXFE_EUNSUPPORTED, "STFT loss backward: hop=%d needs too much shared memory", pl->hop);
     int nf = kTF;
     while (nf > 1 && nf * per + ola > 64 * 1024) nf >>= 1;
     p.nf = nf;
     p.off_U = nf * pl->n_fft * 8;
-    p.off_ola = align16(p.off_U + nf * nb * 8);
+    p.off_ola = align16(p.off_U + nf * p.u_stride * 8);
     const int smem = p.off_ola + ola;
     if (!pl->k8_attr_done) {
         MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -594,7 +606,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev); cudaFree(pl->d_sm_ticket);
-    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
+    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_win_br); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_lo); cudaFree(pl->d_bin_len); cudaFree(pl->d_bin_off); cudaFree(pl->d_bin_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
