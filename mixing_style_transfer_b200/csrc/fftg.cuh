@@ -1,0 +1,108 @@
+// Shared-memory FFT of `frames` rows of n complex points, n = 2^log2n in [64, 4096], used by K1G, K6 and K8.
+//
+// Decimation in frequency, in place, result in bit-reversed order (X[k] at position bitrev(k)).  log2n is split into
+// passes of 3 or 4 radix-2 stages; in a pass one thread owns the 2^R points that those stages combine (spacing hs),
+// holds them in registers, and touches shared memory once to read and once to write them: 3 round trips for 512..4096
+// points instead of one per two stages.  The twiddle of stage t for the point at offset j + mm * hs of its half is
+//   exp(-2 pi i (j + mm hs) / (2 h_t)) = tw[j * s * 2^t] * exp(-2 pi i mm 2^t / 2^R):
+// one table read per stage (R per pass) times a compile-time constant (a sixteenth of a turn).
+//
+// Rows are padded by one element per eight, position p at p + (p >> 3) (row stride n + n/8): a thread's points in
+// the last pass are contiguous (spacing 1, 2 or 4), and the threads of a warp, 8 or 16 elements apart, would
+// otherwise all start in the same bank; the padding also separates the blocks of the middle passes.
+#pragma once
+
+#include <cuda_runtime.h>
+
+namespace mixfe {
+
+constexpr int kGThreads = 256;
+
+__device__ __forceinline__ int fg_pad(int p) { return p + (p >> 3); }
+__host__ __device__ __forceinline__ int fg_row(int n) { return n + (n >> 3); }
+
+// idx / d for 0 <= idx and idx * d < 2^32, d >= 2, with magic = 0xFFFFFFFF / d + 1 (one multiply-high instead of the
+// ~20-instruction runtime division).
+__device__ __forceinline__ unsigned k1g_magic(int d) { return 0xFFFFFFFFu / (unsigned)d + 1u; }
+__device__ __forceinline__ int k1g_div(int idx, unsigned magic) { return (int)__umulhi((unsigned)idx, magic); }
+
+__device__ __forceinline__ float2 cmulf(float2 a, float2 w) {
+    return make_float2(fmaf(a.x, w.x, -a.y * w.y), fmaf(a.x, w.y, a.y * w.x));
+}
+
+// d * exp(-2 pi i K / 16), K a compile-time constant after unrolling
+__device__ __forceinline__ float2 fg_mul_w16(float2 d, int K) {
+    constexpr float kC[8] = {1.0f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f,
+                             0.0f, -0.38268343236508977f, -0.70710678118654752f, -0.92387953251128674f};
+    constexpr float kS[8] = {0.0f, 0.38268343236508977f, 0.70710678118654752f, 0.92387953251128674f,
+                             1.0f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f};
+    if (K == 0) return d;
+    if (K == 4) return make_float2(d.y, -d.x);
+    if (K == 2) return make_float2(kC[2] * (d.x + d.y), kC[2] * (d.y - d.x));
+    if (K == 6) return make_float2(kC[2] * (d.y - d.x), -kC[2] * (d.x + d.y));
+    return make_float2(fmaf(d.x, kC[K], d.y * kS[K]), fmaf(d.y, kC[K], -d.x * kS[K]));
+}
+
+// One pass of R stages, the first with half-size h = 2^lh, the last with half-size hs = 2^(lh - R + 1).
+template <int R>
+__device__ __forceinline__ void fg_pass(float2* z, const float2* __restrict__ tw, int log2n, int frames, int lh, int tid) {
+    constexpr int P = 1 << R;
+    const int lhs = lh - (R - 1), hs = 1 << lhs;
+    const int lq = log2n - R;                         // threads per row = n / P
+    const int ls = log2n - 1 - lh;                    // table stride of the first stage, n / (2 h)
+    const int zs = fg_row(1 << log2n);
+    const int total = frames << lq;
+    for (int idx = tid; idx < total; idx += kGThreads) {
+        const int f = idx >> lq, q = idx & ((1 << lq) - 1);
+        const int g = q >> lhs, j = q & (hs - 1);
+        const int base = (g << (lh + 1)) + j;
+        float2* row = z + f * zs;
+        float2 v[P];
+        if (lhs >= 3) {
+            float2* r = row + fg_pad(base);
+            const int sp = hs + (hs >> 3);
+#pragma unroll
+            for (int m = 0; m < P; ++m) v[m] = r[m * sp];
+        } else {
+#pragma unroll
+            for (int m = 0; m < P; ++m) v[m] = row[fg_pad(base + (m << lhs))];
+        }
+#pragma unroll
+        for (int t = 0; t < R; ++t) {
+            const int dm = P >> (t + 1);
+            const float2 wj = __ldg(tw + (j << (ls + t)));
+#pragma unroll
+            for (int a = 0; a < P; ++a) {
+                if (a & dm) continue;
+                const int b = a + dm, mm = a & (dm - 1);
+                const float2 d = make_float2(v[a].x - v[b].x, v[a].y - v[b].y);
+                v[a] = make_float2(v[a].x + v[b].x, v[a].y + v[b].y);
+                v[b] = fg_mul_w16(cmulf(d, wj), (mm << t) * (16 / P));
+            }
+        }
+        if (lhs >= 3) {
+            float2* r = row + fg_pad(base);
+            const int sp = hs + (hs >> 3);
+#pragma unroll
+            for (int m = 0; m < P; ++m) r[m * sp] = v[m];
+        } else {
+#pragma unroll
+            for (int m = 0; m < P; ++m) row[fg_pad(base + (m << lhs))] = v[m];
+        }
+    }
+}
+
+// All passes, a block barrier after each.  Every thread of the block calls this.
+__device__ __forceinline__ void fg_fft(float2* z, const float2* __restrict__ tw, int log2n, int frames, int tid) {
+    const int passes = (log2n + 3) >> 2, base = log2n / passes, extra = log2n - base * passes;
+    int lh = log2n - 1;
+    for (int ps = 0; ps < passes; ++ps) {
+        const int R = base + (ps < extra ? 1 : 0);
+        if (R == 4) fg_pass<4>(z, tw, log2n, frames, lh, tid);
+        else fg_pass<3>(z, tw, log2n, frames, lh, tid);
+        lh -= R;
+        __syncthreads();
+    }
+}
+
+}  // namespace mixfe

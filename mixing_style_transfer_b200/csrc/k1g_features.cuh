@@ -10,19 +10,19 @@
 // Work decomposition.  One CTA (256 threads) per (clip, tile of 8 frames), walking the 4 stems.  Per stem the
 // frames of the tile are transformed `nf` at a time (as many as fit in shared memory):
 //   load    (L, R) sample pairs with torch 'reflect' indexing, times 0.5 * hann, as complex values in smem
-//   FFT     in-place radix-4 decimation-in-frequency passes over shared memory (one radix-2 pass at the end
-//           when log2(n_fft) is odd); X[k] ends at the bit-reversed position
+//   FFT     in-place decimation in frequency over padded shared-memory rows, 3 or 4 stages per pass in registers
+//           (fftg.cuh); X[k] ends at the bit-reversed position
 //   power   L/R untangled from X[k] and X[n-k]; |L_k|^2, |R_k|^2 into a (frame, bin) column
 //   mel     thread (frame, filter) walks the filter's contiguous support (CSR table in global memory)
 // then, per stem, the same epilogue as K1: log(mel + 1e-10), per-(stem, mel) partial sums, the masking S tile,
 // 32-byte-run stores of the log tile.  The per-tile partials have K1's layout, so K2 finalizes both.
 #pragma once
 
+#include "fftg.cuh"
 #include "k1_features.cuh"
 
 namespace mixfe {
 
-constexpr int kGThreads = 256;
 
 struct K1GParams {
     K1Params base;                   // stems, strides, B, T, F, hop, n_mels(_pad), n_tiles, outputs, partials
@@ -37,51 +37,10 @@ struct K1GParams {
     int off_pw, off_mel, off_S, off_red;
 };
 
-// idx / d for 0 <= idx and idx * d < 2^32, d >= 2, with magic = 0xFFFFFFFF / d + 1 (one multiply-high instead of the
-// ~20-instruction runtime division).
-__device__ __forceinline__ unsigned k1g_magic(int d) { return 0xFFFFFFFFu / (unsigned)d + 1u; }
-__device__ __forceinline__ int k1g_div(int idx, unsigned magic) { return (int)__umulhi((unsigned)idx, magic); }
-
-__device__ __forceinline__ float2 cmulf(float2 a, float2 w) {
-    return make_float2(fmaf(a.x, w.x, -a.y * w.y), fmaf(a.x, w.y, a.y * w.x));
-}
-
-// One radix-4 DIF pass = the two radix-2 stages with half-sizes h and h/2, on `frames` rows of n points.
-// n and h are powers of two: all index arithmetic is shifts and masks.
-__device__ __forceinline__ void k1g_pass4(float2* z, const float2* __restrict__ tw, int n, int frames, int h, int tid) {
-    const int hh = h >> 1, lq = 31 - __clz(n) - 2, lhh = 31 - __clz(hh), ls = lq + 1 - lhh - 1;   // s = n / (2 h) = 2^ls
-    const int total = frames << lq;
-    for (int idx = tid; idx < total; idx += kGThreads) {
-        const int f = idx >> lq, q = idx & ((1 << lq) - 1);
-        const int g = q >> lhh, j = q & (hh - 1);
-        float2* r = z + ((size_t)f << (lq + 2)) + ((g << lhh) << 2) + j;         // f * n + g * 2h + j, 2h = 4 hh
-        const float2 a = r[0], b = r[hh], c = r[h], d = r[h + hh];
-        const float2 w1 = __ldg(tw + (j << ls)), w2 = __ldg(tw + (j << (ls + 1)));
-        const float2 a1 = make_float2(a.x + c.x, a.y + c.y);
-        const float2 b1 = make_float2(b.x + d.x, b.y + d.y);
-        const float2 c1 = cmulf(make_float2(a.x - c.x, a.y - c.y), w1);
-        const float2 t = cmulf(make_float2(b.x - d.x, b.y - d.y), w1);
-        const float2 d1 = make_float2(t.y, -t.x);                    // times exp(-2 pi i (n/4) / n) = -i
-        r[0] = make_float2(a1.x + b1.x, a1.y + b1.y);
-        r[hh] = cmulf(make_float2(a1.x - b1.x, a1.y - b1.y), w2);
-        r[h] = make_float2(c1.x + d1.x, c1.y + d1.y);
-        r[h + hh] = cmulf(make_float2(c1.x - d1.x, c1.y - d1.y), w2);
-    }
-}
-
-// Last stage (h = 1) when log2(n) is odd: neighbours, unit twiddle.
-__device__ __forceinline__ void k1g_pass2_last(float2* z, int n, int frames, int tid) {
-    float4* z4 = reinterpret_cast<float4*>(z);
-    for (int idx = tid; idx < frames * (n >> 1); idx += kGThreads) {
-        const float4 v = z4[idx];
-        z4[idx] = make_float4(v.x + v.z, v.y + v.w, v.x - v.z, v.y - v.w);
-    }
-}
-
 __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant__ K1GParams g) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const K1Params& p = g.base;
-    float2* const z = reinterpret_cast<float2*>(smem);                         // [nf][n_fft]
+    float2* const z = reinterpret_cast<float2*>(smem);                         // [nf][fg_row(n_fft)] padded rows
     float2* const pw = reinterpret_cast<float2*>(smem + g.off_pw);             // [nf][pw_stride]
     float2* const melb = reinterpret_cast<float2*>(smem + g.off_mel);          // [8][n_mels_pad] (L, R)
     float* const S = reinterpret_cast<float*>(smem + g.off_S);                 // [4][8][n_mels_pad]
@@ -89,7 +48,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x, b = blockIdx.y;
-    const int n = g.n_fft, half = n >> 1;
+    const int n = g.n_fft, half = n >> 1, zs = fg_row(n);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const unsigned mg_nb = k1g_magic(half + 1), mg_mp = k1g_magic(p.n_mels_pad);
@@ -110,19 +69,11 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
                 if (j < 0) j = -j;                               // torch 'reflect'
                 if (j >= p.T) j = 2ll * (p.T - 1) - j;
                 const float w = __ldg(g.win + i);
-                z[idx] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
+                z[f * zs + fg_pad(i)] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
             }
             __syncthreads();
-            // ---- FFT ----------------------------------------------------------------------------
-            int h = half;
-            for (; h >= 2; h >>= 2) {
-                k1g_pass4(z, g.twg, n, frames, h, tid);
-                __syncthreads();
-            }
-            if (h == 1) {
-                k1g_pass2_last(z, n, frames, tid);
-                __syncthreads();
-            }
+            // ---- FFT (fftg.cuh; ends with a barrier) ----------------------------------------------------
+            fg_fft(z, g.twg, g.log2n, frames, tid);
             // ---- untangle L / R, power ------------------------------------------------------------
             // Lane i takes bin k = bitrev_{log2n-1}(i): X[k] then sits at position 2 i and X[n-k] at an odd position
             // walking the other way, so a warp reads neighbouring words instead of 32 words of one bank.  The power
@@ -131,8 +82,8 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
             for (int idx = tid; idx < frames * (half + 1); idx += kGThreads) {
                 const int f = k1g_div(idx, mg_nb), i = idx - f * (half + 1);
                 const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
-                const float2 x = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
-                const float2 y = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
+                const float2 x = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
+                const float2 y = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
                 const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
                 pw[(size_t)f * g.pw_stride + k + (k >> pad_sh)] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
             }

@@ -49,7 +49,7 @@ struct K6Params {
 
 __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant__ K6Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
+    float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][fg_row(n)] padded rows (fftg.cuh)
     float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][pw_stride] (L.re, L.im, R.re, R.im)
     float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power, then dP
     float2* const melb = reinterpret_cast<float2*>(smem + p.off_mel);        // [nf][n_mels_pad] dmel
@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
 
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, b = blockIdx.y, s = blockIdx.z;
-    const int n = p.n_fft, half = n >> 1, nb = half + 1;
+    const int n = p.n_fft, half = n >> 1, nb = half + 1, zs = fg_row(n);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const int sh = 32 - p.log2n;
@@ -77,24 +77,16 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
             if (j < 0) j = -j;
             if (j >= p.T) j = 2ll * (p.T - 1) - j;
             const float w = __ldg(p.win + i);
-            z[idx] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
+            z[f * zs + fg_pad(i)] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
         }
         __syncthreads();
-        int h = half;
-        for (; h >= 2; h >>= 2) {
-            k1g_pass4(z, p.twg, n, frames, h, tid);
-            __syncthreads();
-        }
-        if (h == 1) {
-            k1g_pass2_last(z, n, frames, tid);
-            __syncthreads();
-        }
+        fg_fft(z, p.twg, p.log2n, frames, tid);
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
             // lane i takes bin k = bitrev_{log2n-1}(i) (k1g_features' untangle); U and the power column are padded
             const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
             const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
-            const float2 x = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
-            const float2 y = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
+            const float2 x = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
+            const float2 y = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
             const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
             const size_t o = (size_t)f * p.pw_stride + k + (k >> pad_sh);
             U[o] = make_float4(a, bb, d, -c);                                // L = a + i bb, R = d - i c
@@ -146,25 +138,17 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
             const float2 dp = pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)];
             const float a = 2.0f * u.x * dp.x, bi = 2.0f * u.y * dp.x;       // G_L = a + i bi
             const float c = 2.0f * u.z * dp.y, di = 2.0f * u.w * dp.y;       // G_R = c + i di
-            float2* zf = z + (size_t)f * n;
+            float2* zf = z + f * zs;
             if (k == 0 || k == half) {
-                zf[k] = make_float2(a, -c);
+                zf[fg_pad(k)] = make_float2(a, -c);
             } else {
-                zf[k] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
-                zf[n - k] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
+                zf[fg_pad(k)] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
+                zf[fg_pad(n - k)] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
             }
         }
         __syncthreads();
         // ---- inverse transform = conj(FFT(conj Y)) ------------------------------------------------------
-        h = half;
-        for (; h >= 2; h >>= 2) {
-            k1g_pass4(z, p.twg, n, frames, h, tid);
-            __syncthreads();
-        }
-        if (h == 1) {
-            k1g_pass2_last(z, n, frames, tid);
-            __syncthreads();
-        }
+        fg_fft(z, p.twg, p.log2n, frames, tid);
         // ---- window and overlap-add, one frame after the other (frames overlap) ------------------------
         // A thread walks the positions of the bit-reversed result (neighbouring words of z, the window read from its
         // bit-reversed copy) and adds at sample i = bitrev(position); the span is padded (q + (q >> ola_sh)) so that
@@ -172,7 +156,7 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
         for (int f = 0; f < frames; ++f) {
             const int q0 = (f0 + f) * p.hop;
             for (int pos = tid; pos < n; pos += kGThreads) {
-                const float2 r = z[(size_t)f * n + pos];
+                const float2 r = z[f * zs + fg_pad(pos)];
                 const float w = 2.0f * __ldg(p.win_br + pos);
                 const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
                 const int o = q + (q >> ola_sh);

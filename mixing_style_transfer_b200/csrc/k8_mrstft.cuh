@@ -42,25 +42,17 @@ struct K8Params {
 
 __device__ __forceinline__ void k8_load_fft(const K8Params& p, float2* z, const float* xr, const float* yr, int t0, int f0,
                                             int frames, int tid) {
-    const int n = p.n_fft, half = n >> 1;
+    const int n = p.n_fft, half = n >> 1, zs = fg_row(n);
     for (int idx = tid; idx < frames * n; idx += kGThreads) {
         const int f = idx >> p.log2n, i = idx & (n - 1);
         long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
         const float w = __ldg(p.win + i);
-        z[idx] = make_float2(__ldg(xr + j) * w, __ldg(yr + j) * w);
+        z[f * zs + fg_pad(i)] = make_float2(__ldg(xr + j) * w, __ldg(yr + j) * w);
     }
     __syncthreads();
-    int h = half;
-    for (; h >= 2; h >>= 2) {
-        k1g_pass4(z, p.twg, n, frames, h, tid);
-        __syncthreads();
-    }
-    if (h == 1) {
-        k1g_pass2_last(z, n, frames, tid);
-        __syncthreads();
-    }
+    fg_fft(z, p.twg, p.log2n, frames, tid);
 }
 
 __global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__ K8Params p) {
@@ -69,7 +61,7 @@ __global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__
     float* const red = reinterpret_cast<float*>(smem + p.off_red);             // [8 warps][3]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x, row = blockIdx.y;
-    const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n;
+    const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n, zs = fg_row(n);
     const unsigned mg_nb = k1g_magic(nb);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
@@ -83,8 +75,8 @@ __global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__
             // lane i takes bin k = bitrev_{log2n-1}(i): neighbouring words of z instead of one bank (k1g_features)
             const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
             const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
-            const float2 u = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
-            const float2 v = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
+            const float2 u = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
+            const float2 v = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
             const float a = u.x + v.x, bb = u.y - v.y, c = u.x - v.x, d = u.y + v.y;   // X = a + i bb, Y = d - i c
             const float mx = sqrtf(fmaf(a, a, bb * bb)), my = sqrtf(fmaf(d, d, c * c));
             const float dm = my - mx;
@@ -143,7 +135,7 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
     float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [span_pad]
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, row = blockIdx.y;
-    const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n;
+    const int n = p.n_fft, half = n >> 1, nb = half + 1, sh = 32 - p.log2n, zs = fg_row(n);
     const unsigned mg_nb = k1g_magic(nb);
     const int t0 = tile * kTF;
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
@@ -160,8 +152,8 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
             const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
             const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
-            const float2 u = z[(size_t)f * n + (__brev((unsigned)k) >> sh)];
-            const float2 v = z[(size_t)f * n + (__brev((unsigned)((n - k) & (n - 1))) >> sh)];
+            const float2 u = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
+            const float2 v = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
             const float a = u.x + v.x, bb = u.y - v.y, c = u.x - v.x, d = u.y + v.y;   // X = a + i bb, Y = d - i c
             const float mx = sqrtf(fmaf(a, a, bb * bb)), my = sqrtf(fmaf(d, d, c * c));
             const float dl = logf(mx + 1e-5f) - logf(my + 1e-5f);
@@ -175,29 +167,21 @@ __global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
             const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
             const float2 g = U[(size_t)f * p.u_stride + k + (k >> pad_sh)];
-            float2* zf = z + (size_t)f * n;
+            float2* zf = z + f * zs;
             if (k == 0 || k == half) {
-                zf[k] = make_float2(g.x, 0.0f);
+                zf[fg_pad(k)] = make_float2(g.x, 0.0f);
             } else {
-                zf[k] = make_float2(0.5f * g.x, -0.5f * g.y);
-                zf[n - k] = make_float2(0.5f * g.x, 0.5f * g.y);
+                zf[fg_pad(k)] = make_float2(0.5f * g.x, -0.5f * g.y);
+                zf[fg_pad(n - k)] = make_float2(0.5f * g.x, 0.5f * g.y);
             }
         }
         __syncthreads();
-        int h = half;
-        for (; h >= 2; h >>= 2) {
-            k1g_pass4(z, p.twg, n, frames, h, tid);
-            __syncthreads();
-        }
-        if (h == 1) {
-            k1g_pass2_last(z, n, frames, tid);
-            __syncthreads();
-        }
+        fg_fft(z, p.twg, p.log2n, frames, tid);
         // positions of the bit-reversed result in order, padded span (k6_logmel_bwd's overlap-add)
         for (int f = 0; f < frames; ++f) {
             const int q0 = (f0 + f) * p.hop;
             for (int pos = tid; pos < n; pos += kGThreads) {
-                const float2 r = z[(size_t)f * n + pos];
+                const float2 r = z[f * zs + fg_pad(pos)];
                 const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
                 const int o = q + (q >> ola_sh);
                 ola[o] = fmaf(2.0f * __ldg(p.win_br + pos), r.x, ola[o]);

@@ -216,7 +216,7 @@ int build_generic_tables(mixfe_plan* pl) {
         if ((rc = upload(&pl->d_win_br, win_br))) return rc;
     }
     pl->g_pw_stride = (n / 2 + 1 + (pl->g_log2n > 6 ? (n / 2) >> (pl->g_log2n - 6) : 0)) | 1;   // k + (k >> pad_sh), k <= n/2
-    const int per_frame = n * 8 + pl->g_pw_stride * 8;
+    const int per_frame = fg_row(n) * 8 + pl->g_pw_stride * 8;
     int nfr = kTF;
     {
         const char* e = getenv("MIXFE_K1G_SMEM_KB");            // tuning knob: frame-buffer budget per CTA
@@ -224,7 +224,7 @@ int build_generic_tables(mixfe_plan* pl) {
         while (nfr > 1 && nfr * per_frame > budget) nfr >>= 1;
     }
     pl->g_nf = nfr;
-    pl->g_off_pw = nfr * n * 8;
+    pl->g_off_pw = nfr * fg_row(n) * 8;
     const int stage = pl->g_off_pw + nfr * pl->g_pw_stride * 8;
     pl->g_off_mel = align16(stage);
     pl->g_off_S = pl->g_off_mel + kTF * pl->n_mels_pad * 8;
@@ -252,14 +252,14 @@ int build_generic_tables(mixfe_plan* pl) {
             return rc;
         pl->b_span = (kTF - 1) * pl->hop + n;
         pl->b_span_pad = pl->b_span + (pl->g_log2n > 5 ? pl->b_span >> (pl->g_log2n - 5) : 0) + 1;
-        const int per = n * 8 + pl->g_pw_stride * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
+        const int per = fg_row(n) * 8 + pl->g_pw_stride * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
         const int ola = align16(2 * pl->b_span_pad * 4);
         int bn = kTF;
         const char* e6 = getenv("MIXFE_K6_SMEM_KB");
         const int budget6 = (e6 ? atoi(e6) : 50) * 1024;
         while (bn > 1 && bn * per + ola + 64 > budget6) bn >>= 1;
         pl->b_nf = bn;
-        pl->b_off_U = bn * n * 8;
+        pl->b_off_U = bn * fg_row(n) * 8;
         pl->b_off_pw = pl->b_off_U + bn * pl->g_pw_stride * 16;
         pl->b_off_mel = pl->b_off_pw + bn * pl->g_pw_stride * 8;
         pl->b_off_ola = align16(pl->b_off_mel + bn * pl->n_mels_pad * 8);
@@ -484,9 +484,9 @@ int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B,
     if (B == 0) return fail(MIXFE_EINVAL, "empty batch");
     DeviceGuard guard(pl->device);
     int nf = kTF;
-    while (nf > 1 && nf * pl->n_fft * 8 > 72 * 1024) nf >>= 1;
+    while (nf > 1 && nf * fg_row(pl->n_fft) * 8 > 72 * 1024) nf >>= 1;
     p.nf = nf;
-    p.off_red = nf * pl->n_fft * 8;
+    p.off_red = nf * fg_row(pl->n_fft) * 8;
     const int smem = p.off_red + 8 * 3 * 4;
     if (!pl->k8_attr_done) {
         MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -517,12 +517,12 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     if (gs_c < T) return fail(MIXFE_EINVAL, "gradient channel stride smaller than T");
     if (B == 0) return MIXFE_OK;
     DeviceGuard guard(pl->device);
-    const int per = pl->n_fft * 8 + p.u_stride * 8, ola = align16(p.span_pad * 4);
+    const int per = fg_row(pl->n_fft) * 8 + p.u_stride * 8, ola = align16(p.span_pad * 4);
     if (per + ola > 200 * 1024) return fail(MIXFE_EUNSUPPORTED, "STFT loss backward: hop=%d needs too much shared memory", pl->hop);
     int nf = kTF;
     while (nf > 1 && nf * per + ola > 64 * 1024) nf >>= 1;
     p.nf = nf;
-    p.off_U = nf * pl->n_fft * 8;
+    p.off_U = nf * fg_row(pl->n_fft) * 8;
     p.off_ola = align16(p.off_U + nf * p.u_stride * 8);
     const int smem = p.off_ola + ola;
     if (!pl->k8_attr_done) {
