@@ -30,6 +30,47 @@ __device__ __forceinline__ float2 cmulf(float2 a, float2 w) {
     return make_float2(fmaf(a.x, w.x, -a.y * w.y), fmaf(a.x, w.y, a.y * w.x));
 }
 
+// Rows f = 0 .. frames-1 of z <- (a[j], b[j]) * win[i], i = 0 .. n-1, j = (t_first + f) * hop - n/2 + i folded back
+// into [0, T) as torch's 'reflect' padding does (T > n/2).  Tiles whose frames lie inside the signal take the loop
+// without the folding and the 64-bit index arithmetic, four points per thread at a time.
+__device__ __forceinline__ void fg_load_frames(float2* z, const float* __restrict__ a, const float* __restrict__ b,
+                                               const float* __restrict__ win, int log2n, int hop, int T, int t_first,
+                                               int frames, int tid) {
+    const int n = 1 << log2n, half = n >> 1, zs = fg_row(n);
+    const long long start = (long long)t_first * hop - half;
+    if (start >= 0 && start + (long long)(frames - 1) * hop + n <= (long long)T) {
+        const float* a0 = a + start;
+        const float* b0 = b + start;
+        for (int f = 0; f < frames; ++f) {
+            const float* af = a0 + (size_t)f * hop;
+            const float* bf = b0 + (size_t)f * hop;
+            float2* d = z + f * zs;
+            for (int i = tid; i < n; i += 4 * kGThreads) {        // 12 loads in flight, then the stores
+                float w[4], va[4], vb[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int iu = i + u * kGThreads;
+                    if (iu < n) { w[u] = __ldg(win + iu); va[u] = __ldg(af + iu); vb[u] = __ldg(bf + iu); }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int iu = i + u * kGThreads;
+                    if (iu < n) d[fg_pad(iu)] = make_float2(va[u] * w[u], vb[u] * w[u]);
+                }
+            }
+        }
+    } else {
+        for (int idx = tid; idx < (frames << log2n); idx += kGThreads) {
+            const int f = idx >> log2n, i = idx & (n - 1);
+            long long j = start + (long long)f * hop + i;
+            if (j < 0) j = -j;
+            if (j >= T) j = 2ll * (T - 1) - j;
+            const float w = __ldg(win + i);
+            z[f * zs + fg_pad(i)] = make_float2(__ldg(a + j) * w, __ldg(b + j) * w);
+        }
+    }
+}
+
 // d * exp(-2 pi i K / 16), K a compile-time constant after unrolling
 __device__ __forceinline__ float2 fg_mul_w16(float2 d, int K) {
     constexpr float kC[8] = {1.0f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f,

@@ -37,7 +37,7 @@ struct K1GParams {
     int off_pw, off_mel, off_S, off_red;
 };
 
-__global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant__ K1GParams g) {
+__global__ void __launch_bounds__(kGThreads, 3) k1g_features(const __grid_constant__ K1GParams g) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const K1Params& p = g.base;
     float2* const z = reinterpret_cast<float2*>(smem);                         // [nf][fg_row(n_fft)] padded rows
@@ -63,14 +63,7 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
         for (int f0 = 0; f0 < kTF; f0 += g.nf) {
             const int frames = nvalid - f0 < g.nf ? (nvalid - f0 > 0 ? nvalid - f0 : 0) : g.nf;
             // ---- load + window ------------------------------------------------------------------
-            for (int idx = tid; idx < frames * n; idx += kGThreads) {
-                const int f = idx >> g.log2n, i = idx & (n - 1);
-                long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
-                if (j < 0) j = -j;                               // torch 'reflect'
-                if (j >= p.T) j = 2ll * (p.T - 1) - j;
-                const float w = __ldg(g.win + i);
-                z[f * zs + fg_pad(i)] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
-            }
+            fg_load_frames(z, gL, gR, g.win, g.log2n, p.hop, p.T, t0 + f0, frames, tid);
             __syncthreads();
             // ---- FFT (fftg.cuh; ends with a barrier) ----------------------------------------------------
             fg_fft(z, g.twg, g.log2n, frames, tid);
@@ -88,22 +81,31 @@ __global__ void __launch_bounds__(kGThreads) k1g_features(const __grid_constant_
                 pw[(size_t)f * g.pw_stride + k + (k >> pad_sh)] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
             }
             __syncthreads();
-            // ---- mel projection -------------------------------------------------------------------
-            for (int idx = tid; idx < g.nf * p.n_mels_pad; idx += kGThreads) {
-                const int f = k1g_div(idx, mg_mp), m = idx - f * p.n_mels_pad;
-                float aL = 0.0f, aR = 0.0f;
-                if (f < frames && m < p.n_mels) {
-                    const int lo = __ldg(g.mel_lo + m), len = __ldg(g.mel_len + m);
-                    const float* w = g.mel_w + __ldg(g.mel_off + m);
-                    const float2* src = pw + (size_t)f * g.pw_stride;
-                    for (int i = 0; i < len; ++i) {
-                        const float wi = __ldg(w + i);
-                        const float2 v = src[lo + i + ((lo + i) >> pad_sh)];
-                        aL = fmaf(wi, v.x, aL);
-                        aR = fmaf(wi, v.y, aR);
+            // ---- mel projection: 8 lanes per (frame, filter) walk the filter's support, then a 3-step reduction ----
+            {
+                const int sub = tid & 7, grp = tid >> 3, total = g.nf * p.n_mels_pad;
+                for (int it0 = 0; it0 < total; it0 += kGThreads / 8) {
+                    const int it = it0 + grp;
+                    const int f = k1g_div(it, mg_mp), m = it - f * p.n_mels_pad;
+                    float aL = 0.0f, aR = 0.0f;
+                    if (it < total && f < frames && m < p.n_mels) {
+                        const int lo = __ldg(g.mel_lo + m), len = __ldg(g.mel_len + m);
+                        const float* w = g.mel_w + __ldg(g.mel_off + m);
+                        const float2* src = pw + (size_t)f * g.pw_stride;
+                        for (int i = sub; i < len; i += 8) {
+                            const float wi = __ldg(w + i);
+                            const float2 v = src[lo + i + ((lo + i) >> pad_sh)];
+                            aL = fmaf(wi, v.x, aL);
+                            aR = fmaf(wi, v.y, aR);
+                        }
                     }
+#pragma unroll
+                    for (int o = 1; o < 8; o <<= 1) {
+                        aL += __shfl_xor_sync(kFullMask, aL, o);
+                        aR += __shfl_xor_sync(kFullMask, aR, o);
+                    }
+                    if (sub == 0 && it < total) melb[(f0 + f) * p.n_mels_pad + m] = make_float2(aL, aR);
                 }
-                melb[(f0 + f) * p.n_mels_pad + m] = make_float2(aL, aR);
             }
             __syncthreads();
         }

@@ -47,7 +47,7 @@ struct K6Params {
     int off_U, off_pw, off_mel, off_ola;
 };
 
-__global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant__ K6Params p) {
+__global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_constant__ K6Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][fg_row(n)] padded rows (fftg.cuh)
     float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][pw_stride] (L.re, L.im, R.re, R.im)
@@ -71,14 +71,7 @@ __global__ void __launch_bounds__(kGThreads) k6_logmel_bwd(const __grid_constant
     for (int f0 = 0; f0 < nvalid; f0 += p.nf) {
         const int frames = nvalid - f0 < p.nf ? nvalid - f0 : p.nf;
         // ---- forward: load + window, FFT, untangle ------------------------------------------------
-        for (int idx = tid; idx < frames * n; idx += kGThreads) {
-            const int f = idx >> p.log2n, i = idx & (n - 1);
-            long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
-            if (j < 0) j = -j;
-            if (j >= p.T) j = 2ll * (p.T - 1) - j;
-            const float w = __ldg(p.win + i);
-            z[f * zs + fg_pad(i)] = make_float2(__ldg(gL + j) * w, __ldg(gR + j) * w);
-        }
+        fg_load_frames(z, gL, gR, p.win, p.log2n, p.hop, p.T, t0 + f0, frames, tid);
         __syncthreads();
         fg_fft(z, p.twg, p.log2n, frames, tid);
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {

@@ -42,20 +42,12 @@ struct K8Params {
 
 __device__ __forceinline__ void k8_load_fft(const K8Params& p, float2* z, const float* xr, const float* yr, int t0, int f0,
                                             int frames, int tid) {
-    const int n = p.n_fft, half = n >> 1, zs = fg_row(n);
-    for (int idx = tid; idx < frames * n; idx += kGThreads) {
-        const int f = idx >> p.log2n, i = idx & (n - 1);
-        long long j = (long long)(t0 + f0 + f) * p.hop - half + i;
-        if (j < 0) j = -j;
-        if (j >= p.T) j = 2ll * (p.T - 1) - j;
-        const float w = __ldg(p.win + i);
-        z[f * zs + fg_pad(i)] = make_float2(__ldg(xr + j) * w, __ldg(yr + j) * w);
-    }
+    fg_load_frames(z, xr, yr, p.win, p.log2n, p.hop, p.T, t0 + f0, frames, tid);
     __syncthreads();
     fg_fft(z, p.twg, p.log2n, frames, tid);
 }
 
-__global__ void __launch_bounds__(kGThreads) k8_partials(const __grid_constant__ K8Params p) {
+__global__ void __launch_bounds__(kGThreads, 3) k8_partials(const __grid_constant__ K8Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);
     float* const red = reinterpret_cast<float*>(smem + p.off_red);             // [8 warps][3]
@@ -128,7 +120,7 @@ __global__ void __launch_bounds__(256) k8_finish(const K8Params p) {
     }
 }
 
-__global__ void __launch_bounds__(kGThreads) k8_backward(const __grid_constant__ K8Params p) {
+__global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constant__ K8Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
     float2* const U = reinterpret_cast<float2*>(smem + p.off_U);             // [nf][u_stride] G = d loss / d X

@@ -256,7 +256,7 @@ int build_generic_tables(mixfe_plan* pl) {
         const int ola = align16(2 * pl->b_span_pad * 4);
         int bn = kTF;
         const char* e6 = getenv("MIXFE_K6_SMEM_KB");
-        const int budget6 = (e6 ? atoi(e6) : 50) * 1024;
+        const int budget6 = (e6 ? atoi(e6) : 72) * 1024;
         while (bn > 1 && bn * per + ola + 64 > budget6) bn >>= 1;
         pl->b_nf = bn;
         pl->b_off_U = bn * fg_row(n) * 8;
