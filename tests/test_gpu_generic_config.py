@@ -20,7 +20,10 @@ def _to(clip, dev):
     return {n: v.to(dev) for n, v in clip.items()}
 
 
-CONFIGS = [(2048, 512, 80), (512, 128, 64), (4096, 1024, 128), (256, 64, 40), (1024, 512, 96), (2048, 256, 128)]
+# n_fft 64 .. 4096: every split of log2(n_fft) into register passes of 3 or 4 stages (csrc/fftg.cuh): 3+3, 4+3, 4+4,
+# 3+3+3, 4+3+3, 4+4+3, 4+4+4
+CONFIGS = [(2048, 512, 80), (512, 128, 64), (4096, 1024, 128), (256, 64, 40), (1024, 512, 96), (2048, 256, 128),
+           (128, 32, 24), (64, 16, 12)]
 
 
 @pytest.mark.parametrize("n_fft,hop,n_mels", CONFIGS)

@@ -59,6 +59,22 @@ def test_two_dim_input_custom_resolutions_and_upstream_scale(cuda_device):
     assert err <= max(4.0 * err32, 1e-4 * float(g64.abs().max())), f"grad err {err:.3g}, fp32 oracle err {err32:.3g}"
 
 
+def test_small_and_odd_log2_resolutions(cuda_device):
+    """64, 128 and 512 points: the 3+3, 4+3 and 3+3+3 pass splits of csrc/fftg.cuh."""
+    x, y = M.pair(8, 2, 2, 3000)
+    kw = dict(fft_sizes=(64, 128, 512), hop_sizes=(16, 32, 128), win_sizes=(64, 128, 512))
+    mod = pkg.MultiResolutionSTFTLoss(**{k: list(v) for k, v in kw.items()})
+    xd = x.to(cuda_device).requires_grad_(True)
+    loss = mod(xd, y.to(cuda_device))
+    loss.backward()
+    l64, g64 = _oracle(x, y, torch.float64, **kw)
+    _, g32 = _oracle(x, y, torch.float32, **kw)
+    assert abs(float(loss.detach()) - l64) <= 1e-4 * abs(l64)
+    err = float((xd.grad.cpu().double() - g64).abs().max())
+    err32 = float((g32 - g64).abs().max())
+    assert err <= max(4.0 * err32, 1e-4 * float(g64.abs().max())), f"grad err {err:.3g}, fp32 oracle err {err32:.3g}"
+
+
 def test_identical_inputs_give_rounding_level_loss_and_finite_gradient(cuda_device):
     """The reference returns exactly 0 for x == y; x and y share one packed transform here and come out of the
     untangling with different last bits, so the loss is at rounding level instead (and the non-smooth point x == y
