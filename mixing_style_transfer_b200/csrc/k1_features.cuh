@@ -75,9 +75,6 @@ struct K1Params {
     int n_wt;                        // floats in wsteps
     int wmeta[8][2][4];              // per warp, per group slot: steps (even), weight offset, group index, 0
     int want_stats;
-    unsigned* sm_ticket;             // [n_sms] ever-increasing arrival counters, one per SM
-    int dbg_skip;                    // timing experiments only (MIXFE_K1_DBG_SKIP): 1 = no time statistics, 2 = no masking
-    int skew_ns;                     // start delay of every second CTA that lands on an SM (0 = none)
     int off_ex, off_tw, off_s, off_wsteps, off_flo, off_red;
 };
 
@@ -422,26 +419,6 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
         }
     }
 
-    // Persistent CTAs that share an SM start together and, with identical work per tile, would stay in
-    // lockstep: both in the FP-bound FFT phase, then both in the shared-memory-bound phases.  Delaying
-    // every second arrival on an SM keeps the two CTAs in complementary phases.
-    if (p.skew_ns > 0) {
-        if (tid == 0) {
-            unsigned smid;
-            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-            const unsigned ticket = atomicAdd(p.sm_ticket + smid, 1u);
-            if (ticket & 1u) {
-                unsigned long long t0, t1;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-                do {
-                    __nanosleep(500);
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                } while (t1 - t0 < (unsigned long long)p.skew_ns);
-            }
-        }
-        __syncthreads();
-    }
-
     for (;;) {
         const int t0 = tile * kTF;
         const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;          // frames of this tile that exist
@@ -455,7 +432,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             }
             __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
             bool stats_rows = false;
-            if (s == 0 && p.want_stats && !(p.dbg_skip & 1)) {
+            if (s == 0 && p.want_stats) {
                 // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
                 // the clip and every row is 16-byte aligned; else role loads straight from global memory.
                 const long long own0 = (long long)tile * kTF * p.hop;
@@ -693,8 +670,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     sc[2 * ab + 1] = 0.5f * (v[2] + v[3]);
                 }
                 if (p.want_stats) {
-                    if (p.dbg_skip & 2) {
-                    } else if (s < 3) {
+                    if (s < 3) {
                         S[s * kK1Threads + tid] = make_float4(sc[0], sc[1], sc[2], sc[3]);
                     } else {
                         const float4 A0 = S[tid], A1 = S[kK1Threads + tid], A2 = S[2 * kK1Threads + tid];
@@ -789,7 +765,7 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         if (m < p.n_mels) {
             const float2* src = p.part_spec + ((long long)b * p.n_tiles * kNumStems + s) * p.n_mels_pad + m;
             const long long step = (long long)kNumStems * p.n_mels_pad;
-#pragma unroll 8
+#pragma unroll 16
             for (int t = 0; t < p.n_tiles; ++t) {
                 const float2 v = __ldg(src + t * step);
                 slog += (double)v.x;
@@ -805,7 +781,8 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
             sMelTot[s][warp & 3] = c;
         }
     }
-    // 2. time-domain partials: 8 threads per quantity, two records per tile
+    // 2. time-domain partials: 8 threads per quantity, two records per tile; four records in flight per thread,
+    //    combined in record order
     if (tid < kTdN * 8) {
         const int q = tid >> 3, sub = tid & 7;
         const bool is_max = q < 32 && (q & 7) >= 6;
@@ -813,11 +790,21 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         if (q < 37) {
             const float* src = p.part_td + (long long)b * p.n_tiles * (2 * kTdN);
             const int n_rec = 2 * p.n_tiles, step = (q >= 33) ? 2 : 1;          // masking sums live in record 0 only
-            for (int t = sub * step; t < n_rec; t += 8 * step) {
-                const float* r = src + (long long)t * kTdN;
-                double u = (double)__ldg(r + q);
-                if (q == 32) u += (double)__ldg(r + 37) + (double)__ldg(r + 38) + (double)__ldg(r + 39);
-                v = is_max ? fmax(v, u) : v + u;
+            for (int t0 = sub * step; t0 < n_rec; t0 += 32 * step) {
+                double u[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int t = t0 + 8 * step * k;
+                    u[k] = 0.0;
+                    if (t < n_rec) {
+                        const float* r = src + (long long)t * kTdN;
+                        u[k] = (double)__ldg(r + q);
+                        if (q == 32) u[k] += (double)__ldg(r + 37) + (double)__ldg(r + 38) + (double)__ldg(r + 39);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (t0 + 8 * step * k < n_rec) v = is_max ? fmax(v, u[k]) : v + u[k];
             }
         }
 #pragma unroll

@@ -315,13 +315,6 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     p.tw = pl->d_tw; p.wsteps = pl->d_wsteps; p.flo = pl->d_flo; p.n_wt = (pl->off_flo - pl->off_wsteps) / 4;
     memcpy(p.wmeta, pl->wmeta, sizeof(p.wmeta));
     p.want_stats = features ? 1 : 0;
-    p.sm_ticket = pl->d_sm_ticket;
-    {
-        const char* e = getenv("MIXFE_K1_SKEW_NS");
-        p.skew_ns = e ? atoi(e) : pl->k1_skew_ns;
-        const char* d = getenv("MIXFE_K1_DBG_SKIP");
-        p.dbg_skip = d ? atoi(d) : 0;
-    }
     p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_wsteps = pl->off_wsteps;
     p.off_flo = pl->off_flo; p.off_red = pl->off_red;
     if (pl->use_generic) {
@@ -590,8 +583,6 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
         const double c = -2.0 * M_PI * (double)e / 1024.0;
         twl[e] = make_float2((float)std::cos(c), (float)std::sin(c));
     }
-    MIXFE_CUDA(cudaMalloc((void**)&pl->d_sm_ticket, 1024 * sizeof(unsigned)));
-    MIXFE_CUDA(cudaMemset(pl->d_sm_ticket, 0, 1024 * sizeof(unsigned)));
     int rc = upload(&pl->d_tw, tw);
     if (!rc) rc = upload(&pl->d_twfine, twf);
     if (!rc) rc = upload(&pl->d_twlin, twl);
@@ -605,7 +596,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
-    cudaFree(pl->ws); cudaFree(pl->aug_params_dev); cudaFree(pl->d_sm_ticket);
+    cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_win_br); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_lo); cudaFree(pl->d_bin_len); cudaFree(pl->d_bin_off); cudaFree(pl->d_bin_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
