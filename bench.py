@@ -88,6 +88,17 @@ def _ref_worker_run(job):
     return time.perf_counter() - t0, float(f.sum()) + float(lm[0, 0, 1, 0])
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -123,7 +134,7 @@ def run_reference(args):
                              "host_cores_visible": cores},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # =================================================================================================
@@ -413,13 +424,18 @@ def run_native(args):
             line["e2e"] = e2e
         if allgather is not None:
             line["allgather"] = allgather
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
+    # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner with
+    # printf at communicator creation), so fd 1 is pointed at stderr for the run and the line goes to the real stdout.
     a = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
