@@ -159,7 +159,8 @@ int build_mel_tables(mixfe_plan* pl) {
     if ((rc = upload(&pl->d_wsteps, wt))) return rc;
     // shared-memory map of K1
     pl->nxs = (kTF - 1) * pl->hop + kNfft;
-    pl->off_ex = align16(pl->nxs * 8);
+    pl->off_ex = (pl->nxs * 8 + 1023) & ~1023;        // the exchange regions are addressed with XOR swizzles of the low
+                                                      // address bits: their base must stay 1 KB aligned for every hop
     pl->off_tw = pl->off_ex + 8 * kWarpRegion;
     pl->off_s = pl->off_tw + 31 * 32 * 8;            // rows k1 = 1..31 of the twiddle table (row 0 is all ones)
     pl->off_wsteps = pl->off_s + 3 * kK1Threads * 16;   // S: one float4 per thread and stem 0..2

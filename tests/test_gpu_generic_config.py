@@ -48,6 +48,40 @@ def test_features_melpower_logmel_vs_oracle(cuda_device, n_fft, hop, n_mels, T):
     assert float((lm.cpu() - ref_lm).abs().max()) < 5e-3
 
 
+def _fuzz_cases():
+    """Seeded irregular configurations: hops that do not divide n_fft (odd, prime), hops above n_fft/2, clips barely
+    longer than the reflect padding, ragged last tiles.  n_mels stays where every filter has support."""
+    import random
+    rnd = random.Random(20260)
+    cases = []
+    for n_fft in (64, 128, 256, 512, 1024, 2048, 4096):
+        for _ in range(2):
+            hop = rnd.choice([rnd.randrange(max(8, n_fft // 16), n_fft // 2), rnd.randrange(n_fft // 2, n_fft + 1),
+                              rnd.choice([97, 101, 250, 441])])
+            hop = max(8, min(hop, n_fft))
+            n_mels = rnd.choice([8, 16, 24, 40, 64, 80, 96, 128])
+            n_mels = min(n_mels, max(8, n_fft // 12))
+            T = rnd.choice([n_fft // 2 + 1 + rnd.randrange(0, 50), n_fft + rnd.randrange(1, 3000),
+                            8 * hop + rnd.randrange(0, hop), 20000 + rnd.randrange(0, 5000)])
+            cases.append((n_fft, hop, n_mels, T))
+    return cases
+
+
+@pytest.mark.parametrize("n_fft,hop,n_mels,T", _fuzz_cases())
+def test_irregular_configurations_vs_oracle(cuda_device, n_fft, hop, n_mels, T):
+    cfg = O.FrontEndConfig(n_fft=n_fft, hop_length=hop, n_mels=n_mels)
+    clip = O.musical_clip(n_fft * 7 + hop, T)
+    dclip = _to(clip, cuda_device)
+    fe = pkg.MixingFeatureExtractor(44100, n_fft, hop, n_mels)
+    what = f"{n_fft}/{hop}/{n_mels} T={T}"
+    assert_features_close(fe.extract_all_features(dclip), O.mixing_features(clip, cfg), fe.feature_names(), what)
+    ofe = O.MelFrontEnd(cfg)
+    ref = torch.cat([ofe.mel_power(clip[n][None]) for n in O.STEMS], dim=1)
+    mp = fe._plan(cuda_device).debug_mel_power([dclip[n][None] for n in O.STEMS])
+    assert mp.shape == ref.shape == (1, 8, n_mels, 1 + T // hop)
+    assert_melpower_close(mp, ref, what)
+
+
 def test_generic_kernel_serves_non_1024_plans(cuda_device):
     fe = pkg.MixingFeatureExtractor(44100, 2048, 512, 80)
     assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 0          # K1G marker
