@@ -29,7 +29,10 @@ def _noisy_clip(seed, T):
 
 @pytest.mark.parametrize("n_fft,hop,n_mels,T", [(1024, 256, 128, 20000), (2048, 512, 80, 30001), (512, 128, 64, 9000),
                                                 (4096, 1024, 128, 40000), (1024, 256, 128, 1500), (256, 64, 40, 5000),
-                                                (128, 32, 24, 3000), (64, 16, 12, 2000)])
+                                                (128, 32, 24, 3000), (64, 16, 12, 2000),
+                                                # hops that divide nothing, hop > n_fft/2, one-frame clips, ragged tiles
+                                                (1024, 300, 40, 5810), (1024, 703, 64, 561), (2048, 1087, 96, 9343),
+                                                (512, 434, 8, 3700), (256, 93, 16, 2111), (4096, 450, 96, 4323)])
 def test_backward_matches_autograd_through_oracle(cuda_device, n_fft, hop, n_mels, T):
     cfg = O.FrontEndConfig(n_fft=n_fft, hop_length=hop, n_mels=n_mels)
     clip = _noisy_clip(n_fft + T, T)

@@ -75,6 +75,29 @@ def test_small_and_odd_log2_resolutions(cuda_device):
     assert err <= max(4.0 * err32, 1e-4 * float(g64.abs().max())), f"grad err {err:.3g}, fp32 oracle err {err32:.3g}"
 
 
+def test_irregular_hops_and_strided_rows(cuda_device):
+    """Hops that divide nothing, a hop above n_fft/2, and prediction / target that are views into wider tensors
+    (unaligned rows, row stride != T)."""
+    T = 7001
+    xb, yb = M.pair(9, 2, 3, T + 13)
+    x, y = xb[:, :2, 5:5 + T], yb[:, 1:, 8:8 + T]
+    kw = dict(fft_sizes=(1024, 256, 2048), hop_sizes=(300, 93, 1087), win_sizes=(1024, 256, 2048))
+    mod = pkg.MultiResolutionSTFTLoss(**{k: list(v) for k, v in kw.items()})
+    xd_full = xb.to(cuda_device).requires_grad_(True)
+    loss = mod(xd_full[:, :2, 5:5 + T], yb.to(cuda_device)[:, 1:, 8:8 + T])
+    loss.backward()
+    l64, g64 = _oracle(x.contiguous(), y.contiguous(), torch.float64, **kw)
+    _, g32 = _oracle(x.contiguous(), y.contiguous(), torch.float32, **kw)
+    assert abs(float(loss.detach()) - l64) <= 1e-4 * abs(l64)
+    got = xd_full.grad.cpu().double()
+    err = float((got[:, :2, 5:5 + T] - g64).abs().max())
+    err32 = float((g32 - g64).abs().max())
+    assert err <= max(4.0 * err32, 1e-4 * float(g64.abs().max())), f"grad err {err:.3g}, fp32 oracle err {err32:.3g}"
+    outside = got.clone()
+    outside[:, :2, 5:5 + T] = 0.0
+    assert float(outside.abs().max()) == 0.0                 # nothing written outside the view
+
+
 def test_identical_inputs_give_rounding_level_loss_and_finite_gradient(cuda_device):
     """The reference returns exactly 0 for x == y; x and y share one packed transform here and come out of the
     untangling with different last bits, so the loss is at rounding level instead (and the non-smooth point x == y
@@ -84,7 +107,7 @@ def test_identical_inputs_give_rounding_level_loss_and_finite_gradient(cuda_devi
     xd = x.to(cuda_device).requires_grad_(True)
     loss = mod(xd, x.to(cuda_device))
     loss.backward()
-    assert 0.0 <= float(loss) < 1e-5 and bool(torch.isfinite(xd.grad).all())
+    assert 0.0 <= float(loss.detach()) < 1e-5 and bool(torch.isfinite(xd.grad).all())
 
 
 def test_unsupported_configurations_raise():
