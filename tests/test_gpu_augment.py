@@ -207,3 +207,36 @@ def test_bad_arguments(cuda_device):
     st = [clip[n][None] for n in O.STEMS]
     with pytest.raises(ValueError, match="unstable"):
         aug._plan(cuda_device).augment(st, arr, None)
+
+
+def _fuzz_lengths():
+    import random
+    rnd = random.Random(77)
+    edge = [1, 2, 3, 31, 32, 33, 127, 511, 512, 513, 1023, 1025, 8191, 8193]          # around the scan's block sizes
+    return [(i, T) for i, T in enumerate(edge + [rnd.randrange(600, 90000) for _ in range(8)])]
+
+
+@pytest.mark.parametrize("seed,T", _fuzz_lengths())
+def test_random_decisions_lengths_and_unaligned_views(cuda_device, seed, T):
+    """Seeded random augmentation decisions (prob 0.7) on clips of awkward lengths, the stems passed as views that
+    start 1..3 floats into a wider tensor (no 128-bit loads possible)."""
+    torch.manual_seed(1000 + seed)
+    par = O.draw_clip_aug(prob=0.7)
+    if T < 22050:
+        par.impulse = None                     # F.conv1d 'same' against a 22050-tap impulse needs nothing special,
+                                               # but the oracle's direct form is slow; the reverb has its own tests
+    clip = O.musical_clip(300 + seed, T)
+    off = 1 + seed % 3
+    wide = {n: torch.zeros(2, T + 8).to(cuda_device) for n in O.STEMS}
+    views = {}
+    for n in O.STEMS:
+        wide[n][:, off:off + T] = clip[n].to(cuda_device)
+        views[n] = wide[n][:, off:off + T]
+    aug = pkg.AudioAugmenter()
+    got = aug.apply(views, [_decisions_from_oracle(par)])
+    ref = O.apply_clip_aug(clip, par, fft_reverb=True)
+    err = _rel_err(got, ref)
+    assert err < 5e-6, f"T={T} off={off}: rel max err {err:.3g}"
+    for n in O.STEMS:                                              # inputs untouched, padding untouched
+        assert torch.equal(wide[n][:, off:off + T].cpu(), clip[n])
+        assert float(wide[n][:, :off].abs().max()) == 0.0 and float(wide[n][:, off + T:].abs().max()) == 0.0

@@ -55,3 +55,19 @@ def test_other_sample_rate(cuda_device):
     got = fe.gated_loudness({n: v.to(cuda_device) for n, v in clip.items()})
     ref = B.stems_gated_loudness({n: v.numpy() for n, v in clip.items()}, fs)
     assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 1e-3
+
+
+@pytest.mark.parametrize("seed,T,off", [(1, 17640, 1), (2, 17641, 3), (3, 22049, 2), (4, 35279, 1), (5, 35281, 0),
+                                        (6, 61237, 3), (7, 130003, 2)])
+def test_awkward_lengths_and_unaligned_views(cuda_device, seed, T, off):
+    """Lengths around the 100 ms sub-block edges (4410 samples) and the 8-sub-block chunk edge (35280), stems passed as
+    views that start `off` floats into a wider tensor."""
+    clip = O.musical_clip(500 + seed, T)
+    wide = {n: torch.zeros(2, T + 4) for n in O.STEMS}
+    for n in O.STEMS:
+        wide[n][:, off:off + T] = clip[n] * (0.02 if n == "other" else 1.0)
+    dev_wide = {n: v.to(cuda_device) for n, v in wide.items()}
+    fe = pkg.MixingFeatureExtractor()
+    got = fe.gated_loudness({n: v[:, off:off + T] for n, v in dev_wide.items()})
+    ref = B.stems_gated_loudness({n: wide[n][:, off:off + T].numpy() for n in O.STEMS}, 44100)
+    assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 1e-3, (got.cpu().numpy(), ref)
