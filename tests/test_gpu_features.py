@@ -228,3 +228,25 @@ def test_full_size_properties(fe, cuda_device):
 def test_smoke_entry(cuda_device):
     import __graft_entry__ as ge
     ge.smoke()
+
+
+@pytest.mark.parametrize("sr,n_mels", [(8000, 128), (16000, 128), (16000, 64), (22050, 128), (32000, 80), (48000, 128),
+                                       (96000, 128), (44100, 8), (44100, 1), (11025, 33)])
+def test_other_sample_rates_and_filter_counts(cuda_device, sr, n_mels):
+    """The mel walk's tables (groups of 8 filters, start residues, empty filters) depend on the filterbank's shape:
+    low sample rates give filters narrower than a bin (some empty), n_mels not a multiple of 8 gives a ragged last
+    group.  Features, mel power and log-mel against the oracle."""
+    cfg = O.FrontEndConfig(sample_rate=sr, n_mels=n_mels)
+    T = 30011
+    clip = O.musical_clip(sr % 1000 + n_mels, T, sample_rate=sr)
+    dclip = _to(clip, cuda_device)
+    fe = pkg.MixingFeatureExtractor(sr, 1024, 256, n_mels)
+    what = f"sr={sr} n_mels={n_mels}"
+    assert_features_close(fe.extract_all_features(dclip), O.mixing_features(clip, cfg), fe.feature_names(), what)
+    ofe = O.MelFrontEnd(cfg)
+    ref = torch.cat([ofe.mel_power(clip[n][None]) for n in O.STEMS], dim=1)
+    mp = fe._plan(cuda_device).debug_mel_power([dclip[n][None] for n in O.STEMS])
+    assert_melpower_close(mp, ref, what)
+    lm = pkg.MelSpectrogramPreprocessor(sr, 1024, 256, n_mels)({n: v[None] for n, v in dclip.items()})
+    ref_lm = O.log_mel({n: v[None] for n, v in clip.items()}, cfg)
+    assert float((lm.cpu() - ref_lm).abs().max()) < 5e-3
