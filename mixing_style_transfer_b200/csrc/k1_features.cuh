@@ -62,6 +62,10 @@ struct K1Params {
     long long stride_b, stride_c;
     int B, T, F, hop, n_mels, n_mels_pad, n_tiles;
     int nxs;                         // staged samples per channel = (kTF-1)*hop + 1024
+    // Staging decisions the host makes once per launch (pointers, strides and hop decide the alignment of every
+    // (clip, tile, stem) at once; the tile index alone decides whether it lies inside the clip):
+    int tma_lo, tma_hi;              // tiles tma_lo..tma_hi are staged by TMA bulk copies (empty range = none)
+    int rows_hi;                     // tiles 0..rows_hi get their time-statistics rows by TMA (-1 = none)
     long long total_items;           // B * n_tiles
     float* logmel;
     long long lm_stride_b;
@@ -152,14 +156,16 @@ struct K1Stage {                     // where the samples of one (clip, tile, st
     bool tma;
 };
 
+__device__ __forceinline__ bool k1_stage_is_tma(const K1Params& p, int tile) {
+    return tile >= p.tma_lo && tile <= p.tma_hi;
+}
+
 __device__ __forceinline__ K1Stage k1_stage_of(const K1Params& p, int b, int tile, int s) {
     K1Stage st;
     st.gL = p.stem[s] + (long long)b * p.stride_b;
     st.gR = st.gL + p.stride_c;
     st.base = (long long)tile * kTF * p.hop - kNfft / 2;
-    const bool interior = st.base >= 0 && st.base + p.nxs <= (long long)p.T;
-    st.tma = interior && (p.nxs & 3) == 0 &&
-             ((reinterpret_cast<unsigned long long>(st.gL + st.base) | reinterpret_cast<unsigned long long>(st.gR + st.base)) & 15ull) == 0;
+    st.tma = k1_stage_is_tma(p, tile);
     return st;
 }
 
@@ -435,15 +441,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             if (s == 0 && p.want_stats) {
                 // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
                 // the clip and every row is 16-byte aligned; else role loads straight from global memory.
-                const long long own0 = (long long)tile * kTF * p.hop;
-                const long long cb = (long long)b * p.stride_b + own0;
-                unsigned long long amask = (unsigned long long)(p.hop & 127);
-#pragma unroll
-                for (int q = 0; q < kNumStems; ++q)
-                    amask |= reinterpret_cast<unsigned long long>(p.stem[q] + cb) |
-                             reinterpret_cast<unsigned long long>(p.stem[q] + cb + p.stride_c);
-                if ((amask & 15ull) == 0 && kTF * p.hop * 4 <= kWarpRegion && own0 + kTF * p.hop <= (long long)p.T) {
+                if (tile <= p.rows_hi) {
                     if (tid == 0) {
+                        const long long cb = (long long)b * p.stride_b + (long long)tile * kTF * p.hop;
                         const unsigned bytes = (unsigned)(kTF * p.hop) * 4u;
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         mbar_expect_tx(bar2, 8u * bytes);
@@ -498,21 +498,20 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 const bool have_next = s + 1 < kNumStems || next_item < p.total_items;
                 bool next_tma = false;
                 if (have_next) {
-                    const K1Stage st = k1_stage_of(p, nb, ntile, ns);
-                    next_tma = st.tma;
-                    if (st.tma) {
+                    next_tma = k1_stage_is_tma(p, ntile);
+                    if (next_tma) {
                         // no CTA barrier: the last warp to finish reading xs starts the copy
                         __syncwarp();
                         if (lane == 0) {
                             __threadfence_block();
                             if (atomicAdd(arrivals, 1) == kK1Threads / 32 - 1) {
                                 *arrivals = 0;
-                                k1_stage_tma(p, st, xsL, bar);
+                                k1_stage_tma(p, k1_stage_of(p, nb, ntile, ns), xsL, bar);
                             }
                         }
                     } else {
                         __syncthreads();     // B0': every warp has its frame in registers, xs is dead
-                        k1_stage_coop(p, st, xsL, tid);
+                        k1_stage_coop(p, k1_stage_of(p, nb, ntile, ns), xsL, tid);
                     }
                 }
                 cur_tma = next_tma;
@@ -521,11 +520,16 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     // staging): the statistics loads at the top of the next tile then hit L2 instead of HBM
                     const long long own0 = (long long)ntile * kTF * p.hop;
                     const int lines_per_row = (kTF * p.hop * 4) >> 7;
-                    for (int i = tid; i < 6 * lines_per_row; i += kK1Threads) {
-                        const int row = i / lines_per_row, off = (i - row * lines_per_row) * 32;
-                        if (own0 + off < p.T) {
-                            const float* g = p.stem[1 + (row >> 1)] + (long long)nb * p.stride_b + (row & 1) * p.stride_c + own0 + off;
-                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g));
+                    for (int l = tid; l < lines_per_row; l += kK1Threads) {
+                        if (own0 + l * 32 < p.T) {
+                            const float* g0 = p.stem[1] + (long long)nb * p.stride_b + own0 + l * 32;
+                            const long long ds = p.stem[2] - p.stem[1], dd = p.stem[3] - p.stem[1];
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0 + p.stride_c));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0 + ds));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0 + ds + p.stride_c));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0 + dd));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(g0 + dd + p.stride_c));
                         }
                     }
                 }

@@ -318,6 +318,24 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
     p.want_stats = features ? 1 : 0;
     p.off_ex = pl->off_ex; p.off_tw = pl->off_tw; p.off_s = pl->off_s; p.off_wsteps = pl->off_wsteps;
     p.off_flo = pl->off_flo; p.off_red = pl->off_red;
+    {
+        // TMA bulk copies need 16-byte aligned global addresses and sizes.  Every row start is
+        // stem + b * stride_b + c * stride_c + tile * kTF * hop (- 512 for the frame staging): with 16-byte aligned
+        // stem pointers and strides that are multiples of 4 floats all of them are aligned at once (kTF * hop * 4 is a
+        // multiple of 32 bytes), so the kernel only has to compare the tile index with the range that lies inside the
+        // clip.
+        bool aligned = (stride_b % 4 == 0 || B == 1) && stride_c % 4 == 0;
+        for (int s = 0; s < 4; ++s) aligned = aligned && (reinterpret_cast<uintptr_t>(stems[s]) & 15u) == 0;
+        const long long tile_span = (long long)kTF * pl->hop;
+        p.tma_lo = 1; p.tma_hi = 0; p.rows_hi = -1;
+        if (aligned && pl->nxs % 4 == 0) {
+            p.tma_lo = (int)((kNfft / 2 + tile_span - 1) / tile_span);                 // tile * span - 512 >= 0
+            const long long room = (long long)T + kNfft / 2 - pl->nxs;                 // tile * span - 512 + nxs <= T
+            p.tma_hi = room < 0 ? -1 : (int)std::min<long long>(room / tile_span, n_tiles - 1);
+        }
+        if (aligned && pl->hop % 16 == 0 && tile_span * 4 <= kWarpRegion)
+            p.rows_hi = (int)std::min<long long>((long long)T / tile_span - 1, n_tiles - 1);   // (tile + 1) * span <= T
+    }
     if (pl->use_generic) {
         K1GParams g{};
         g.base = p;
