@@ -769,7 +769,7 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         if (m < p.n_mels) {
             const float2* src = p.part_spec + ((long long)b * p.n_tiles * kNumStems + s) * p.n_mels_pad + m;
             const long long step = (long long)kNumStems * p.n_mels_pad;
-#pragma unroll 16
+#pragma unroll 8
             for (int t = 0; t < p.n_tiles; ++t) {
                 const float2 v = __ldg(src + t * step);
                 slog += (double)v.x;
@@ -785,8 +785,7 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
             sMelTot[s][warp & 3] = c;
         }
     }
-    // 2. time-domain partials: 8 threads per quantity, two records per tile; four records in flight per thread,
-    //    combined in record order
+    // 2. time-domain partials: 8 threads per quantity, two records per tile
     if (tid < kTdN * 8) {
         const int q = tid >> 3, sub = tid & 7;
         const bool is_max = q < 32 && (q & 7) >= 6;
@@ -794,21 +793,11 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         if (q < 37) {
             const float* src = p.part_td + (long long)b * p.n_tiles * (2 * kTdN);
             const int n_rec = 2 * p.n_tiles, step = (q >= 33) ? 2 : 1;          // masking sums live in record 0 only
-            for (int t0 = sub * step; t0 < n_rec; t0 += 32 * step) {
-                double u[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int t = t0 + 8 * step * k;
-                    u[k] = 0.0;
-                    if (t < n_rec) {
-                        const float* r = src + (long long)t * kTdN;
-                        u[k] = (double)__ldg(r + q);
-                        if (q == 32) u[k] += (double)__ldg(r + 37) + (double)__ldg(r + 38) + (double)__ldg(r + 39);
-                    }
-                }
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (t0 + 8 * step * k < n_rec) v = is_max ? fmax(v, u[k]) : v + u[k];
+            for (int t = sub * step; t < n_rec; t += 8 * step) {
+                const float* r = src + (long long)t * kTdN;
+                double u = (double)__ldg(r + q);
+                if (q == 32) u += (double)__ldg(r + 37) + (double)__ldg(r + 38) + (double)__ldg(r + 39);
+                v = is_max ? fmax(v, u) : v + u;
             }
         }
 #pragma unroll
