@@ -29,9 +29,7 @@ struct K1GParams {
     int n_fft, log2n, nf;            // nf: frames transformed at once
     const float2* twg;               // [n_fft/2] exp(-2 pi i e / n_fft)
     const float* win;                // [n_fft] 0.5 * periodic hann
-    const int* mel_lo;               // [n_mels] first bin of the filter's support
-    const int* mel_len;              // [n_mels] bins in the support
-    const int* mel_off;              // [n_mels] offset of the filter's weights in mel_w
+    const int4* mel_meta;            // [n_mels] (first bin of the filter's support, bins in it, offset of its weights in mel_w, -)
     const float* mel_w;
     int pw_stride;                   // float2 entries per frame of the padded power column (odd)
     int off_pw, off_mel, off_S, off_red;
@@ -89,8 +87,9 @@ __global__ void __launch_bounds__(kGThreads, 3) k1g_features(const __grid_consta
                     const int f = k1g_div(it, mg_mp), m = it - f * p.n_mels_pad;
                     float aL = 0.0f, aR = 0.0f;
                     if (it < total && f < frames && m < p.n_mels) {
-                        const int lo = __ldg(g.mel_lo + m), len = __ldg(g.mel_len + m);
-                        const float* w = g.mel_w + __ldg(g.mel_off + m);
+                        const int4 mm = __ldg(g.mel_meta + m);
+                        const int lo = mm.x, len = mm.y;
+                        const float* w = g.mel_w + mm.z;
                         const float2* src = pw + (size_t)f * g.pw_stride;
                         for (int i = sub; i < len; i += 8) {
                             const float wi = __ldg(w + i);

@@ -12,7 +12,7 @@
 //   frame  = xpad[t hop + i]                      overlap-add, then the adjoint of the reflect padding
 //
 // One CTA per (tile of 8 frames, clip, stem).  The forward spectrum is recomputed (no activations are saved: the
-// forward writes only the log-mel), with K1G's shared-memory radix-4 FFT.  L and R share both transforms: forward as
+// forward writes only the log-mel), with the shared-memory FFT core of fftg.cuh.  L and R share both transforms: forward as
 // one complex FFT of L + iR; backward as one complex FFT of conj(Y), Y = Hermitian extension of G_L plus i times that
 // of G_R, whose inverse transform is dframe_L + i dframe_R.  Frames are overlap-added in shared memory; the tile's
 // span goes to global memory with atomicAdd (a sample receives at most two tiles' values when n_fft <= 9 hop, so
@@ -35,13 +35,9 @@ struct K6Params {
     const float2* twg;               // [n_fft/2]
     const float* win;                // [n_fft] 0.5 * periodic hann
     const float* win_br;             // the same, bit-reversed: win_br[p] = win[bitrev(p)]
-    const int* mel_lo;               // filterbank by filter (CSR): first bin, bins, weight offset
-    const int* mel_len;
-    const int* mel_off;
+    const int4* mel_meta;            // filterbank by filter (CSR): (first bin, bins, weight offset, -)
     const float* mel_w;
-    const int* bin_lo;               // filterbank by bin (CSR of the transpose): first filter, filters, weight offset
-    const int* bin_len;
-    const int* bin_off;
+    const int4* bin_meta;            // filterbank by bin (CSR of the transpose): (first filter, filters, weight offset, -)
     const float* bin_w;
     int pw_stride;                   // entries per frame of U and of the power column (both padded: k + (k >> pad_sh))
     int off_U, off_pw, off_mel, off_ola;
@@ -51,7 +47,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][fg_row(n)] padded rows (fftg.cuh)
     float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][pw_stride] (L.re, L.im, R.re, R.im)
-    float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power, then dP
+    float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power
     float2* const melb = reinterpret_cast<float2*>(smem + p.off_mel);        // [nf][n_mels_pad] dmel
     float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [2][span_pad]
 
@@ -91,8 +87,9 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
             const int f = k1g_div(idx, mg_mp), m = idx - f * p.n_mels_pad;
             float dL = 0.0f, dR = 0.0f;
             if (m < p.n_mels) {
-                const int lo = __ldg(p.mel_lo + m), len = __ldg(p.mel_len + m);
-                const float* w = p.mel_w + __ldg(p.mel_off + m);
+                const int4 mm = __ldg(p.mel_meta + m);
+                const int lo = mm.x, len = mm.y;
+                const float* w = p.mel_w + mm.z;
                 const float2* src = pw + (size_t)f * p.pw_stride;
                 float aL = 0.0f, aR = 0.0f;
                 for (int i = 0; i < len; ++i) {
@@ -108,35 +105,31 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
             melb[idx] = make_float2(dL, dR);
         }
         __syncthreads();
-        // ---- dP[k] = sum_m fb[k][m] dmel[m] (overwrites the power column) ----------------------------
-        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
-            const int lo = __ldg(p.bin_lo + k), len = __ldg(p.bin_len + k);
-            const float* w = p.bin_w + __ldg(p.bin_off + k);
-            const float2* src = melb + (size_t)f * p.n_mels_pad + lo;
-            float aL = 0.0f, aR = 0.0f;
-            for (int i = 0; i < len; ++i) {
-                const float wi = __ldg(w + i);
-                const float2 v = src[i];
-                aL = fmaf(wi, v.x, aL);
-                aR = fmaf(wi, v.y, aR);
-            }
-            pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)] = make_float2(aL, aR);
-        }
-        __syncthreads();
-        // ---- conj(Y) in natural order: G = 2 X dP, Hermitian extension, L + iR packing ------------------
-        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
-            const float4 u = U[(size_t)f * p.pw_stride + k + (k >> pad_sh)];
-            const float2 dp = pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)];
-            const float a = 2.0f * u.x * dp.x, bi = 2.0f * u.y * dp.x;       // G_L = a + i bi
-            const float c = 2.0f * u.z * dp.y, di = 2.0f * u.w * dp.y;       // G_R = c + i di
-            float2* zf = z + f * zs;
-            if (k == 0 || k == half) {
-                zf[fg_pad(k)] = make_float2(a, -c);
-            } else {
-                zf[fg_pad(k)] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
-                zf[fg_pad(n - k)] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
+        // ---- dP[k] = sum_m fb[k][m] dmel[m]; G = 2 X dP; conj of the Hermitian extension, L + iR packing, natural
+        //      order.  One thread per bin: its filter range is read once for all frames of the group. ---------------
+        for (int k = tid; k <= half; k += kGThreads) {
+            const int4 bm = __ldg(p.bin_meta + k);
+            const float* w = p.bin_w + bm.z;
+            const int ko = k + (k >> pad_sh);
+            for (int f = 0; f < frames; ++f) {
+                const float2* src = melb + (size_t)f * p.n_mels_pad + bm.x;
+                float dL = 0.0f, dR = 0.0f;
+                for (int i = 0; i < bm.y; ++i) {
+                    const float wi = __ldg(w + i);
+                    const float2 v = src[i];
+                    dL = fmaf(wi, v.x, dL);
+                    dR = fmaf(wi, v.y, dR);
+                }
+                const float4 u = U[(size_t)f * p.pw_stride + ko];
+                const float a = 2.0f * u.x * dL, bi = 2.0f * u.y * dL;       // G_L = a + i bi
+                const float c = 2.0f * u.z * dR, di = 2.0f * u.w * dR;       // G_R = c + i di
+                float2* zf = z + f * zs;
+                if (k == 0 || k == half) {
+                    zf[fg_pad(k)] = make_float2(a, -c);
+                } else {
+                    zf[fg_pad(k)] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
+                    zf[fg_pad(n - k)] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
+                }
             }
         }
         __syncthreads();

@@ -9,7 +9,7 @@
 // and the loss is the mean over resolutions of sc + lm (:433-446).
 //
 // k8_partials: one CTA per (tile of 8 frames, row = batch x channel).  x and y of a row share ONE complex FFT
-// (x + i y; K1G's shared-memory radix-4 passes) and are untangled like L/R in K1.  Per tile: sum (|Y| - |X|)^2,
+// (x + i y; the shared-memory FFT core of fftg.cuh) and are untangled like L/R in K1.  Per tile: sum (|Y| - |X|)^2,
 // sum |Y|^2, sum |log(|X| + 1e-5) - log(|Y| + 1e-5)| (fixed-order CTA reduction, no atomics).
 // k8_finish: fp64 sum of the tile partials in a fixed order -> {A, Bn, L1, sc, lm, alpha, beta} with
 //   alpha = 1 / ((sqrt(Bn) + 1e-8) sqrt(A)) (0 when A = 0), beta = 1 / count: the factors of d loss / d |X|.

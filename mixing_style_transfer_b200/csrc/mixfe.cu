@@ -202,7 +202,9 @@ int build_generic_tables(mixfe_plan* pl) {
     std::vector<float> win(n);
     for (int i = 0; i < n; ++i) win[i] = (float)(0.5 * (0.5 - 0.5 * std::cos(2.0 * M_PI * (double)i / (double)n)));
     int rc;
-    if ((rc = upload(&pl->d_mel_lo, lo)) || (rc = upload(&pl->d_mel_len, len)) || (rc = upload(&pl->d_mel_off, off)) ||
+    std::vector<int4> mel_meta(nm);
+    for (int m = 0; m < nm; ++m) mel_meta[m] = make_int4(lo[m], len[m], off[m], 0);
+    if ((rc = upload(&pl->d_mel_meta, mel_meta)) ||
         (rc = upload(&pl->d_mel_w, w)) || (rc = upload(&pl->d_twg, tw)) || (rc = upload(&pl->d_win, win)))
         return rc;
     pl->g_log2n = 0;
@@ -248,7 +250,9 @@ int build_generic_tables(mixfe_plan* pl) {
             }
         }
         if (bw.empty()) bw.push_back(0.0f);
-        if ((rc = upload(&pl->d_bin_lo, blo)) || (rc = upload(&pl->d_bin_len, blen)) || (rc = upload(&pl->d_bin_off, boff)) ||
+        std::vector<int4> bin_meta(blo.size());
+        for (size_t k = 0; k < blo.size(); ++k) bin_meta[k] = make_int4(blo[k], blen[k], boff[k], 0);
+        if ((rc = upload(&pl->d_bin_meta, bin_meta)) ||
             (rc = upload(&pl->d_bin_w, bw)))
             return rc;
         pl->b_span = (kTF - 1) * pl->hop + n;
@@ -341,7 +345,7 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         g.base = p;
         g.n_fft = pl->n_fft; g.log2n = pl->g_log2n; g.nf = pl->g_nf;
         g.twg = pl->d_twg; g.win = pl->d_win;
-        g.mel_lo = pl->d_mel_lo; g.mel_len = pl->d_mel_len; g.mel_off = pl->d_mel_off; g.mel_w = pl->d_mel_w;
+        g.mel_meta = pl->d_mel_meta; g.mel_w = pl->d_mel_w;
         g.pw_stride = pl->g_pw_stride; g.off_pw = pl->g_off_pw; g.off_mel = pl->g_off_mel; g.off_S = pl->g_off_S;
         g.off_red = pl->g_off_red;
         if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "K1G: B=%d > 65535 clips per call", B);
@@ -394,8 +398,8 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
     p.B = B; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
     p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span; p.span_pad = pl->b_span_pad;
     p.twg = pl->d_twg; p.win = pl->d_win; p.win_br = pl->d_win_br;
-    p.mel_lo = pl->d_mel_lo; p.mel_len = pl->d_mel_len; p.mel_off = pl->d_mel_off; p.mel_w = pl->d_mel_w;
-    p.bin_lo = pl->d_bin_lo; p.bin_len = pl->d_bin_len; p.bin_off = pl->d_bin_off; p.bin_w = pl->d_bin_w;
+    p.mel_meta = pl->d_mel_meta; p.mel_w = pl->d_mel_w;
+    p.bin_meta = pl->d_bin_meta; p.bin_w = pl->d_bin_w;
     p.pw_stride = pl->g_pw_stride;
     p.off_U = pl->b_off_U; p.off_pw = pl->b_off_pw; p.off_mel = pl->b_off_mel; p.off_ola = pl->b_off_ola;
     const int n_tiles = (p.F + kTF - 1) / kTF;
@@ -616,8 +620,8 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
-    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_win_br); cudaFree(pl->d_mel_lo); cudaFree(pl->d_mel_len); cudaFree(pl->d_mel_off);
-    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_lo); cudaFree(pl->d_bin_len); cudaFree(pl->d_bin_off); cudaFree(pl->d_bin_w);
+    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_win_br); cudaFree(pl->d_mel_meta);
+    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;
