@@ -250,3 +250,20 @@ def test_other_sample_rates_and_filter_counts(cuda_device, sr, n_mels):
     lm = pkg.MelSpectrogramPreprocessor(sr, 1024, 256, n_mels)({n: v[None] for n, v in dclip.items()})
     ref_lm = O.log_mel({n: v[None] for n, v in clip.items()}, cfg)
     assert float((lm.cpu() - ref_lm).abs().max()) < 5e-3
+
+
+@pytest.mark.parametrize("Tw,T", [(12001, 9000), (12002, 9000), (12003, 11000), (12004, 9000)])
+def test_aligned_base_with_unaligned_row_strides(fe, cuda_device, Tw, T):
+    """The first row is 16-byte aligned but the channel / clip strides are not multiples of 4 floats (Tw = 12001..12003):
+    later rows are misaligned, so the host must not pick the TMA staging for the launch.  Tw = 12004 is the aligned
+    control.  Same numbers as a contiguous copy, bit for bit in the log-mel."""
+    g = torch.Generator().manual_seed(Tw)
+    big = (torch.rand(3, 8, Tw, generator=g) * 2 - 1) * 0.3
+    dev_big = big.to(cuda_device)
+    views = {n: dev_big[:, 2 * i:2 * i + 2, :T] for i, n in enumerate(O.STEMS)}
+    f, lm = fe.features_and_logmel(views)
+    f2, lm2 = fe.features_and_logmel({n: v.contiguous() for n, v in views.items()})
+    assert torch.equal(lm, lm2)
+    assert torch.allclose(f, f2, rtol=1e-5, atol=1e-6)
+    clip = {n: big[2, 2 * i:2 * i + 2, :T].contiguous() for i, n in enumerate(O.STEMS)}
+    assert_features_close(f[2], O.mixing_features(clip), fe.feature_names(), f"Tw={Tw} clip 2")
