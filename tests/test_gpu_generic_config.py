@@ -130,3 +130,17 @@ def test_generic_kernel_on_training_config(cuda_device):
     env = dict(os.environ, MIXFE_FORCE_GENERIC="1")
     res = subprocess.run([sys.executable, "-c", _FORCED % root], env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and "forced-generic ok" in res.stdout, res.stdout + res.stderr
+
+
+@pytest.mark.parametrize("n_fft,hop,n_mels,nb", [(2048, 512, 80, 32), (2048, 512, 80, 80), (512, 128, 64, 1), (512, 128, 64, 2),
+                                                 (1024, 256, 96, 33), (1024, 300, 128, 127), (256, 64, 40, 7)])
+def test_detailed_spectral_mode_on_other_configurations(cuda_device, n_fft, hop, n_mels, nb):
+    """use_detailed_spectral=True (src/mixing_utils.py:200-224) with bin counts below, at and just under n_mels, on the
+    generic kernel and on K1 with a non-default filter count."""
+    cfg = O.FrontEndConfig(n_fft=n_fft, hop_length=hop, n_mels=n_mels, use_detailed_spectral=True, n_spectral_bins=nb)
+    T = 21013
+    clip = O.musical_clip(n_fft + nb, T)
+    fe = pkg.MixingFeatureExtractor(44100, n_fft, hop, n_mels, use_detailed_spectral=True, n_spectral_bins=nb)
+    assert fe.get_feature_dim() == cfg.feature_dim
+    got = fe.extract_all_features(_to(clip, cuda_device))
+    assert_features_close(got, O.mixing_features(clip, cfg), fe.feature_names(), f"{n_fft}/{hop}/{n_mels} detailed {nb}")
