@@ -1,6 +1,8 @@
 // Shared-memory FFT of `frames` rows of n complex points, n = 2^log2n in [64, 4096], used by K1G, K6 and K8.
 //
-// Decimation in frequency, in place, result in bit-reversed order (X[k] at position bitrev(k)).  log2n is split into
+// fg_fft: decimation in frequency, in place, result in bit-reversed order (X[k] at position bitrev(k)); fg_fft_dit:
+// decimation in time, from bit-reversed to natural order (K6 runs its inverse transform with it, in place on the
+// spectrum fg_fft left).  log2n is split into
 // passes of 3 or 4 radix-2 stages; in a pass one thread owns the 2^R points that those stages combine (spacing hs),
 // holds them in registers, and touches shared memory once to read and once to write them: 3 round trips for 512..4096
 // points instead of one per two stages.  The twiddle of stage t for the point at offset j + mm * hs of its half is
@@ -142,6 +144,69 @@ __device__ __forceinline__ void fg_fft(float2* z, const float2* __restrict__ tw,
         if (R == 4) fg_pass<4>(z, tw, log2n, frames, lh, tid);
         else fg_pass<3>(z, tw, log2n, frames, lh, tid);
         lh -= R;
+        __syncthreads();
+    }
+}
+
+// Decimation in time: the mirror image.  Input in bit-reversed order (element k at position bitrev(k)), output in
+// natural order.  One pass of R stages, the first with half-size h0 = 2^lh0, the last with h0 * 2^(R-1); a thread owns
+// the 2^R points base + j + m h0.  Stage t multiplies the upper point of a pair by
+//   exp(-2 pi i (j + mm h0) / (2 h0 2^t)) = tw[j * n / (2 h0 2^t)] * exp(-2 pi i mm / 2^(t+1))   before the butterfly.
+template <int R>
+__device__ __forceinline__ void fg_pass_dit(float2* z, const float2* __restrict__ tw, int log2n, int frames, int lh0, int tid) {
+    constexpr int P = 1 << R;
+    const int h0 = 1 << lh0;
+    const int lq = log2n - R;
+    const int zs = fg_row(1 << log2n);
+    const int total = frames << lq;
+    for (int idx = tid; idx < total; idx += kGThreads) {
+        const int f = idx >> lq, q = idx & ((1 << lq) - 1);
+        const int g = q >> lh0, j = q & (h0 - 1);
+        const int base = (g << (lh0 + R)) + j;
+        float2* row = z + f * zs;
+        float2 v[P];
+        if (lh0 >= 3) {
+            float2* r = row + fg_pad(base);
+            const int sp = h0 + (h0 >> 3);
+#pragma unroll
+            for (int m = 0; m < P; ++m) v[m] = r[m * sp];
+        } else {
+#pragma unroll
+            for (int m = 0; m < P; ++m) v[m] = row[fg_pad(base + (m << lh0))];
+        }
+#pragma unroll
+        for (int t = 0; t < R; ++t) {
+            const int dm = 1 << t;
+            const float2 wj = __ldg(tw + (j << (log2n - 1 - lh0 - t)));
+#pragma unroll
+            for (int a = 0; a < P; ++a) {
+                if (a & dm) continue;
+                const int b = a + dm, mm = a & (dm - 1);
+                const float2 tb = fg_mul_w16(cmulf(v[b], wj), mm * (8 >> t));
+                v[b] = make_float2(v[a].x - tb.x, v[a].y - tb.y);
+                v[a] = make_float2(v[a].x + tb.x, v[a].y + tb.y);
+            }
+        }
+        if (lh0 >= 3) {
+            float2* r = row + fg_pad(base);
+            const int sp = h0 + (h0 >> 3);
+#pragma unroll
+            for (int m = 0; m < P; ++m) r[m * sp] = v[m];
+        } else {
+#pragma unroll
+            for (int m = 0; m < P; ++m) row[fg_pad(base + (m << lh0))] = v[m];
+        }
+    }
+}
+
+__device__ __forceinline__ void fg_fft_dit(float2* z, const float2* __restrict__ tw, int log2n, int frames, int tid) {
+    const int passes = (log2n + 3) >> 2, base = log2n / passes, extra = log2n - base * passes;
+    int lh0 = 0;
+    for (int ps = 0; ps < passes; ++ps) {
+        const int R = base + (ps < extra ? 1 : 0);
+        if (R == 4) fg_pass_dit<4>(z, tw, log2n, frames, lh0, tid);
+        else fg_pass_dit<3>(z, tw, log2n, frames, lh0, tid);
+        lh0 += R;
         __syncthreads();
     }
 }

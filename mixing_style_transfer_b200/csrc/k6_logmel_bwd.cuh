@@ -34,19 +34,18 @@ struct K6Params {
     int span_pad;                    // floats per channel of the padded overlap-add span
     const float2* twg;               // [n_fft/2]
     const float* win;                // [n_fft] 0.5 * periodic hann
-    const float* win_br;             // the same, bit-reversed: win_br[p] = win[bitrev(p)]
     const int4* mel_meta;            // filterbank by filter (CSR): (first bin, bins, weight offset, -)
     const float* mel_w;
-    const int4* bin_meta;            // filterbank by bin (CSR of the transpose): (first filter, filters, weight offset, -)
+    const int4* bin_meta;            // filterbank by bin (CSR of the transpose): (first filter, filters, weight offset, -),
+                                     // entry i for bin bitrev_{log2n-1}(i), entry n/2 for the Nyquist bin
     const float* bin_w;
-    int pw_stride;                   // entries per frame of U and of the power column (both padded: k + (k >> pad_sh))
-    int off_U, off_pw, off_mel, off_ola;
+    int pw_stride;                   // entries per frame of the padded power column (k + (k >> pad_sh))
+    int off_pw, off_mel, off_ola;
 };
 
 __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_constant__ K6Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][fg_row(n)] padded rows (fftg.cuh)
-    float4* const U = reinterpret_cast<float4*>(smem + p.off_U);             // [nf][pw_stride] (L.re, L.im, R.re, R.im)
     float2* const pw = reinterpret_cast<float2*>(smem + p.off_pw);           // [nf][pw_stride] power
     float2* const melb = reinterpret_cast<float2*>(smem + p.off_mel);        // [nf][n_mels_pad] dmel
     float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [2][span_pad]
@@ -71,15 +70,14 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
         __syncthreads();
         fg_fft(z, p.twg, p.log2n, frames, tid);
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            // lane i takes bin k = bitrev_{log2n-1}(i) (k1g_features' untangle); U and the power column are padded
+            // lane i takes bin k = bitrev_{log2n-1}(i) (k1g_features' untangle); the power column is padded.  The
+            // spectrum itself stays in z: the gradient stage below reads it again and overwrites it in place.
             const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
             const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
             const float2 x = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
             const float2 y = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
             const float a = x.x + y.x, bb = x.y - y.y, c = x.x - y.x, d = x.y + y.y;
-            const size_t o = (size_t)f * p.pw_stride + k + (k >> pad_sh);
-            U[o] = make_float4(a, bb, d, -c);                                // L = a + i bb, R = d - i c
-            pw[o] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
+            pw[(size_t)f * p.pw_stride + k + (k >> pad_sh)] = make_float2(fmaf(a, a, bb * bb), fmaf(d, d, c * c));
         }
         __syncthreads();
         // ---- mel, then dmel = g / (mel + 1e-10) ---------------------------------------------------
@@ -105,46 +103,48 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
             melb[idx] = make_float2(dL, dR);
         }
         __syncthreads();
-        // ---- dP[k] = sum_m fb[k][m] dmel[m]; G = 2 X dP; conj of the Hermitian extension, L + iR packing, natural
-        //      order.  One thread per bin: its filter range is read once for all frames of the group. ---------------
-        for (int k = tid; k <= half; k += kGThreads) {
-            const int4 bm = __ldg(p.bin_meta + k);
+        // ---- dP[k] = sum_m fb[k][m] dmel[m]; G = 2 X dP; conj of the Hermitian extension of G_L + i G_R, written IN
+        //      PLACE over X[k] and X[n-k] (element k of the inverse transform's input at position bitrev(k), which is
+        //      what the decimation-in-time passes take).  One thread per bin, lane i on bin bitrev(i) as in the
+        //      untangle; the bin's filter range is read once for all frames of the group. -------------------------
+        for (int i = tid; i <= half; i += kGThreads) {
+            const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
+            const int4 bm = __ldg(p.bin_meta + i);           // the table is in lane order (mixfe.cu)
             const float* w = p.bin_w + bm.z;
-            const int ko = k + (k >> pad_sh);
+            const int px = fg_pad((int)(__brev((unsigned)k) >> sh));
+            const int py = fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh));
             for (int f = 0; f < frames; ++f) {
                 const float2* src = melb + (size_t)f * p.n_mels_pad + bm.x;
                 float dL = 0.0f, dR = 0.0f;
-                for (int i = 0; i < bm.y; ++i) {
-                    const float wi = __ldg(w + i);
-                    const float2 v = src[i];
+                for (int q = 0; q < bm.y; ++q) {
+                    const float wi = __ldg(w + q);
+                    const float2 v = src[q];
                     dL = fmaf(wi, v.x, dL);
                     dR = fmaf(wi, v.y, dR);
                 }
-                const float4 u = U[(size_t)f * p.pw_stride + ko];
-                const float a = 2.0f * u.x * dL, bi = 2.0f * u.y * dL;       // G_L = a + i bi
-                const float c = 2.0f * u.z * dR, di = 2.0f * u.w * dR;       // G_R = c + i di
                 float2* zf = z + f * zs;
+                const float2 x = zf[px], y = zf[py];
+                const float xa = x.x + y.x, xb = x.y - y.y, xc = x.x - y.x, xd = x.y + y.y;   // L = xa + i xb, R = xd - i xc
+                const float a = 2.0f * xa * dL, bi = 2.0f * xb * dL;         // G_L = a + i bi
+                const float c = 2.0f * xd * dR, di = -2.0f * xc * dR;        // G_R = c + i di
                 if (k == 0 || k == half) {
-                    zf[fg_pad(k)] = make_float2(a, -c);
+                    zf[px] = make_float2(a, -c);
                 } else {
-                    zf[fg_pad(k)] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
-                    zf[fg_pad(n - k)] = make_float2(0.5f * (a + di), -0.5f * (c - bi));  // conj of (conj G_L + i conj G_R) / 2
+                    zf[px] = make_float2(0.5f * (a - di), -0.5f * (bi + c));      // conj of (G_L + i G_R) / 2
+                    zf[py] = make_float2(0.5f * (a + di), -0.5f * (c - bi));      // conj of (conj G_L + i conj G_R) / 2
                 }
             }
         }
         __syncthreads();
-        // ---- inverse transform = conj(FFT(conj Y)) ------------------------------------------------------
-        fg_fft(z, p.twg, p.log2n, frames, tid);
+        // ---- inverse transform = conj(FFT(conj Y)), bit-reversed in, natural order out -----------------------
+        fg_fft_dit(z, p.twg, p.log2n, frames, tid);
         // ---- window and overlap-add, one frame after the other (frames overlap) ------------------------
-        // A thread walks the positions of the bit-reversed result (neighbouring words of z, the window read from its
-        // bit-reversed copy) and adds at sample i = bitrev(position); the span is padded (q + (q >> ola_sh)) so that
-        // the 32 samples of a warp, n/32 apart, fall into 32 banks.
         for (int f = 0; f < frames; ++f) {
             const int q0 = (f0 + f) * p.hop;
-            for (int pos = tid; pos < n; pos += kGThreads) {
-                const float2 r = z[f * zs + fg_pad(pos)];
-                const float w = 2.0f * __ldg(p.win_br + pos);
-                const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
+            for (int i = tid; i < n; i += kGThreads) {
+                const float2 r = z[f * zs + fg_pad(i)];
+                const float w = 2.0f * __ldg(p.win + i);
+                const int q = q0 + i;
                 const int o = q + (q >> ola_sh);
                 ola[o] = fmaf(w, r.x, ola[o]);
                 ola[p.span_pad + o] = fmaf(-w, r.y, ola[p.span_pad + o]);

@@ -35,9 +35,8 @@ struct K8Params {
     const float* gscale;             // device scalar: upstream gradient / n_resolutions   (backward)
     float* gx;                       // gradient of x, zero-initialised by the caller, addressing gs_b, gs_c (backward)
     long long gs_b, gs_c;
-    int u_stride, span_pad;          // padded row of U (k + (k >> pad_sh)), padded overlap-add span (q + (q >> ola_sh))
-    const float* win_br;             // window in bit-reversed order
-    int off_U, off_ola, off_red;
+    int span_pad;                    // padded overlap-add span (q + (q >> ola_sh))
+    int off_ola, off_red;
 };
 
 __device__ __forceinline__ void k8_load_fft(const K8Params& p, float2* z, const float* xr, const float* yr, int t0, int f0,
@@ -122,8 +121,7 @@ __global__ void __launch_bounds__(256) k8_finish(const K8Params p) {
 
 __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constant__ K8Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][n]
-    float2* const U = reinterpret_cast<float2*>(smem + p.off_U);             // [nf][u_stride] G = d loss / d X
+    float2* const z = reinterpret_cast<float2*>(smem);                       // [nf][fg_row(n)] padded rows (fftg.cuh)
     float* const ola = reinterpret_cast<float*>(smem + p.off_ola);           // [span_pad]
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, row = blockIdx.y;
@@ -133,7 +131,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constan
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const float* xr = p.x + (long long)(row / p.C) * p.xs_b + (long long)(row % p.C) * p.xs_c;
     const float* yr = p.y + (long long)(row / p.C) * p.ys_b + (long long)(row % p.C) * p.ys_c;
-    const int pad_sh = p.log2n > 6 ? p.log2n - 6 : 31, ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
+    const int ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
     const float gs = __ldg(p.gscale);
     const float alpha = (float)p.state[5] * gs, beta = (float)p.state[6] * gs;
 
@@ -144,39 +142,35 @@ __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constan
         for (int idx = tid; idx < frames * nb; idx += kGThreads) {
             const int f = k1g_div(idx, mg_nb), i = idx - f * nb;
             const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));
-            const float2 u = z[f * zs + fg_pad((int)(__brev((unsigned)k) >> sh))];
-            const float2 v = z[f * zs + fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh))];
+            float2* zf = z + f * zs;
+            const int px = fg_pad((int)(__brev((unsigned)k) >> sh));
+            const int py = fg_pad((int)(__brev((unsigned)((n - k) & (n - 1))) >> sh));
+            const float2 u = zf[px], v = zf[py];
             const float a = u.x + v.x, bb = u.y - v.y, c = u.x - v.x, d = u.y + v.y;   // X = a + i bb, Y = d - i c
             const float mx = sqrtf(fmaf(a, a, bb * bb)), my = sqrtf(fmaf(d, d, c * c));
             const float dl = logf(mx + 1e-5f) - logf(my + 1e-5f);
             const float sg = dl > 0.0f ? 1.0f : (dl < 0.0f ? -1.0f : 0.0f);
             const float gm = fmaf(alpha, mx - my, beta * sg / (mx + 1e-5f));            // d loss / d |X|
             const float inv = mx > 0.0f ? gm / mx : 0.0f;
-            U[(size_t)f * p.u_stride + k + (k >> pad_sh)] = make_float2(inv * a, inv * bb);
-        }
-        __syncthreads();
-        // conj of the Hermitian extension of G, natural order (the imaginary slot of the packed transform stays empty)
-        for (int idx = tid; idx < frames * nb; idx += kGThreads) {
-            const int f = k1g_div(idx, mg_nb), k = idx - f * nb;
-            const float2 g = U[(size_t)f * p.u_stride + k + (k >> pad_sh)];
-            float2* zf = z + f * zs;
+            const float gx = inv * a, gy = inv * bb;                                    // G = d loss / d X
+            // conj of the Hermitian extension of G, IN PLACE over the two spectrum entries it came from: element k of the
+            // inverse transform's input at position bitrev(k) (the imaginary slot of the packed transform stays empty)
             if (k == 0 || k == half) {
-                zf[fg_pad(k)] = make_float2(g.x, 0.0f);
+                zf[px] = make_float2(gx, 0.0f);
             } else {
-                zf[fg_pad(k)] = make_float2(0.5f * g.x, -0.5f * g.y);
-                zf[fg_pad(n - k)] = make_float2(0.5f * g.x, 0.5f * g.y);
+                zf[px] = make_float2(0.5f * gx, -0.5f * gy);
+                zf[py] = make_float2(0.5f * gx, 0.5f * gy);
             }
         }
         __syncthreads();
-        fg_fft(z, p.twg, p.log2n, frames, tid);
-        // positions of the bit-reversed result in order, padded span (k6_logmel_bwd's overlap-add)
+        fg_fft_dit(z, p.twg, p.log2n, frames, tid);              // bit-reversed in, natural order out
         for (int f = 0; f < frames; ++f) {
             const int q0 = (f0 + f) * p.hop;
-            for (int pos = tid; pos < n; pos += kGThreads) {
-                const float2 r = z[f * zs + fg_pad(pos)];
-                const int q = q0 + (int)(__brev((unsigned)pos) >> sh);
+            for (int i = tid; i < n; i += kGThreads) {
+                const float2 r = z[f * zs + fg_pad(i)];
+                const int q = q0 + i;
                 const int o = q + (q >> ola_sh);
-                ola[o] = fmaf(2.0f * __ldg(p.win_br + pos), r.x, ola[o]);
+                ola[o] = fmaf(2.0f * __ldg(p.win + i), r.x, ola[o]);
             }
             __syncthreads();
         }

@@ -209,15 +209,6 @@ int build_generic_tables(mixfe_plan* pl) {
         return rc;
     pl->g_log2n = 0;
     while ((1 << pl->g_log2n) < n) ++pl->g_log2n;
-    {
-        std::vector<float> win_br(n);                 // window in the FFT's output order, for the overlap-add loops
-        for (int q = 0; q < n; ++q) {
-            int r = 0;
-            for (int bit = 0; bit < pl->g_log2n; ++bit) r |= ((q >> bit) & 1) << (pl->g_log2n - 1 - bit);
-            win_br[q] = win[r];
-        }
-        if ((rc = upload(&pl->d_win_br, win_br))) return rc;
-    }
     pl->g_pw_stride = (n / 2 + 1 + (pl->g_log2n > 6 ? (n / 2) >> (pl->g_log2n - 6) : 0)) | 1;   // k + (k >> pad_sh), k <= n/2
     const int per_frame = fg_row(n) * 8 + pl->g_pw_stride * 8;
     int nfr = kTF;
@@ -237,35 +228,39 @@ int build_generic_tables(mixfe_plan* pl) {
     MIXFE_CUDA(cudaFuncSetAttribute(k1g_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_g));
     // K6 (log-mel backward): filterbank by bin + its shared-memory map
     {
-        std::vector<int> blo(nf, 0), blen(nf, 0), boff(nf, 0);
+        // Entry i describes bin k = bitrev_{log2n-1}(i) (i = n/2: the Nyquist bin): K6's lane i works on that bin
+        // (k6_logmel_bwd.cuh), so the table and the weights are laid out in the order the lanes read them.
+        std::vector<int4> bin_meta(nf);
         std::vector<float> bw;
-        for (int k = 0; k < nf; ++k) {
+        for (int i = 0; i < nf; ++i) {
+            int k = n / 2;
+            if (i < n / 2) {
+                k = 0;
+                for (int bit = 0; bit < pl->g_log2n - 1; ++bit) k |= ((i >> bit) & 1) << (pl->g_log2n - 2 - bit);
+            }
             int first = -1, last = -1;
             for (int m = 0; m < nm; ++m)
                 if (pl->fb[(size_t)k * nm + m] != 0.0f) { if (first < 0) first = m; last = m; }
-            boff[k] = (int)bw.size();
+            bin_meta[i] = make_int4(0, 0, (int)bw.size(), 0);
             if (first >= 0) {
-                blo[k] = first; blen[k] = last - first + 1;
+                bin_meta[i].x = first; bin_meta[i].y = last - first + 1;
                 for (int m = first; m <= last; ++m) bw.push_back(pl->fb[(size_t)k * nm + m]);
             }
         }
         if (bw.empty()) bw.push_back(0.0f);
-        std::vector<int4> bin_meta(blo.size());
-        for (size_t k = 0; k < blo.size(); ++k) bin_meta[k] = make_int4(blo[k], blen[k], boff[k], 0);
         if ((rc = upload(&pl->d_bin_meta, bin_meta)) ||
             (rc = upload(&pl->d_bin_w, bw)))
             return rc;
         pl->b_span = (kTF - 1) * pl->hop + n;
         pl->b_span_pad = pl->b_span + (pl->g_log2n > 5 ? pl->b_span >> (pl->g_log2n - 5) : 0) + 1;
-        const int per = fg_row(n) * 8 + pl->g_pw_stride * 16 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
+        const int per = fg_row(n) * 8 + pl->g_pw_stride * 8 + pl->n_mels_pad * 8;
         const int ola = align16(2 * pl->b_span_pad * 4);
         int bn = kTF;
         const char* e6 = getenv("MIXFE_K6_SMEM_KB");
         const int budget6 = (e6 ? atoi(e6) : 72) * 1024;
         while (bn > 1 && bn * per + ola + 64 > budget6) bn >>= 1;
         pl->b_nf = bn;
-        pl->b_off_U = bn * fg_row(n) * 8;
-        pl->b_off_pw = pl->b_off_U + bn * pl->g_pw_stride * 16;
+        pl->b_off_pw = bn * fg_row(n) * 8;
         pl->b_off_mel = pl->b_off_pw + bn * pl->g_pw_stride * 8;
         pl->b_off_ola = align16(pl->b_off_mel + bn * pl->n_mels_pad * 8);
         pl->smem_b = pl->b_off_ola + ola;
@@ -397,11 +392,11 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
     p.g = grad_logmel; p.g_stride_b = g_stride_b;
     p.B = B; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
     p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span; p.span_pad = pl->b_span_pad;
-    p.twg = pl->d_twg; p.win = pl->d_win; p.win_br = pl->d_win_br;
+    p.twg = pl->d_twg; p.win = pl->d_win;
     p.mel_meta = pl->d_mel_meta; p.mel_w = pl->d_mel_w;
     p.bin_meta = pl->d_bin_meta; p.bin_w = pl->d_bin_w;
     p.pw_stride = pl->g_pw_stride;
-    p.off_U = pl->b_off_U; p.off_pw = pl->b_off_pw; p.off_mel = pl->b_off_mel; p.off_ola = pl->b_off_ola;
+    p.off_pw = pl->b_off_pw; p.off_mel = pl->b_off_mel; p.off_ola = pl->b_off_ola;
     const int n_tiles = (p.F + kTF - 1) / kTF;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_LOGMEL_BWD, stream);
@@ -486,8 +481,7 @@ int stft_loss_common(mixfe_plan* pl, const float* x, const float* y, int B, int 
     p.rows = B * C; p.C = C; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_fft = pl->n_fft; p.log2n = pl->g_log2n;
     p.n_tiles = (p.F + kTF - 1) / kTF; p.span = (kTF - 1) * pl->hop + pl->n_fft;
     p.span_pad = p.span + (pl->g_log2n > 5 ? p.span >> (pl->g_log2n - 5) : 0) + 1;
-    p.u_stride = pl->g_pw_stride;
-    p.twg = pl->d_twg; p.win = pl->d_win; p.win_br = pl->d_win_br;
+    p.twg = pl->d_twg; p.win = pl->d_win;
     return MIXFE_OK;
 }
 
@@ -533,13 +527,12 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     if (gs_c < T) return fail(MIXFE_EINVAL, "gradient channel stride smaller than T");
     if (B == 0) return MIXFE_OK;
     DeviceGuard guard(pl->device);
-    const int per = fg_row(pl->n_fft) * 8 + p.u_stride * 8, ola = align16(p.span_pad * 4);
+    const int per = fg_row(pl->n_fft) * 8, ola = align16(p.span_pad * 4);
     if (per + ola > 200 * 1024) return fail(MIXFE_EUNSUPPORTED, "STFT loss backward: hop=%d needs too much shared memory", pl->hop);
     int nf = kTF;
     while (nf > 1 && nf * per + ola > 64 * 1024) nf >>= 1;
     p.nf = nf;
-    p.off_U = nf * fg_row(pl->n_fft) * 8;
-    p.off_ola = align16(p.off_U + nf * p.u_stride * 8);
+    p.off_ola = align16(nf * fg_row(pl->n_fft) * 8);
     const int smem = p.off_ola + ola;
     if (!pl->k8_attr_done) {
         MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -620,7 +613,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
-    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_win_br); cudaFree(pl->d_mel_meta);
+    cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;

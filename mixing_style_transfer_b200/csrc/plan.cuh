@@ -22,12 +22,11 @@ struct mixfe_plan {
     bool use_generic = false;
     float2* d_twg = nullptr;            // [n_fft/2] exp(-2 pi i e / n_fft)
     float* d_win = nullptr;             // [n_fft] 0.5 * periodic hann
-    float* d_win_br = nullptr;          // [n_fft] the same in bit-reversed order
     int4* d_mel_meta = nullptr;         // CSR form of the filterbank: (first bin, bins, weight offset, -) per filter
     float* d_mel_w = nullptr;
     int4* d_bin_meta = nullptr;         // CSR of the transposed filterbank (K6): (first filter, filters, weight offset, -) per bin
     float* d_bin_w = nullptr;
-    int b_nf = 0, b_span = 0, b_span_pad = 0, b_off_U = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)
+    int b_nf = 0, b_span = 0, b_span_pad = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)
     int g_nf = 0, g_log2n = 0, g_pw_stride = 0, g_off_pw = 0, g_off_mel = 0, g_off_S = 0, g_off_red = 0, smem_g = 0;
     // plan-owned workspace (grows to the high-water mark, then never reallocates)
     void* ws = nullptr;
