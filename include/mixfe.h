@@ -106,6 +106,15 @@ int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_S
 int mixfe_gated_loudness(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                          long long stride_b, long long stride_c, int B, int T, float* lufs, void* cuda_stream);
 
+/* EXTENSION (same status as mixfe_gated_loudness): the proposal's dynamic-range descriptor
+ * DR_IQR = IQR(L_short(t)) (Mixing_Style_Representation_Learning_Proposal.pdf p.2 section 2.1; no code in the
+ * reference).  Short-term loudness = K-weighted loudness of 3 s windows every 100 ms (EBU Tech 3341); windows under
+ * -70 LUFS are dropped; iqr = q75 - q25 of the rest, linear interpolation between order statistics.  iqr: device
+ * [B][5] fp32 in LU = vocals, bass, drums, other, mixture (0 when fewer than two windows remain).  Needs
+ * sample_rate % 10 == 0 and 3 s <= T <= 6 min 52 s (MIXFE_EINVAL / MIXFE_EUNSUPPORTED otherwise). */
+int mixfe_short_term_loudness_iqr(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
+                                  long long stride_b, long long stride_c, int B, int T, float* iqr, void* cuda_stream);
+
 /* Replaces ONE resolution of MultiResolutionSTFTLoss.forward (src/loss.py:332-448; the cycle loss of
  * src/train_style_transfer.py:239) and its autograd.  The plan's (n_fft, hop) is the resolution (win = n_fft, periodic
  * Hann, center=True, reflect).  x (prediction), y (target): device fp32, element (b, c, t) at

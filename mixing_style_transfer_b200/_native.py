@@ -73,7 +73,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_set_filterbank", "mixfe_feature_dim", "mixfe_num_frames", "mixfe_workspace_bytes",
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
-           "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness",
+           "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
            "mixfe_stft_loss_forward", "mixfe_stft_loss_backward")
 
 
@@ -110,6 +110,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
         L.mixfe_gated_loudness.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
+        L.mixfe_short_term_loudness_iqr.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
         L.mixfe_stft_loss_forward.argtypes = [vp, vp, vp, ci, ci, ci, ll, ll, ll, ll, vp, vp]
         L.mixfe_stft_loss_backward.argtypes = [vp, vp, vp, ci, ci, ci, ll, ll, ll, ll, vp, vp, vp, ll, ll, vp]
         L.mixfe_plan_enable_timing.argtypes = [vp, ci]
@@ -283,6 +284,17 @@ class Plan:
         ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
         with torch.cuda.device(self.device):
             _check(lib().mixfe_gated_loudness(self._h, ptrs, sb, sc, B, T, _ptr(out), _stream(self.device)))
+        return out
+
+    def short_term_loudness_iqr(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
+        """(B,5) inter-quartile range of the short-term (3 s / 100 ms) K-weighted loudness in LU, same order (kernel K7;
+        extension: the proposal's DR_IQR)."""
+        st, sb, sc = unify_stems(stems)
+        B, _, T = st[0].shape
+        out = torch.empty((B, 5), dtype=torch.float32, device=self.device)
+        ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_short_term_loudness_iqr(self._h, ptrs, sb, sc, B, T, _ptr(out), _stream(self.device)))
         return out
 
     def debug_mel_power(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:

@@ -10,6 +10,11 @@
 // r^warm < 1e-13.  The squares of the filtered samples are summed per 100 ms sub-block (a gating block is four
 // consecutive sub-blocks): two running bins per 512-sample step, fixed-order warp reductions, no atomics.
 // k7_gate: one warp per (clip, signal): block loudness, absolute gate (-70 LUFS), relative gate (-10 LU), LUFS.
+// k7_short_iqr: the proposal's dynamic-range descriptor DR_IQR = IQR(L_short(t)) (proposal p.2 section 2.1; not in the
+//   reference's code either): short-term loudness over 3 s windows (30 sub-blocks) every 100 ms as EBU Tech 3341
+//   defines it, windows under the absolute gate (-70 LUFS) dropped, inter-quartile range q75 - q25 of the rest with
+//   linear interpolation between order statistics (numpy.quantile's default).  One CTA per (clip, signal): the windows
+//   are formed from the sub-block energies, sorted in shared memory (bitonic), and the two quantiles read off.
 #pragma once
 
 #include "k3_augment.cuh"
@@ -18,6 +23,9 @@ namespace mixfe {
 
 constexpr int kLoudSignals = kNumStems + 1;
 constexpr int kLoudMaxSubs = 8;            // sub-blocks per chunk
+constexpr int kShortSubs = 30;             // sub-blocks per short-term window (3 s)
+constexpr int kShortMaxWin = 4096;         // windows per clip the sort holds (6 min 52 s of audio)
+constexpr int kShortThreads = 256;
 
 struct K7Params {
     const float* stem[kNumStems];
@@ -26,6 +34,7 @@ struct K7Params {
     double sos[2][5];                                // b0 b1 b2 a1 a2: high shelf, high-pass
     double* sub_energy;                              // [B][5][2][n_sub]
     float* out;                                      // [B][5] LUFS
+    float* out_iqr;                                  // [B][5] LU (k7_short_iqr)
 };
 
 __global__ void __launch_bounds__(kLoudSignals * 32) k7_kweight_energy(const __grid_constant__ K7Params p) {
@@ -145,6 +154,61 @@ __global__ void __launch_bounds__(kLoudSignals * 32) k7_gate(const K7Params p) {
         if (cnt > 0.0) lufs = -0.691 + 10.0 * log10(sL / cnt + sR / cnt);
     }
     if (lane == 0) p.out[(long long)b * kLoudSignals + sig] = (float)lufs;
+}
+
+__global__ void __launch_bounds__(kShortThreads) k7_short_iqr(const K7Params p) {
+    __shared__ double val[kShortMaxWin];
+    __shared__ int n_valid;
+    const int tid = threadIdx.x, sig = blockIdx.x, b = blockIdx.y;
+    const double* eL = p.sub_energy + ((long long)b * kLoudSignals + sig) * 2 * p.n_sub;
+    const double* eR = eL + p.n_sub;
+    const int n_win = p.n_sub - (kShortSubs - 1);
+    int N = 2;
+    while (N < n_win) N <<= 1;
+    if (tid == 0) n_valid = 0;
+    __syncthreads();
+    const double inv = 1.0 / ((double)kShortSubs * (double)p.sub);
+    int mine = 0;
+    for (int j = tid; j < N; j += kShortThreads) {
+        double l = INFINITY;                                   // padding and gated windows sort to the end
+        if (j < n_win) {
+            double zL = 0.0, zR = 0.0;
+            for (int q = 0; q < kShortSubs; ++q) { zL += eL[j + q]; zR += eR[j + q]; }
+            const double v = -0.691 + 10.0 * log10((zL + zR) * inv);
+            if (v >= -70.0) { l = v; ++mine; }
+        }
+        val[j] = l;
+    }
+    if (mine) atomicAdd(&n_valid, mine);
+    __syncthreads();
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < N; i += kShortThreads) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const double a = val[i], c = val[ixj];
+                    const bool up = (i & k) == 0;
+                    if ((a > c) == up) { val[i] = c; val[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (tid == 0) {
+        const int n = n_valid;
+        float r = 0.0f;
+        if (n >= 2) {
+            auto quant = [&](double q) {
+                const double pos = q * (double)(n - 1);
+                const int i0 = (int)pos;
+                const int i1 = i0 + 1 < n ? i0 + 1 : i0;
+                const double fr = pos - (double)i0;
+                return val[i0] + (val[i1] - val[i0]) * fr;
+            };
+            r = (float)(quant(0.75) - quant(0.25));
+        }
+        p.out_iqr[(long long)b * kLoudSignals + sig] = r;
+    }
 }
 
 }  // namespace mixfe

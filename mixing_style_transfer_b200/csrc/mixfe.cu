@@ -425,15 +425,20 @@ void k_weighting(double fs, double (&sos)[2][5]) {
     }
 }
 
+// out: integrated loudness (k7_gate) or NULL; out_iqr: short-term-loudness IQR (k7_short_iqr) or NULL
 int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B, int T,
-                       float* out, cudaStream_t stream) {
-    if (!pl || !stems || !out) return fail(MIXFE_EINVAL, "null plan, stems or output");
+                       float* out, float* out_iqr, cudaStream_t stream) {
+    if (!pl || !stems || (!out && !out_iqr)) return fail(MIXFE_EINVAL, "null plan, stems or output");
     for (int s = 0; s < 4; ++s)
         if (!stems[s]) return fail(MIXFE_EINVAL, "stems[%d] is NULL", s);
     if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
     if (pl->sr % 10) return fail(MIXFE_EUNSUPPORTED, "gated loudness: sample rate %d is not a multiple of 10 Hz", pl->sr);
     const int sub = pl->sr / 10;
     if (T < 4 * sub) return fail(MIXFE_EINVAL, "Audio must have length greater than the block size (%d samples)", 4 * sub);
+    if (out_iqr && T < kShortSubs * sub)
+        return fail(MIXFE_EINVAL, "short-term loudness needs at least 3 s of audio (%d samples)", kShortSubs * sub);
+    if (out_iqr && T / sub - (kShortSubs - 1) > kShortMaxWin)
+        return fail(MIXFE_EUNSUPPORTED, "short-term loudness IQR: more than %d windows (clip longer than 6 min 52 s)", kShortMaxWin);
     if (B == 0) return MIXFE_OK;
     if (stride_c < T || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
     if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "gated loudness: B=%d > 65535 clips per call", B);
@@ -455,14 +460,15 @@ int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long st
     int rc = ensure_workspace(pl, bytes, stream);
     if (rc) return rc;
     p.sub_energy = reinterpret_cast<double*>(pl->ws);
-    p.out = out;
+    p.out = out; p.out_iqr = out_iqr;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_LOUDNESS, stream);
         k7_kweight_energy<<<dim3(p.n_chunks, 2, B), kLoudSignals * 32, 0, stream>>>(p);
-        k7_gate<<<B, kLoudSignals * 32, 0, stream>>>(p);
+        if (out) k7_gate<<<B, kLoudSignals * 32, 0, stream>>>(p);
+        if (out_iqr) k7_short_iqr<<<dim3(kLoudSignals, B), kShortThreads, 0, stream>>>(p);
     }
     MIXFE_CUDA(cudaGetLastError());
-    launch_counter() += 2;
+    launch_counter() += 1 + (out ? 1 : 0) + (out_iqr ? 1 : 0);
     return MIXFE_OK;
 }
 
@@ -703,7 +709,12 @@ int mixfe_logmel_backward(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STE
 
 int mixfe_gated_loudness(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,
                          int B, int T, float* lufs, void* cuda_stream) {
-    return run_gated_loudness(pl, stems, stride_b, stride_c, B, T, lufs, static_cast<cudaStream_t>(cuda_stream));
+    return run_gated_loudness(pl, stems, stride_b, stride_c, B, T, lufs, nullptr, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_short_term_loudness_iqr(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,
+                                  long long stride_c, int B, int T, float* iqr, void* cuda_stream) {
+    return run_gated_loudness(pl, stems, stride_b, stride_c, B, T, nullptr, iqr, static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long x_stride_b,

@@ -128,6 +128,20 @@ class MixingFeatureExtractor:
             out = out[0]
         return out if out.device == src_device else out.to(src_device)
 
+    def short_term_loudness_iqr(self, stems_dict):
+        """EXTENSION (not in the reference's code; its proposal, p.2 section 2.1, names DR_IQR = IQR(L_short(t))): the
+        inter-quartile range of the short-term loudness -- K-weighted, 3 s windows every 100 ms (EBU Tech 3341), windows
+        under -70 LUFS dropped -- of the four stems and of their mixture, (5,) or (B,5) in LU, order vocals, bass,
+        drums, other, mixture.  Needs 3 s <= T <= 6 min 52 s."""
+        first = stems_dict[STEMS[0]]
+        src_device = first.device
+        device = _resolve_device(first, None)
+        stems, batched = _gather_stems(stems_dict, device)
+        out = self._plan(device).short_term_loudness_iqr(stems)
+        if not batched:
+            out = out[0]
+        return out if out.device == src_device else out.to(src_device)
+
     def feature_names(self) -> List[str]:
         """Names of the D entries in the reference's sorted-key order (src/mixing_utils.py:320-357)."""
         if self.use_detailed_spectral:

@@ -82,3 +82,39 @@ def stems_gated_loudness(stems, fs: int = 44100) -> np.ndarray:
     for a in arrs:
         mix = (mix + a).astype(np.float32)
     return np.array([integrated_loudness(a, fs) for a in arrs + [mix]], dtype=np.float64)
+
+
+def short_term_loudness(x: np.ndarray, fs: int) -> np.ndarray:
+    """x: (channels, T) -> short-term loudness in LUFS of every 3 s window, hop 100 ms (EBU Tech 3341)."""
+    x = np.atleast_2d(np.asarray(x))
+    sub = sub_block_len(fs)
+    T = x.shape[-1]
+    if T < 30 * sub:
+        raise ValueError("short-term loudness needs at least 3 s of audio")
+    y = _sosfilt(k_weighting_sos(fs), x)
+    n_win = (T - 30 * sub) // sub + 1
+    z = np.stack([[np.mean(y[c, j * sub:j * sub + 30 * sub] ** 2) for j in range(n_win)] for c in range(x.shape[0])])
+    with np.errstate(divide="ignore"):
+        return -0.691 + 10.0 * np.log10(z.sum(axis=0))
+
+
+def short_term_iqr(x: np.ndarray, fs: int) -> float:
+    """The proposal's DR_IQR = IQR(L_short(t)) (PDF p.2 section 2.1; PARITY UNPINNED like the rest of this file: the
+    proposal fixes neither window, gate nor quantile rule).  Windows under -70 LUFS are dropped; q75 - q25 with
+    numpy's default linear interpolation; 0 when fewer than two windows remain."""
+    l = short_term_loudness(x, fs)
+    l = l[l >= -70.0]
+    if l.size < 2:
+        return 0.0
+    q25, q75 = np.quantile(l, [0.25, 0.75])
+    return float(q75 - q25)
+
+
+def stems_short_term_iqr(stems, fs: int = 44100) -> np.ndarray:
+    """dict of 4 x (2,T) stems -> [vocals, bass, drums, other, mixture] IQR in LU (mixture as in stems_gated_loudness)."""
+    order = ("vocals", "bass", "drums", "other")
+    arrs = [np.asarray(stems[k], dtype=np.float32) for k in order]
+    mix = np.zeros_like(arrs[0])
+    for a in arrs:
+        mix = (mix + a).astype(np.float32)
+    return np.array([short_term_iqr(a, fs) for a in arrs + [mix]], dtype=np.float64)

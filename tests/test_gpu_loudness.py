@@ -71,3 +71,35 @@ def test_awkward_lengths_and_unaligned_views(cuda_device, seed, T, off):
     got = fe.gated_loudness({n: v[:, off:off + T] for n, v in dev_wide.items()})
     ref = B.stems_gated_loudness({n: wide[n][:, off:off + T].numpy() for n in O.STEMS}, 44100)
     assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 1e-3, (got.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("T", [132300, 132301, 200001, 441000, 1323000])
+def test_short_term_loudness_iqr_vs_oracle(cuda_device, T):
+    """DR_IQR extension (k7_short_iqr): 3 s to 30 s clips, levels that move inside the clip."""
+    clip = O.musical_clip(T % 89, T)
+    t = torch.arange(T) / 44100.0
+    clip["vocals"] = clip["vocals"] * (0.2 + 0.8 * (torch.sin(2 * torch.pi * 0.11 * t) ** 2))     # slow swell
+    clip["bass"] = clip["bass"] * torch.where(t < T / 88200.0, 1.0, 0.1)                          # -20 dB step half way
+    clip["other"] = torch.cat([clip["other"][:, :T // 3], torch.zeros(2, T - T // 3)], dim=1)     # silent tail: gated
+    fe = pkg.MixingFeatureExtractor()
+    n0 = pkg.launch_count()
+    got = fe.short_term_loudness_iqr({n: v.to(cuda_device) for n, v in clip.items()})
+    assert pkg.launch_count() == n0 + 2
+    assert got.shape == (5,) and got.dtype == torch.float32
+    ref = B.stems_short_term_iqr({n: v.numpy() for n, v in clip.items()}, 44100)
+    assert np.abs(got.cpu().numpy().astype(np.float64) - ref).max() < 2e-3, (got.cpu().numpy(), ref)
+
+
+def test_short_term_iqr_batched_silence_and_limits(cuda_device):
+    fe = pkg.MixingFeatureExtractor()
+    T = 150000
+    clips = [O.musical_clip(60 + i, T) for i in range(3)]
+    clips[2]["drums"] = torch.zeros(2, T)
+    batch = {n: torch.stack([c[n] for c in clips]).to(cuda_device) for n in O.STEMS}
+    got = fe.short_term_loudness_iqr(batch)
+    assert got.shape == (3, 5) and float(got[2, 2]) == 0.0                     # no window passes the gate
+    for i, c in enumerate(clips):
+        one = fe.short_term_loudness_iqr({n: v.to(cuda_device) for n, v in c.items()})
+        assert torch.equal(one, got[i])
+    with pytest.raises(ValueError, match="3 s"):
+        fe.short_term_loudness_iqr({n: torch.zeros(2, 132299, device=cuda_device) for n in O.STEMS})

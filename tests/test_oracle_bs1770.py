@@ -39,3 +39,31 @@ def test_gates():
         B.integrated_loudness(np.zeros((2, fs // 10 * 4 - 1)), fs)
     with pytest.raises(ValueError):
         B.integrated_loudness(np.zeros((2, 44101)), 44101)
+
+
+def test_short_term_iqr_of_a_steady_tone_is_zero_and_of_a_level_step_is_the_step():
+    """DR_IQR = IQR(L_short): a steady sine has one short-term level; a sine that drops by 12 dB half way through has
+    two equally populated levels (plus the few windows that straddle the step), so the IQR is close to 12 LU."""
+    fs, T = 48000, 48000 * 20
+    t = np.arange(T) / fs
+    tone = 0.3 * np.sin(2 * np.pi * 997.0 * t)
+    steady = np.stack([tone, tone])
+    assert abs(B.short_term_iqr(steady, fs)) < 1e-6
+    env = np.where(t < 10.0, 1.0, 10.0 ** (-12.0 / 20.0))
+    stepped = np.stack([tone * env, tone * env])
+    iqr = B.short_term_iqr(stepped, fs)
+    assert 11.5 < iqr <= 12.0 + 1e-6, iqr
+    l = B.short_term_loudness(stepped, fs)
+    assert l.shape == ((T - 3 * fs) // (fs // 10) + 1,)
+    assert abs((l[0] - l[-1]) - 12.0) < 1e-3
+
+
+def test_short_term_iqr_drops_silent_windows_and_needs_three_seconds():
+    fs = 44100
+    x = np.zeros((2, fs * 8))
+    x[:, :fs * 4] = 0.2 * np.sin(2 * np.pi * 440.0 * np.arange(fs * 4) / fs)
+    l = B.short_term_loudness(x, fs)
+    assert (l < -70.0).any()                                  # the silent tail
+    assert B.short_term_iqr(x, fs) < 15.0                     # bounded by the audible windows, not by -inf
+    with pytest.raises(ValueError, match="3 s"):
+        B.short_term_loudness(np.zeros((2, fs * 3 - 1)), fs)
