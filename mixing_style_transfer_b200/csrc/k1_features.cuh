@@ -623,7 +623,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     if (n > 0) {
                         const unsigned char* p0 = col + flo[m];
                         const float* wp = wsteps + p.wmeta[warp][ab][1] + fi;
-#pragma unroll 2
+#pragma unroll 4
                         for (int i = 0; i < n; i += 2) {
                             const float w0 = wp[8 * i], w1 = wp[8 * i + 8];
                             const float2 u0 = *reinterpret_cast<const float2*>(p0 + 8 * i);
