@@ -14,7 +14,9 @@
 // One CTA per (tile of 8 frames, clip, stem).  The forward spectrum is recomputed (no activations are saved: the
 // forward writes only the log-mel), with the shared-memory FFT core of fftg.cuh.  L and R share both transforms: forward as
 // one complex FFT of L + iR; backward as one complex FFT of conj(Y), Y = Hermitian extension of G_L plus i times that
-// of G_R, whose inverse transform is dframe_L + i dframe_R.  Frames are overlap-added in shared memory; the tile's
+// of G_R, whose inverse transform is dframe_L + i dframe_R.  conj(Y) is written in place over the forward spectrum,
+// which fg_fft leaves in bit-reversed order, and the inverse runs as decimation in time (bit-reversed in, natural order
+// out): one spectrum buffer, no permutation pass.  Frames are overlap-added in shared memory; the tile's
 // span goes to global memory with atomicAdd (a sample receives at most two tiles' values when n_fft <= 9 hop, so
 // the sum is order-independent there; within n_fft/2 samples of the clip edges the reflected terms add a third).
 #pragma once
