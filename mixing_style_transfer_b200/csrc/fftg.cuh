@@ -9,9 +9,11 @@
 //   exp(-2 pi i (j + mm hs) / (2 h_t)) = tw[j * s * 2^t] * exp(-2 pi i mm 2^t / 2^R):
 // one table read per stage (R per pass) times a compile-time constant (a sixteenth of a turn).
 //
-// Rows are padded by one element per eight, position p at p + (p >> 3) (row stride n + n/8): a thread's points in
-// the last pass are contiguous (spacing 1, 2 or 4), and the threads of a warp, 8 or 16 elements apart, would
-// otherwise all start in the same bank; the padding also separates the blocks of the middle passes.
+// Rows are padded by one element per sixteen, position p at p + (p >> 4) (row stride n + n/16).  A 64-bit access is
+// served half a warp at a time, 16 bank pairs wide: with this padding the 16 contiguous points of a half-warp (loads,
+// untangle, overlap-add, the first passes) stay in 16 different bank pairs, and so do the points of the last pass,
+// where a thread owns 8 or 16 contiguous points and the lanes are 8 or 16 apart (8 t + t/2, 17 t).  Counted over the
+// passes, the untangle and the contiguous walks this is 1.3x to 1.8x fewer wavefronts than one pad per eight.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -20,8 +22,8 @@ namespace mixfe {
 
 constexpr int kGThreads = 256;
 
-__device__ __forceinline__ int fg_pad(int p) { return p + (p >> 3); }
-__host__ __device__ __forceinline__ int fg_row(int n) { return n + (n >> 3); }
+__device__ __forceinline__ int fg_pad(int p) { return p + (p >> 4); }
+__host__ __device__ __forceinline__ int fg_row(int n) { return n + (n >> 4); }
 
 // idx / d for 0 <= idx and idx * d < 2^32, d >= 2, with magic = 0xFFFFFFFF / d + 1 (one multiply-high instead of the
 // ~20-instruction runtime division).
@@ -101,9 +103,9 @@ __device__ __forceinline__ void fg_pass(float2* z, const float2* __restrict__ tw
         const int base = (g << (lh + 1)) + j;
         float2* row = z + f * zs;
         float2 v[P];
-        if (lhs >= 3) {
+        if (lhs >= 4) {
             float2* r = row + fg_pad(base);
-            const int sp = hs + (hs >> 3);
+            const int sp = hs + (hs >> 4);
 #pragma unroll
             for (int m = 0; m < P; ++m) v[m] = r[m * sp];
         } else {
@@ -123,9 +125,9 @@ __device__ __forceinline__ void fg_pass(float2* z, const float2* __restrict__ tw
                 v[b] = fg_mul_w16(cmulf(d, wj), (mm << t) * (16 / P));
             }
         }
-        if (lhs >= 3) {
+        if (lhs >= 4) {
             float2* r = row + fg_pad(base);
-            const int sp = hs + (hs >> 3);
+            const int sp = hs + (hs >> 4);
 #pragma unroll
             for (int m = 0; m < P; ++m) r[m * sp] = v[m];
         } else {
@@ -165,9 +167,9 @@ __device__ __forceinline__ void fg_pass_dit(float2* z, const float2* __restrict_
         const int base = (g << (lh0 + R)) + j;
         float2* row = z + f * zs;
         float2 v[P];
-        if (lh0 >= 3) {
+        if (lh0 >= 4) {
             float2* r = row + fg_pad(base);
-            const int sp = h0 + (h0 >> 3);
+            const int sp = h0 + (h0 >> 4);
 #pragma unroll
             for (int m = 0; m < P; ++m) v[m] = r[m * sp];
         } else {
@@ -187,9 +189,9 @@ __device__ __forceinline__ void fg_pass_dit(float2* z, const float2* __restrict_
                 v[a] = make_float2(v[a].x + tb.x, v[a].y + tb.y);
             }
         }
-        if (lh0 >= 3) {
+        if (lh0 >= 4) {
             float2* r = row + fg_pad(base);
-            const int sp = h0 + (h0 >> 3);
+            const int sp = h0 + (h0 >> 4);
 #pragma unroll
             for (int m = 0; m < P; ++m) r[m * sp] = v[m];
         } else {
