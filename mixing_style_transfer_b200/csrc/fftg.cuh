@@ -142,7 +142,9 @@ __device__ __forceinline__ void fg_fft(float2* z, const float2* __restrict__ tw,
     const int passes = (log2n + 3) >> 2, base = log2n / passes, extra = log2n - base * passes;
     int lh = log2n - 1;
     for (int ps = 0; ps < passes; ++ps) {
-        const int R = base + (ps < extra ? 1 : 0);
+        // the 4-stage passes go last (1024 points: 3 + 3 + 4): a 4-stage pass in the middle is the one arrangement whose
+        // lanes collide two-way (scripts/bank_sim.py); fg_fft_dit mirrors this with its 4-stage passes first
+        const int R = base + (ps >= passes - extra ? 1 : 0);
         if (R == 4) fg_pass<4>(z, tw, log2n, frames, lh, tid);
         else fg_pass<3>(z, tw, log2n, frames, lh, tid);
         lh -= R;
