@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k1g_features(const __grid_consta
             // Lane i takes bin k = bitrev_{log2n-1}(i): X[k] then sits at position 2 i and X[n-k] at an odd position
             // walking the other way, so a warp reads neighbouring words instead of 32 words of one bank.  The power
             // column is padded (k + (k >> pad_sh)) so that the scattered k of a warp fall into different banks.
-            const int sh = 32 - g.log2n, pad_sh = g.log2n > 6 ? g.log2n - 6 : 31;
+            const int sh = 32 - g.log2n, pad_sh = g.log2n > 6 ? g.log2n - 5 : 31;
             for (int idx = tid; idx < frames * (half + 1); idx += kGThreads) {
                 const int f = k1g_div(idx, mg_nb), i = idx - f * (half + 1);
                 const int k = i == half ? half : (int)(__brev((unsigned)i) >> (sh + 1));

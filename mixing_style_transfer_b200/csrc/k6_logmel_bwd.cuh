@@ -33,7 +33,7 @@ struct K6Params {
     const float* g;                  // d loss / d logmel: (b, ch, m, f) at g[b * g_stride_b + (ch * n_mels + m) * F + f]
     long long g_stride_b;
     int B, T, F, hop, n_mels, n_mels_pad, n_fft, log2n, nf, span;
-    int span_pad;                    // floats per channel of the padded overlap-add span
+    int span_pad;                    // floats per channel of the overlap-add span buffer (>= span)
     const float2* twg;               // [n_fft/2]
     const float* win;                // [n_fft] 0.5 * periodic hann
     const int4* mel_meta;            // filterbank by filter (CSR): (first bin, bins, weight offset, -)
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const int sh = 32 - p.log2n;
     const unsigned mg_nb = k1g_magic(nb), mg_mp = k1g_magic(p.n_mels_pad);
-    const int pad_sh = p.log2n > 6 ? p.log2n - 6 : 31, ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
+    const int pad_sh = p.log2n > 6 ? p.log2n - 5 : 31;
     const float* gL = p.stem[s] + (long long)b * p.stride_b;
     const float* gR = gL + p.stride_c;
 
@@ -146,8 +146,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
             for (int i = tid; i < n; i += kGThreads) {
                 const float2 r = z[f * zs + fg_pad(i)];
                 const float w = 2.0f * __ldg(p.win + i);
-                const int q = q0 + i;
-                const int o = q + (q >> ola_sh);
+                const int o = q0 + i;
                 ola[o] = fmaf(w, r.x, ola[o]);
                 ola[p.span_pad + o] = fmaf(-w, r.y, ola[p.span_pad + o]);
             }
@@ -163,9 +162,8 @@ __global__ void __launch_bounds__(kGThreads, 3) k6_logmel_bwd(const __grid_const
         long long j = (long long)t0 * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
-        const int o = i + (i >> ola_sh);
-        atomicAdd(dLp + j, ola[o]);
-        atomicAdd(dRp + j, ola[p.span_pad + o]);
+        atomicAdd(dLp + j, ola[i]);
+        atomicAdd(dRp + j, ola[p.span_pad + i]);
     }
 }
 

@@ -35,7 +35,7 @@ struct K8Params {
     const float* gscale;             // device scalar: upstream gradient / n_resolutions   (backward)
     float* gx;                       // gradient of x, zero-initialised by the caller, addressing gs_b, gs_c (backward)
     long long gs_b, gs_c;
-    int span_pad;                    // padded overlap-add span (q + (q >> ola_sh))
+    int span_pad;                    // floats of the overlap-add span buffer (>= span)
     int off_ola, off_red;
 };
 
@@ -131,7 +131,6 @@ __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constan
     const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;
     const float* xr = p.x + (long long)(row / p.C) * p.xs_b + (long long)(row % p.C) * p.xs_c;
     const float* yr = p.y + (long long)(row / p.C) * p.ys_b + (long long)(row % p.C) * p.ys_c;
-    const int ola_sh = p.log2n > 5 ? p.log2n - 5 : 31;
     const float gs = __ldg(p.gscale);
     const float alpha = (float)p.state[5] * gs, beta = (float)p.state[6] * gs;
 
@@ -168,9 +167,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constan
             const int q0 = (f0 + f) * p.hop;
             for (int i = tid; i < n; i += kGThreads) {
                 const float2 r = z[f * zs + fg_pad(i)];
-                const int q = q0 + i;
-                const int o = q + (q >> ola_sh);
-                ola[o] = fmaf(2.0f * __ldg(p.win + i), r.x, ola[o]);
+                ola[q0 + i] = fmaf(2.0f * __ldg(p.win + i), r.x, ola[q0 + i]);
             }
             __syncthreads();
         }
@@ -182,7 +179,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k8_backward(const __grid_constan
         long long j = (long long)t0 * p.hop - half + i;
         if (j < 0) j = -j;
         if (j >= p.T) j = 2ll * (p.T - 1) - j;
-        atomicAdd(gr + j, ola[i + (i >> ola_sh)]);
+        atomicAdd(gr + j, ola[i]);
     }
 }
 

@@ -209,7 +209,7 @@ int build_generic_tables(mixfe_plan* pl) {
         return rc;
     pl->g_log2n = 0;
     while ((1 << pl->g_log2n) < n) ++pl->g_log2n;
-    pl->g_pw_stride = (n / 2 + 1 + (pl->g_log2n > 6 ? (n / 2) >> (pl->g_log2n - 6) : 0)) | 1;   // k + (k >> pad_sh), k <= n/2
+    pl->g_pw_stride = (n / 2 + 1 + (pl->g_log2n > 6 ? (n / 2) >> (pl->g_log2n - 5) : 0)) | 1;   // k + (k >> pad_sh), k <= n/2
     const int per_frame = fg_row(n) * 8 + pl->g_pw_stride * 8;
     int nfr = kTF;
     {
