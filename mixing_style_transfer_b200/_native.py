@@ -159,6 +159,25 @@ def unify_stems(stems: Sequence[torch.Tensor]):
     return st, st[0].stride(0), st[0].stride(1)
 
 
+def _check_out(t: torch.Tensor, shape, device: torch.device, name: str) -> None:
+    """A caller-provided output buffer must be fp32, on the plan's device and exactly `shape`; strides are checked by
+    the caller where the kernel assumes a layout.  Raises ValueError instead of letting a kernel write out of bounds."""
+    if t.dtype != torch.float32:
+        raise ValueError(f"{name}: dtype {t.dtype}, expected torch.float32")
+    if t.device != device:
+        raise ValueError(f"{name}: on {t.device}, the plan lives on {device}")
+    if tuple(t.shape) != tuple(shape):
+        raise ValueError(f"{name}: shape {tuple(t.shape)}, expected {tuple(shape)}")
+
+
+def _span(t: torch.Tensor):
+    """[first byte, last byte + 1) of the memory a strided tensor touches."""
+    if t.numel() == 0:
+        return (t.data_ptr(), t.data_ptr())
+    last = sum((n - 1) * st for n, st in zip(t.shape, t.stride()))
+    return (t.data_ptr(), t.data_ptr() + (last + 1) * t.element_size())
+
+
 def copy_async(dst_ptr: int, src: torch.Tensor, nbytes: int) -> None:
     """Copy-engine D2D copy of `nbytes` from the (contiguous) tensor `src` to the raw device address `dst_ptr` on the
     current stream of src's device; dst_ptr may be an NVSwitch multicast address."""
@@ -217,11 +236,18 @@ class Plan:
         if want_features:
             feats = features_out if features_out is not None else \
                 torch.empty((B, self.feature_dim), dtype=torch.float32, device=self.device)
+            if features_out is not None:
+                _check_out(feats, (B, self.feature_dim), self.device, "features_out")
+                if B and (feats.stride(1) != 1 or (B > 1 and feats.stride(0) != self.feature_dim)):
+                    raise ValueError("features_out must be a dense (B, D) buffer")
         if want_logmel:
             lm = logmel_out if logmel_out is not None else \
                 torch.empty((B, 8, self.n_mels, F), dtype=torch.float32, device=self.device)
-            if lm.stride(3) != 1 or lm.stride(2) != F or lm.stride(1) != self.n_mels * F:
-                raise ValueError("logmel_out must be contiguous in its last three dims")
+            if logmel_out is not None:
+                _check_out(lm, (B, 8, self.n_mels, F), self.device, "logmel_out")
+            if lm.stride(3) != 1 or lm.stride(2) != F or lm.stride(1) != self.n_mels * F or \
+                    (B > 1 and lm.stride(0) < 8 * self.n_mels * F):
+                raise ValueError("logmel_out must be contiguous in its last three dims (any batch stride >= one clip)")
         ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
         with torch.cuda.device(self.device):
             _check(lib().mixfe_features_logmel(self._h, ptrs, sb, sc, B, T, _ptr(feats), _ptr(lm),
@@ -271,6 +297,9 @@ class Plan:
         """Adds grad_scale * d(sc + lm)/dx of this resolution into grad_x ((B,C,T) fp32, contiguous in T)."""
         x, y = self._bct(x), self._bct(y)
         B, C, T = x.shape
+        _check_out(grad_x, (B, C, T), self.device, "grad_x")
+        if grad_x.stride(2) != 1 or grad_x.stride(1) < T or (B > 1 and grad_x.stride(0) < T):
+            raise ValueError("grad_x must have unit stride in T and non-overlapping rows")
         with torch.cuda.device(self.device):
             _check(lib().mixfe_stft_loss_backward(self._h, _ptr(x), _ptr(y), B, C, T, x.stride(0), x.stride(1), y.stride(0),
                                                   y.stride(1), _ptr(state), _ptr(grad_scale), _ptr(grad_x), grad_x.stride(0),
@@ -322,6 +351,11 @@ class Plan:
                 if (o.shape != s.shape or o.stride() != s.stride() or o.dtype != torch.float32
                         or o.device != s.device):
                     raise ValueError("augment: `outs` must match the inputs' shape, strides, dtype and device")
+        spans_in = [_span(t) for t in st]
+        for o in outs:
+            lo, hi = _span(o)
+            if any(lo < b and a < hi for a, b in spans_in):
+                raise ValueError("augment: an output buffer overlaps an input (the kernels read ahead of what they write)")
         pin = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
         pout = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in outs])
         L = 0

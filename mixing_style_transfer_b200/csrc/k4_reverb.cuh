@@ -359,14 +359,10 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     p4.part_energy = p3.part_energy; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
     const int smem_cols = (kColsPerCta * kColStride + 1024) * (int)sizeof(float2);
     const int smem_rows = (8 * 1024 + 1024) * (int)sizeof(float2);
-    if (!pl->k4_attr_done) {
-        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
-        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
-        MIXFE_CUDA(cudaFuncSetAttribute(k4_cols<kColsInv>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cols));
-        MIXFE_CUDA(cudaFuncSetAttribute(k4_rows<kRowsX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_rows));
-        MIXFE_CUDA(cudaFuncSetAttribute(k4_rows<kRowsH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_rows));
-        pl->k4_attr_done = true;
-    }
+    if ((rc = smem_optin(k4_cols<kColsX>, pl->device, smem_cols)) || (rc = smem_optin(k4_cols<kColsH>, pl->device, smem_cols)) ||
+        (rc = smem_optin(k4_cols<kColsInv>, pl->device, smem_cols)) || (rc = smem_optin(k4_rows<kRowsX>, pl->device, smem_rows)) ||
+        (rc = smem_optin(k4_rows<kRowsH>, pl->device, smem_rows)))
+        return rc;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_REVERB, stream);
         const dim3 g1(kRevN2 / kColsPerCta, 1, n_slots), gs(kRevN2 / kColsPerCta, n_seg, n_slots);

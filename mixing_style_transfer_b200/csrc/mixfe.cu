@@ -169,7 +169,7 @@ int build_mel_tables(mixfe_plan* pl) {
     pl->smem_k1 = pl->off_red + 8 * 4 * 4 + 32;          // masking scratch, mbarrier, arrival counter
     if (pl->smem_k1 > 227 * 1024)
         return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
-    MIXFE_CUDA(cudaFuncSetAttribute(k1_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_k1));
+    if (int rc = smem_optin(k1_features, pl->device, pl->smem_k1)) return rc;
     int per_sm = 0;
     MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_features, kK1Threads, pl->smem_k1));
     pl->k1_ctas = std::max(1, per_sm) * pl->n_sms;
@@ -197,8 +197,8 @@ int build_generic_tables(mixfe_plan* pl) {
         const double a = -2.0 * M_PI * (double)e / (double)n;
         tw[e] = make_float2((float)std::cos(a), (float)std::sin(a));
     }
-    // torch.hann_window(n, periodic=True) is evaluated in fp32 by torch; the Python layer hands over the exact
-    // buffer through mixfe_plan_set_window when it matters.  Default: double precision, rounded once.
+    // torch.hann_window(n, periodic=True): evaluated here in double precision and rounded once (the fp32 values torch
+    // produces differ by at most one ulp, far below the parity tolerance).
     std::vector<float> win(n);
     for (int i = 0; i < n; ++i) win[i] = (float)(0.5 * (0.5 - 0.5 * std::cos(2.0 * M_PI * (double)i / (double)n)));
     int rc;
@@ -225,7 +225,7 @@ int build_generic_tables(mixfe_plan* pl) {
     pl->g_off_red = pl->g_off_S + kNumStems * kTF * pl->n_mels_pad * 4;
     pl->smem_g = pl->g_off_red + 8 * 4 * 4;
     if (pl->smem_g > 227 * 1024) return fail(MIXFE_EUNSUPPORTED, "K1G needs %d bytes of shared memory", pl->smem_g);
-    MIXFE_CUDA(cudaFuncSetAttribute(k1g_features, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_g));
+    if (int rc = smem_optin(k1g_features, pl->device, pl->smem_g)) return rc;
     // K6 (log-mel backward): filterbank by bin + its shared-memory map
     {
         // Entry i describes bin k = bitrev_{log2n-1}(i) (i = n/2: the Nyquist bin): K6's lane i works on that bin
@@ -265,7 +265,7 @@ int build_generic_tables(mixfe_plan* pl) {
         pl->b_off_ola = align16(pl->b_off_mel + bn * pl->n_mels_pad * 8);
         pl->smem_b = pl->b_off_ola + ola;
         if (pl->smem_b > 227 * 1024) pl->smem_b = 0;          // hop too large for the overlap-add buffer: backward unsupported
-        else MIXFE_CUDA(cudaFuncSetAttribute(k6_logmel_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->smem_b));
+        else if (int rc6 = smem_optin(k6_logmel_bwd, pl->device, pl->smem_b)) return rc6;
     }
     return MIXFE_OK;
 }
@@ -504,11 +504,7 @@ int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B,
     p.nf = nf;
     p.off_red = nf * fg_row(pl->n_fft) * 8;
     const int smem = p.off_red + 8 * 3 * 4;
-    if (!pl->k8_attr_done) {
-        MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        MIXFE_CUDA(cudaFuncSetAttribute(k8_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        pl->k8_attr_done = true;
-    }
+    if ((rc = smem_optin(k8_partials, pl->device, 100 * 1024)) || (rc = smem_optin(k8_backward, pl->device, 200 * 1024))) return rc;
     rc = ensure_workspace(pl, sizeof(float) * 3 * (size_t)p.rows * p.n_tiles, stream);
     if (rc) return rc;
     p.part = reinterpret_cast<float*>(pl->ws);
@@ -540,11 +536,7 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     p.nf = nf;
     p.off_ola = align16(nf * fg_row(pl->n_fft) * 8);
     const int smem = p.off_ola + ola;
-    if (!pl->k8_attr_done) {
-        MIXFE_CUDA(cudaFuncSetAttribute(k8_partials, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        MIXFE_CUDA(cudaFuncSetAttribute(k8_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        pl->k8_attr_done = true;
-    }
+    if ((rc = smem_optin(k8_partials, pl->device, 100 * 1024)) || (rc = smem_optin(k8_backward, pl->device, 200 * 1024))) return rc;
     p.state = const_cast<double*>(state); p.gscale = gscale; p.gx = gx; p.gs_b = gs_b; p.gs_c = gs_c;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);

@@ -1,6 +1,10 @@
 // The plan object behind the opaque mixfe_plan handle of include/mixfe.h.
 #pragma once
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 
 struct mixfe_plan {
@@ -35,8 +39,6 @@ struct mixfe_plan {
     void* aug_params_host = nullptr;    // pinned staging buffer for them
     size_t aug_params_cap = 0;
     // optional per-kernel timing (bench.py): event pairs recorded around launches, drained on query
-    bool k8_attr_done = false;          // dynamic shared-memory opt-in of the STFT-loss kernels
-    bool k4_attr_done = false;          // dynamic shared-memory opt-in of the reverb kernels
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[MIXFE_NUM_KERNELS];
 };
@@ -73,6 +75,21 @@ struct KernelTimer {
         }
     }
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is state of (kernel, device), shared by every plan: a plan with a
+// smaller footprint must not lower the limit an earlier plan launches with.  Keep a monotone per-(kernel, device)
+// maximum and only ever raise it.
+template <class K>
+inline int smem_optin(K* kernel, int device, int bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> high;
+    std::lock_guard<std::mutex> lock(mu);
+    int& cur = high[{reinterpret_cast<const void*>(kernel), device}];
+    if (bytes <= cur) return MIXFE_OK;
+    MIXFE_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    cur = bytes;
+    return MIXFE_OK;
+}
 
 struct DeviceGuard {
     int prev = -1;

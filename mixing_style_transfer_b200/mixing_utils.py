@@ -158,16 +158,21 @@ class MixingFeatureExtractor:
         return names
 
     # -- internals -------------------------------------------------------------------------
+    def _new_plan(self, device: torch.device) -> Plan:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if self.use_detailed_spectral and self.n_spectral_bins > self.n_mels:
+            # torch.stack([arange(n_bins), curve]) raises in the reference (:220)
+            raise RuntimeError("stack expects each tensor to be equal size: n_spectral_bins > n_mels")
+        nb = self.n_spectral_bins if self.use_detailed_spectral else 0
+        return Plan(torch.device("cuda", idx), self.sr, self.n_fft, self.hop_length, self.n_mels, nb, fb=self._fb)
+
     def _plan(self, device: torch.device) -> Plan:
+        """The extractor's plan on `device` (one per device).  A plan is single-stream: its workspace is shared by
+        every call, so concurrent use from several CUDA streams needs one extractor (or plan) per stream."""
         idx = device.index if device.index is not None else torch.cuda.current_device()
         pl = self._plans.get(idx)
         if pl is None:
-            if self.use_detailed_spectral and self.n_spectral_bins > self.n_mels:
-                # torch.stack([arange(n_bins), curve]) raises in the reference (:220)
-                raise RuntimeError("stack expects each tensor to be equal size: n_spectral_bins > n_mels")
-            nb = self.n_spectral_bins if self.use_detailed_spectral else 0
-            pl = Plan(torch.device("cuda", idx), self.sr, self.n_fft, self.hop_length, self.n_mels, nb, fb=self._fb)
-            self._plans[idx] = pl
+            pl = self._plans[idx] = self._new_plan(device)
         return pl
 
     def _run(self, stems_dict, want_features: bool, want_logmel: bool):

@@ -49,7 +49,7 @@ class MelSpectrogramPreprocessor(nn.Module):
         self.n_mels = n_mels
         self.mel_transform = _MelTransform(sample_rate, n_fft, n_mels)
         self._plans: Dict[int, Plan] = {}
-        self._fb_version = None
+        self._fb_versions: Dict[int, tuple] = {}       # per device: the filterbank its plan was built from
 
     def _plan(self, device: torch.device) -> Plan:
         idx = device.index if device.index is not None else torch.cuda.current_device()
@@ -59,9 +59,9 @@ class MelSpectrogramPreprocessor(nn.Module):
         if pl is None:
             pl = Plan(torch.device("cuda", idx), self.sample_rate, self.n_fft, self.hop_length, self.n_mels, 0, fb=fb)
             self._plans[idx] = pl
-        elif version != self._fb_version:
+        elif version != self._fb_versions.get(idx):
             pl.set_filterbank(fb)              # a checkpoint load replaced the buffer
-        self._fb_version = version
+        self._fb_versions[idx] = version
         return pl
 
     def forward(self, stems_dict):

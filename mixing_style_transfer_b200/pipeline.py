@@ -17,8 +17,10 @@ from ._native import STEMS
 class HostPipeline:
     def __init__(self, extractor, n_clips: int, T: int, chunk: int = 12, device=None, with_logmel: bool = True):
         self.fe = extractor
-        self.device = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
-        self.plan = extractor._plan(self.device)
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        # a plan (its growable workspace) serves ONE stream at a time: the pipeline runs its kernels on a private stream,
+        # so it owns a private plan instead of borrowing the extractor's
+        self.plan = extractor._new_plan(self.device)
         self.n, self.T, self.chunk = n_clips, T, max(1, min(chunk, n_clips))
         self.with_logmel = with_logmel
         # chunk boundaries: short chunks at both ends (the first upload and the last download are the only legs
