@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define MIXFE_ABI_VERSION 1
+#define MIXFE_ABI_VERSION 2
 
 #define MIXFE_OK 0
 #define MIXFE_EINVAL (-1)       /* bad argument (shape, stride, NULL) */
@@ -38,7 +38,9 @@ typedef struct mixfe_aug_params {
     float gain_lin[MIXFE_NUM_STEMS];     /* 10^(gain_db/20) as fp32, 1.0f when the gain gate did not fire (:389-392) */
     int tilt_on[MIXFE_NUM_STEMS];        /* spectral-tilt gate (:395) */
     double tilt_sos[MIXFE_NUM_STEMS][6]; /* one biquad b0 b1 b2 a0 a1 a2 = scipy butter(2, ...) (:426-429) */
-    int comp_on[MIXFE_NUM_STEMS];        /* static compressor gate (:399), threshold -20 dB ratio 4 (:435) */
+    int comp_on[MIXFE_NUM_STEMS];        /* static compressor gate (:399) */
+    float comp_threshold_db[MIXFE_NUM_STEMS]; /* apply_compression(threshold=-20) (:435); augment_stems uses -20 */
+    float comp_ratio[MIXFE_NUM_STEMS];   /* apply_compression(ratio=4) (:435), > 0; augment_stems uses 4 */
     int bw_on[MIXFE_NUM_STEMS];          /* bandwidth-limit gate (:403) */
     double bw_sos[MIXFE_NUM_STEMS][12];  /* two biquads = scipy butter(4, cutoff, 'low') (:452) */
     int reverb_on;                       /* reverb gate (:409); impulse row must be valid when set */
@@ -56,6 +58,11 @@ const char* mixfe_last_error(void);
 int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, int hop,
                       int n_mels, int n_spectral_bins);
 int mixfe_plan_destroy(mixfe_plan* plan);
+
+/* Replaces AudioAugmenter.__init__ (src/mixing_utils.py:367-370): a plan that serves only mixfe_augment,
+ * mixfe_effects and mixfe_reverb (FFT twiddles of the reverb; no mel / STFT tables).  Every feature entry point
+ * returns MIXFE_EINVAL on such a plan. */
+int mixfe_plan_create_augment(mixfe_plan** out, int device, int sample_rate);
 
 /* Optional: replace the plan's filterbank by a host matrix fb[n_fft/2+1][n_mels] (row-major),
  * e.g. the `mel_scale.fb` buffer of a reference checkpoint. */
@@ -85,6 +92,23 @@ int mixfe_augment(mixfe_plan* plan, const float* const in[MIXFE_NUM_STEMS],
                   float* const out[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,
                   int B, int T, const mixfe_aug_params* params, const float* impulse, int L,
                   void* cuda_stream);
+
+/* Replaces the single-effect methods AudioAugmenter.apply_spectral_tilt / apply_compression(audio, threshold, ratio) /
+ * apply_bandwidth_limit (src/mixing_utils.py:421-456) and the gain of :389-392 on ONE tensor: in/out device fp32,
+ * element (b, c, t) at in[b*stride_b + c*stride_c + t], C channels per clip.  The decisions of params[b] with STEM
+ * INDEX 0 (gain_lin[0], tilt_on[0], tilt_sos[0], comp_*[0], bw_*[0]) are applied to every channel of clip b;
+ * reverb_on is ignored.  out must not alias in. */
+int mixfe_effects(mixfe_plan* plan, const float* in, float* out, long long stride_b, long long stride_c,
+                  int B, int C, int T, const mixfe_aug_params* params, void* cuda_stream);
+
+/* Replaces AudioAugmenter.apply_reverb(audio, decay) (src/mixing_utils.py:458-479) on ONE tensor:
+ * out = 0.7 in + 0.3 r,  r[c][n] = sum_k in[c][n + k - L/2] h_b[k]  (F.conv1d with padding L/2, cropped to T), without
+ * the stem sum and the energy redistribution augment_stems adds (:409-417).  C = 1 or 2 channels per clip (wider
+ * tensors: call per channel pair).  impulse: device fp32, clip b's L taps at impulse + b*impulse_stride_b;
+ * impulse_stride_b = 0 shares one impulse (what the reference does for the channels of one call).
+ * L = int(sample_rate * decay) in the reference (:460); L <= 2^19. */
+int mixfe_reverb(mixfe_plan* plan, const float* in, float* out, long long stride_b, long long stride_c,
+                 int B, int C, int T, const float* impulse, long long impulse_stride_b, int L, void* cuda_stream);
 
 /* Replaces autograd through MelSpectrogramPreprocessor.forward (src/model.py:41-67), the path the style-transfer
  * loop differentiates (src/train_style_transfer.py:206-215): given d loss / d logmel, ADDS d loss / d stems into

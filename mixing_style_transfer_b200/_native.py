@@ -16,7 +16,8 @@ import torch
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _REPO = os.path.dirname(_PKG)
 CSRC = os.path.join(_PKG, "csrc")
-LIB_PATH = os.path.join(_PKG, "libmixfe.so")
+# MIXFE_LIB: developer knob for A/B runs of kernel variants (scripts/): load another build of the same ABI
+LIB_PATH = os.environ.get("MIXFE_LIB") or os.path.join(_PKG, "libmixfe.so")
 INCLUDE = os.path.join(_REPO, "include", "mixfe.h")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -25,6 +26,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 STEMS = ("vocals", "bass", "drums", "other")   # reference: src/model.py:54, src/mixing_utils.py:287
 
 E_INVAL, E_UNSUPPORTED, E_CUDA, E_SHORT = -1, -2, -3, -4
+ABI_VERSION = 2                                   # MIXFE_ABI_VERSION of include/mixfe.h
 
 
 def _sources():
@@ -58,6 +60,8 @@ class AugParams(ctypes.Structure):
         ("tilt_on", ctypes.c_int * 4),
         ("tilt_sos", (ctypes.c_double * 6) * 4),
         ("comp_on", ctypes.c_int * 4),
+        ("comp_threshold_db", ctypes.c_float * 4),
+        ("comp_ratio", ctypes.c_float * 4),
         ("bw_on", ctypes.c_int * 4),
         ("bw_sos", (ctypes.c_double * 12) * 4),
         ("reverb_on", ctypes.c_int),
@@ -74,7 +78,8 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_features_logmel", "mixfe_logmel_backward", "mixfe_augment", "mixfe_debug_mel_power", "mixfe_launch_count",
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
            "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
-           "mixfe_stft_loss_forward", "mixfe_stft_loss_backward")
+           "mixfe_stft_loss_forward", "mixfe_stft_loss_backward", "mixfe_plan_create_augment", "mixfe_effects",
+           "mixfe_reverb")
 
 
 def lib() -> ctypes.CDLL:
@@ -90,6 +95,10 @@ def lib() -> ctypes.CDLL:
                 f"{LIB_PATH} is missing: the CUDA extension has not been built "
                 "(run `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
         L = ctypes.CDLL(LIB_PATH)
+        L.mixfe_abi_version.restype = ctypes.c_int
+        if L.mixfe_abi_version() != ABI_VERSION:
+            raise RuntimeError(f"{LIB_PATH} has ABI version {L.mixfe_abi_version()}, this package binds version "
+                               f"{ABI_VERSION}: rebuild it (`python -c 'import __graft_entry__ as g; g.build()'`)")
         vp, ll, ci = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int
         L.mixfe_abi_version.restype = ci
         L.mixfe_last_error.restype = ctypes.c_char_p
@@ -105,6 +114,9 @@ def lib() -> ctypes.CDLL:
         L.mixfe_logmel_backward.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, ctypes.POINTER(vp), ll, ll, vp]
         L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
                                     ctypes.POINTER(AugParams), vp, ci, vp]
+        L.mixfe_plan_create_augment.argtypes = [ctypes.POINTER(vp), ci, ci]
+        L.mixfe_effects.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, ctypes.POINTER(AugParams), vp]
+        L.mixfe_reverb.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, vp, ll, ci, vp]
         L.mixfe_launch_count.restype = ll
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
@@ -187,8 +199,9 @@ def copy_async(dst_ptr: int, src: torch.Tensor, nbytes: int) -> None:
 class Plan:
     """Owner of a mixfe_plan (constant tables + workspace) bound to one CUDA device."""
 
-    def __init__(self, device: torch.device, sample_rate: int, n_fft: int, hop: int, n_mels: int,
+    def __init__(self, device: torch.device, sample_rate: int, n_fft: int = 0, hop: int = 0, n_mels: int = 0,
                  n_spectral_bins: int = 0, fb: Optional[torch.Tensor] = None):
+        """n_fft = 0: an augmentation-only plan (mixfe_plan_create_augment), no mel / STFT tables."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("libmixfe plans live on CUDA devices; there is no CPU path")
@@ -198,12 +211,15 @@ class Plan:
         with torch.cuda.device(idx):
             torch.cuda.current_stream()          # make sure the primary context exists
             h = ctypes.c_void_p()
-            _check(lib().mixfe_plan_create(ctypes.byref(h), idx, sample_rate, n_fft, hop, n_mels, n_spectral_bins))
+            if n_fft:
+                _check(lib().mixfe_plan_create(ctypes.byref(h), idx, sample_rate, n_fft, hop, n_mels, n_spectral_bins))
+            else:
+                _check(lib().mixfe_plan_create_augment(ctypes.byref(h), idx, sample_rate))
         self._h = h
         self.n_mels = n_mels
         self.hop = hop
         self.n_fft = n_fft
-        self.feature_dim = int(lib().mixfe_feature_dim(self._h))
+        self.feature_dim = int(lib().mixfe_feature_dim(self._h)) if n_fft else 0
         if fb is not None:
             self.set_filterbank(fb)
 
@@ -214,6 +230,8 @@ class Plan:
         _check(lib().mixfe_plan_set_filterbank(self._h, ctypes.c_void_p(fb.data_ptr())))
 
     def num_frames(self, T: int) -> int:
+        if not self.n_fft:
+            raise ValueError("augmentation-only plan (AudioAugmenter's): it has no STFT / mel tables")
         return 1 + T // self.hop
 
     def workspace_bytes(self) -> int:
@@ -366,6 +384,48 @@ class Plan:
             _check(lib().mixfe_augment(self._h, pin, pout, sb, sc, B, T, params, _ptr(impulse), L,
                                        _stream(self.device)))
         return outs
+
+    def effects(self, x: torch.Tensor, params, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """x: CUDA (B,C,T); params: ctypes array of B AugParams whose stem index 0 holds the decisions (gain, tilt,
+        compressor, band-limit) applied to every channel of clip b.  Returns a new tensor (or `out`)."""
+        if x.dtype != torch.float32:
+            x = x.float()
+        if x.stride(2) != 1:
+            x = x.contiguous()
+        B, C, T = x.shape
+        if out is None:
+            out = torch.empty_strided(x.shape, x.stride(), dtype=torch.float32, device=self.device)
+        else:
+            _check_out(out, x.shape, self.device, "out")
+            if out.stride() != x.stride():
+                raise ValueError("effects: `out` must have the input's strides")
+            (a, b_), (c, d) = _span(x), _span(out)
+            if c < b_ and a < d:
+                raise ValueError("effects: the output buffer overlaps the input")
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_effects(self._h, _ptr(x), _ptr(out), x.stride(0), x.stride(1), B, C, T, params,
+                                       _stream(self.device)))
+        return out
+
+    def reverb(self, x: torch.Tensor, impulse: torch.Tensor) -> torch.Tensor:
+        """x: CUDA (B,C,T), C in {1, 2}; impulse (L,) shared by all clips or (B,L).  0.7 x + 0.3 corr(x, h) (kernel K4)."""
+        if x.dtype != torch.float32:
+            x = x.float()
+        if x.stride(2) != 1:
+            x = x.contiguous()
+        B, C, T = x.shape
+        impulse = impulse.to(self.device, torch.float32).contiguous()
+        if impulse.dim() == 1:
+            stride, L = 0, impulse.shape[0]
+        elif impulse.dim() == 2 and impulse.shape[0] == B:
+            stride, L = impulse.stride(0), impulse.shape[1]
+        else:
+            raise ValueError(f"impulse shape {tuple(impulse.shape)}: (L,) or ({B}, L)")
+        out = torch.empty_strided(x.shape, x.stride(), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_reverb(self._h, _ptr(x), _ptr(out), x.stride(0), x.stride(1), B, C, T, _ptr(impulse),
+                                      stride, L, _stream(self.device)))
+        return out
 
     KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5, "stft_loss": 6}
 

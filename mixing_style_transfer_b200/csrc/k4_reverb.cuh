@@ -72,8 +72,13 @@ struct K4Params {
     float* out[kNumStems];                 // augmented stems (K3 output); updated in place by the last pass
     long long stride_b, stride_c;
     int T, L, half, seg_len, n_seg, n_chunks;
+    // standalone mode (AudioAugmenter.apply_reverb on one tensor, :458-479): out[0] = 0.7 sa_in + 0.3 corr(sa_in, h),
+    // no stem sum, no redistribution; n_ch = 1 packs a single channel (imaginary part zero)
+    int standalone, n_ch;
+    const float* sa_in;
+    long long imp_stride;                  // floats between the impulses of consecutive clips (0: one impulse for all)
     const int* slot_clip;                  // [n_slots] clip index of each reverb slot
-    const float* impulse;                  // [B][L]
+    const float* impulse;                  // [B][L] (row b at impulse + b * imp_stride)
     float2* X;                             // [n_slots][n_seg][2^20]
     float2* H;                             // [n_slots][2^20]
     const double* part_energy;             // [B][4][2][n_chunks]
@@ -99,7 +104,7 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
     float2* const Hs = p.H + (long long)slot * kRevN;
 
     for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
-    if (MODE == kColsInv) {
+    if (MODE == kColsInv && !p.standalone) {
         // energy shares of the four stems (recomputed by every CTA: 8 * n_chunks doubles per stem)
         if (warp < kNumStems) {
             double e = 0.0;
@@ -125,15 +130,20 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
                 if (t >= 0 && t < p.T) {
                     const long long o = (long long)b * p.stride_b + t;
                     float mL = 0.0f, mR = 0.0f;
+                    if (p.standalone) {
+                        mL = __ldg(p.sa_in + o);
+                        if (p.n_ch == 2) mR = __ldg(p.sa_in + o + p.stride_c);
+                    } else {
 #pragma unroll
-                    for (int s = 0; s < kNumStems; ++s) {              // ((0 + v) + b) + d) + o
-                        mL += p.out[s][o];
-                        mR += p.out[s][o + p.stride_c];
+                        for (int s = 0; s < kNumStems; ++s) {          // ((0 + v) + b) + d) + o
+                            mL += p.out[s][o];
+                            mR += p.out[s][o + p.stride_c];
+                        }
                     }
                     v = make_float2(mL, mR);
                 }
             } else if (MODE == kColsH) {
-                if (n < p.L) v.x = __ldg(p.impulse + (long long)b * p.L + n);
+                if (n < p.L) v.x = __ldg(p.impulse + (long long)b * p.imp_stride + n);
             } else {
                 v = Xs[n];
             }
@@ -180,7 +190,11 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
                 Hs[n] = v;
             } else {
                 const long long t = seg0 + n;                        // c[m] is the output sample seg0 + m
-                if (n < p.seg_len && t < p.T) {
+                if (n < p.seg_len && t < p.T && p.standalone) {
+                    const long long o = (long long)b * p.stride_b + t;
+                    p.out[0][o] = __ldg(p.sa_in + o) * 0.7f + v.x * 0.3f;                           // :478-479
+                    if (p.n_ch == 2) p.out[0][o + p.stride_c] = __ldg(p.sa_in + o + p.stride_c) * 0.7f + v.y * 0.3f;
+                } else if (n < p.seg_len && t < p.T) {
                     const long long o = (long long)b * p.stride_b + t;
                     float y[kNumStems][2];
                     float mL = 0.0f, mR = 0.0f;
@@ -214,7 +228,7 @@ __global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int row = blockIdx.x * 8 + warp, seg = blockIdx.y, slot = blockIdx.z;
     float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * kRevN + (long long)row * kRevN2;
-    float2* const Hs = p.H + (long long)slot * kRevN + (long long)row * kRevN2;
+    float2* const Hs = p.H + (p.imp_stride == 0 ? 0ll : (long long)slot * kRevN) + (long long)row * kRevN2;
     for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
     __syncthreads();
     float2* const exw = exall + warp * 1024;
@@ -250,13 +264,123 @@ __global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params 
 }
 
 // ------------------------------------------------------------------------------------------------
-// host side of mixfe_augment
+// host side of mixfe_augment / mixfe_effects / mixfe_reverb
 // ------------------------------------------------------------------------------------------------
 inline double pole_radius(double a1, double a2) {
     const double disc = a1 * a1 - 4.0 * a2;
     if (disc < 0.0) return std::sqrt(a2);
     const double r1 = std::fabs((-a1 + std::sqrt(disc)) * 0.5), r2 = std::fabs((-a1 - std::sqrt(disc)) * 0.5);
     return r1 > r2 ? r1 : r2;
+}
+
+inline void mat2_mul(const double (&a)[4], const double (&b)[4], double (&c)[4]) {
+    const double r[4] = {a[0] * b[0] + a[1] * b[2], a[0] * b[1] + a[1] * b[3], a[2] * b[0] + a[3] * b[2], a[2] * b[1] + a[3] * b[3]};
+    for (int i = 0; i < 4; ++i) c[i] = r[i];
+}
+
+// One normalised section (b0 b1 b2 a1 a2) -> the tables of biquad_block (k3_augment.cuh).
+inline void build_section(const double (&c)[5], AugSection& out) {
+    std::memset(&out, 0, sizeof out);
+    out.b0 = (float)c[0]; out.b1 = (float)c[1]; out.b2 = (float)c[2]; out.a1 = (float)c[3]; out.a2 = (float)c[4];
+    out.form = (c[1] == 2.0 * c[0] && c[2] == c[0]) ? 1 : ((c[1] == -2.0 * c[0] && c[2] == c[0]) ? 2 : 0);
+    // The lane recurrences run with the fp32 coefficients; the tables describe exactly that system.
+    const double a1 = (double)out.a1, a2 = (double)out.a2;
+    const double A[4] = {-a1, -a2, 1.0, 0.0};
+    double P[4] = {1.0, 0.0, 0.0, 1.0};
+    for (int n = 0; n < kAugV; ++n) mat2_mul(P, A, P);
+    for (int i = 0; i < 4; ++i) out.mp[0][i] = P[i];       // M = A^16
+    for (int d = 1; d < 5; ++d) mat2_mul(out.mp[d - 1], out.mp[d - 1], out.mp[d]);
+}
+
+// Static compressor constants (k3_augment.cuh): the knee in the amplitude domain and 2^(c0 + c1 lg2 a).
+inline void compressor_constants(float thr_db, float ratio, float& knee, float& c0, float& c1) {
+    // smallest fp32 a with fl32(20 * fl32(log10 a)) > thr, as the reference's fp32 mask `audio_db > threshold` (:440)
+    auto db32 = [](float a) { return 20.0f * (float)std::log10((double)a); };
+    float a = (float)std::pow(10.0, (double)thr_db / 20.0);
+    for (int i = 0; i < 8 && db32(a) > thr_db; ++i) a = std::nextafterf(a, 0.0f);
+    for (int i = 0; i < 16 && !(db32(a) > thr_db); ++i) a = std::nextafterf(a, INFINITY);
+    knee = a;
+    const double inv = 1.0 / (double)ratio;
+    c1 = (float)inv;
+    c0 = (float)((double)thr_db * (1.0 - inv) * 0.16609640474436813);        // log2(10) / 20
+}
+
+struct AugLaunch {                         // what the three entry points share
+    std::vector<AugClipDev> clips;
+    std::vector<AugSection> sections;      // [B][4][3]
+    int chunk = 0, warm = 0, n_chunks = 0;
+};
+
+// decisions -> kernel form; pole radii size the warm-up of the chunked scan
+inline int prepare_augment(const mixfe_aug_params* params, int B, int T, int n_stems, AugLaunch& L) {
+    L.clips.assign(B, AugClipDev{});
+    L.sections.assign((size_t)B * kNumStems * kAugSections, AugSection{});
+    double rmax = 0.0;
+    for (int b = 0; b < B; ++b) {
+        AugClipDev& c = L.clips[b];
+        const mixfe_aug_params& q = params[b];
+        for (int s = 0; s < n_stems; ++s) {
+            c.gain[s] = q.gain_lin[s];
+            c.flags[s] = (q.tilt_on[s] ? 1 : 0) | (q.comp_on[s] ? 2 : 0) | (q.bw_on[s] ? 4 : 0);
+            c.knee[s] = INFINITY; c.c0[s] = 0.0f; c.c1[s] = 1.0f;
+            if (q.comp_on[s]) {
+                if (!(q.comp_ratio[s] > 0.0f) || !std::isfinite(q.comp_threshold_db[s]))
+                    return fail(MIXFE_EINVAL, "clip %d stem %d: compressor threshold %g dB, ratio %g", b, s,
+                                (double)q.comp_threshold_db[s], (double)q.comp_ratio[s]);
+                compressor_constants(q.comp_threshold_db[s], q.comp_ratio[s], c.knee[s], c.c0[s], c.c1[s]);
+            }
+            for (int sec = 0; sec < kAugSections; ++sec) {
+                const double* sos = sec == 0 ? q.tilt_sos[s] : q.bw_sos[s] + 6 * (sec - 1);
+                const bool on = sec == 0 ? q.tilt_on[s] != 0 : q.bw_on[s] != 0;
+                if (!on) continue;
+                const double a0 = sos[3];
+                if (a0 == 0.0) return fail(MIXFE_EINVAL, "clip %d stem %d: a0 = 0", b, s);
+                const double cn[5] = {sos[0] / a0, sos[1] / a0, sos[2] / a0, sos[4] / a0, sos[5] / a0};
+                const double r = pole_radius(cn[3], cn[4]);
+                if (!(r < 1.0)) return fail(MIXFE_EINVAL, "clip %d stem %d: unstable filter section (pole radius %g)", b, s, r);
+                rmax = std::max(rmax, r);
+                build_section(cn, L.sections[((size_t)b * kNumStems + s) * kAugSections + sec]);
+            }
+        }
+    }
+    // warm-up so that r^warm < 1e-13, in whole 512-sample blocks; chunk >= 8 * warm keeps the overhead <= 12.5 %
+    int warm = 0;
+    if (rmax > 0.0) {
+        const double need = std::log(1e-13) / std::log(rmax);
+        warm = need > 4.0e6 ? 1 << 30 : ((int)std::ceil(need) + kAugBlock - 1) / kAugBlock * kAugBlock;
+    }
+    int chunk = 8192;
+    while (chunk < 8 * (long long)warm && chunk < T) chunk *= 2;
+    if (chunk >= T || warm >= T) { chunk = (T + kAugBlock - 1) / kAugBlock * kAugBlock; warm = 0; }   // one exact chunk per row
+    L.chunk = chunk; L.warm = warm; L.n_chunks = (T + chunk - 1) / chunk;
+    return MIXFE_OK;
+}
+
+struct ReverbLayout { int n_seg = 0, seg_len = 0; };
+
+// the five launches of the FFT-domain correlation for the slots listed in p4.slot_clip
+inline int launch_reverb(mixfe_plan* pl, K4Params& p4, int n_slots, cudaStream_t stream) {
+    const int smem_cols = (kColsPerCta * kColStride + 1024) * (int)sizeof(float2);
+    const int smem_rows = (8 * 1024 + 1024) * (int)sizeof(float2);
+    int rc;
+    if ((rc = smem_optin(k4_cols<kColsX>, pl->device, smem_cols)) || (rc = smem_optin(k4_cols<kColsH>, pl->device, smem_cols)) ||
+        (rc = smem_optin(k4_cols<kColsInv>, pl->device, smem_cols)) || (rc = smem_optin(k4_rows<kRowsX>, pl->device, smem_rows)) ||
+        (rc = smem_optin(k4_rows<kRowsH>, pl->device, smem_rows)))
+        return rc;
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_REVERB, stream);
+        // one impulse for all clips (imp_stride 0): its spectrum is computed once and every slot reads slot 0's
+        const int h_slots = p4.imp_stride == 0 ? 1 : n_slots;
+        const dim3 g1(kRevN2 / kColsPerCta, 1, h_slots), gs(kRevN2 / kColsPerCta, p4.n_seg, n_slots);
+        k4_cols<kColsH><<<g1, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsH><<<dim3(kRevN1 / 8, 1, h_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsX><<<gs, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsX><<<dim3(kRevN1 / 8, p4.n_seg, n_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsInv><<<gs, 256, smem_cols, stream>>>(p4);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 5;
+    return MIXFE_OK;
 }
 
 inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* const out[kNumStems],
@@ -273,31 +397,13 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     if (stride_c < T || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
     DeviceGuard guard(pl->device);
 
-    // ---- decisions -> kernel form; pole radii size the warm-up of the chunked scan ---------------
-    std::vector<AugClipDev> clips(B);
+    AugLaunch al;
+    int rc = prepare_augment(params, B, T, kNumStems, al);
+    if (rc) return rc;
     std::vector<int> slot_clip;
-    double rmax = 0.0;
     for (int b = 0; b < B; ++b) {
-        AugClipDev& c = clips[b];
-        std::memset(&c, 0, sizeof c);
-        const mixfe_aug_params& q = params[b];
-        for (int s = 0; s < kNumStems; ++s) {
-            c.gain[s] = q.gain_lin[s];
-            c.flags[s] = (q.tilt_on[s] ? 1 : 0) | (q.comp_on[s] ? 2 : 0) | (q.bw_on[s] ? 4 : 0);
-            for (int sec = 0; sec < 3; ++sec) {
-                const double* sos = sec == 0 ? q.tilt_sos[s] : q.bw_sos[s] + 6 * (sec - 1);
-                const bool on = sec == 0 ? q.tilt_on[s] != 0 : q.bw_on[s] != 0;
-                if (!on) continue;
-                const double a0 = sos[3];
-                if (a0 == 0.0) return fail(MIXFE_EINVAL, "clip %d stem %d: a0 = 0", b, s);
-                c.sos[s][sec][0] = sos[0] / a0; c.sos[s][sec][1] = sos[1] / a0; c.sos[s][sec][2] = sos[2] / a0;
-                c.sos[s][sec][3] = sos[4] / a0; c.sos[s][sec][4] = sos[5] / a0;
-                const double r = pole_radius(c.sos[s][sec][3], c.sos[s][sec][4]);
-                if (!(r < 1.0)) return fail(MIXFE_EINVAL, "clip %d stem %d: unstable filter section (pole radius %g)", b, s, r);
-                rmax = std::max(rmax, r);
-            }
-        }
-        c.reverb_on = q.reverb_on ? 1 : 0;
+        AugClipDev& c = al.clips[b];
+        c.reverb_on = params[b].reverb_on ? 1 : 0;
         c.reverb_slot = -1;
         if (c.reverb_on) {
             if (!impulse || L <= 0) return fail(MIXFE_EINVAL, "clip %d wants reverb but no impulse was given", b);
@@ -305,16 +411,7 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
             slot_clip.push_back(b);
         }
     }
-    // warm-up so that r^warm < 1e-13, in whole 512-sample blocks; chunk >= 8 * warm keeps the overhead <= 12.5 %
-    int warm = 0;
-    if (rmax > 0.0) {
-        const double need = std::log(1e-13) / std::log(rmax);
-        warm = need > 4.0e6 ? 1 << 30 : ((int)std::ceil(need) + kAugBlock - 1) / kAugBlock * kAugBlock;
-    }
-    int chunk = 8192;
-    while (chunk < 8 * (long long)warm && chunk < T) chunk *= 2;
-    if (chunk >= T || warm >= T) { chunk = (T + kAugBlock - 1) / kAugBlock * kAugBlock; warm = 0; }   // one exact chunk per row
-    const int n_chunks = (T + chunk - 1) / chunk;
+    const int n_chunks = al.n_chunks;
 
     // ---- workspace -------------------------------------------------------------------------------------
     const int n_slots = (int)slot_clip.size();
@@ -327,21 +424,25 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_clips = carve(sizeof(AugClipDev) * B);
+    const size_t o_sections = carve(sizeof(AugSection) * al.sections.size());
     const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
     const size_t o_slots = carve(sizeof(int) * (size_t)std::max(1, n_slots));
     const size_t o_X = carve(sizeof(float2) * (size_t)kRevN * n_slots * std::max(1, n_seg));
     const size_t o_H = carve(sizeof(float2) * (size_t)kRevN * n_slots);
-    int rc = ensure_workspace(pl, off, stream);
+    rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, al.clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size(),
+                               cudaMemcpyHostToDevice, stream));
     if (n_slots)
         MIXFE_CUDA(cudaMemcpyAsync(ws + o_slots, slot_clip.data(), sizeof(int) * n_slots, cudaMemcpyHostToDevice, stream));
 
     K3Params p3{};
     for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in[s]; p3.out[s] = out[s]; }
-    p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = chunk; p3.warm = warm;
-    p3.n_chunks = n_chunks; p3.clips = reinterpret_cast<const AugClipDev*>(ws + o_clips);
+    p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = al.chunk; p3.warm = al.warm;
+    p3.n_chunks = n_chunks; p3.n_stems = kNumStems; p3.clips = reinterpret_cast<const AugClipDev*>(ws + o_clips);
+    p3.sections = reinterpret_cast<const AugSection*>(ws + o_sections);
     p3.part_energy = reinterpret_cast<double*>(ws + o_energy);
     {
         KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
@@ -355,26 +456,84 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     for (int s = 0; s < kNumStems; ++s) p4.out[s] = out[s];
     p4.stride_b = stride_b; p4.stride_c = stride_c; p4.T = T; p4.L = L; p4.half = L / 2; p4.seg_len = seg_len;
     p4.n_seg = n_seg; p4.n_chunks = n_chunks; p4.slot_clip = reinterpret_cast<const int*>(ws + o_slots);
+    p4.standalone = 0; p4.n_ch = 2; p4.sa_in = nullptr; p4.imp_stride = L;
     p4.impulse = impulse; p4.X = reinterpret_cast<float2*>(ws + o_X); p4.H = reinterpret_cast<float2*>(ws + o_H);
     p4.part_energy = p3.part_energy; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
-    const int smem_cols = (kColsPerCta * kColStride + 1024) * (int)sizeof(float2);
-    const int smem_rows = (8 * 1024 + 1024) * (int)sizeof(float2);
-    if ((rc = smem_optin(k4_cols<kColsX>, pl->device, smem_cols)) || (rc = smem_optin(k4_cols<kColsH>, pl->device, smem_cols)) ||
-        (rc = smem_optin(k4_cols<kColsInv>, pl->device, smem_cols)) || (rc = smem_optin(k4_rows<kRowsX>, pl->device, smem_rows)) ||
-        (rc = smem_optin(k4_rows<kRowsH>, pl->device, smem_rows)))
-        return rc;
+    return launch_reverb(pl, p4, n_slots, stream);
+}
+
+// AudioAugmenter.apply_spectral_tilt / apply_compression / apply_bandwidth_limit (:421-456) and the gain of :389-392 on
+// ONE tensor (B, C, T): the decisions of params[b] (stem index 0) are applied to every channel of clip b.
+inline int run_effects(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                       int T, const mixfe_aug_params* params, cudaStream_t stream) {
+    if (!pl || !in || !out || !params) return fail(MIXFE_EINVAL, "null argument");
+    if (in == out) return fail(MIXFE_EINVAL, "out must not alias in");
+    if (B < 0 || C <= 0 || T <= 0) return fail(MIXFE_EINVAL, "bad B, C or T");
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535 || C > 65535) return fail(MIXFE_EINVAL, "B or C > 65535 per call");
+    if ((C > 1 && stride_c < T) || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
+    DeviceGuard guard(pl->device);
+    AugLaunch al;
+    int rc = prepare_augment(params, B, T, 1, al);
+    if (rc) return rc;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_clips = carve(sizeof(AugClipDev) * B);
+    const size_t o_sections = carve(sizeof(AugSection) * al.sections.size());
+    rc = ensure_workspace(pl, off, stream);
+    if (rc) return rc;
+    char* ws = reinterpret_cast<char*>(pl->ws);
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, al.clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size(),
+                               cudaMemcpyHostToDevice, stream));
+    K3Params p3{};
+    for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in; p3.out[s] = out; }
+    p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = al.chunk; p3.warm = al.warm;
+    p3.n_chunks = al.n_chunks; p3.n_stems = 1; p3.clips = reinterpret_cast<const AugClipDev*>(ws + o_clips);
+    p3.sections = reinterpret_cast<const AugSection*>(ws + o_sections);
+    p3.part_energy = nullptr;
     {
-        KernelTimer timer(pl, MIXFE_KERNEL_REVERB, stream);
-        const dim3 g1(kRevN2 / kColsPerCta, 1, n_slots), gs(kRevN2 / kColsPerCta, n_seg, n_slots);
-        k4_cols<kColsH><<<g1, 256, smem_cols, stream>>>(p4);
-        k4_rows<kRowsH><<<dim3(kRevN1 / 8, 1, n_slots), 256, smem_rows, stream>>>(p4);
-        k4_cols<kColsX><<<gs, 256, smem_cols, stream>>>(p4);
-        k4_rows<kRowsX><<<dim3(kRevN1 / 8, n_seg, n_slots), 256, smem_rows, stream>>>(p4);
-        k4_cols<kColsInv><<<gs, 256, smem_cols, stream>>>(p4);
+        KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
+        k3_augment<<<dim3(al.n_chunks, C, B), 32, 0, stream>>>(p3);
     }
     MIXFE_CUDA(cudaGetLastError());
-    launch_counter() += 5;
+    launch_counter()++;
     return MIXFE_OK;
+}
+
+// AudioAugmenter.apply_reverb (:458-479) on ONE tensor (B, C, T), C in {1, 2}: out = 0.7 in + 0.3 corr(in, h_b).
+inline int run_reverb(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                      int T, const float* impulse, long long impulse_stride_b, int L, cudaStream_t stream) {
+    if (!pl || !in || !out || !impulse) return fail(MIXFE_EINVAL, "null argument");
+    if (in == out) return fail(MIXFE_EINVAL, "out must not alias in");
+    if (B < 0 || T <= 0 || L <= 0) return fail(MIXFE_EINVAL, "bad B, T or L");
+    if (C != 1 && C != 2) return fail(MIXFE_EINVAL, "C=%d: one or two channels per clip (split wider tensors into pairs)", C);
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535) return fail(MIXFE_EINVAL, "B > 65535 clips per call");
+    if ((C > 1 && stride_c < T) || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
+    if (impulse_stride_b != 0 && impulse_stride_b < L) return fail(MIXFE_EINVAL, "impulse stride smaller than L");
+    if (L > kRevN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevN / 2);
+    DeviceGuard guard(pl->device);
+    const int seg_len = kRevN - L + 1, n_seg = (T + seg_len - 1) / seg_len;
+    std::vector<int> slot_clip(B);
+    for (int b = 0; b < B; ++b) slot_clip[b] = b;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_slots = carve(sizeof(int) * (size_t)B);
+    const size_t o_X = carve(sizeof(float2) * (size_t)kRevN * B * n_seg);
+    const size_t o_H = carve(sizeof(float2) * (size_t)kRevN * (impulse_stride_b == 0 ? 1 : B));
+    int rc = ensure_workspace(pl, off, stream);
+    if (rc) return rc;
+    char* ws = reinterpret_cast<char*>(pl->ws);
+    MIXFE_CUDA(cudaMemcpyAsync(ws + o_slots, slot_clip.data(), sizeof(int) * B, cudaMemcpyHostToDevice, stream));
+    K4Params p4{};
+    p4.out[0] = out;
+    p4.stride_b = stride_b; p4.stride_c = stride_c; p4.T = T; p4.L = L; p4.half = L / 2; p4.seg_len = seg_len;
+    p4.n_seg = n_seg; p4.n_chunks = 0; p4.slot_clip = reinterpret_cast<const int*>(ws + o_slots);
+    p4.standalone = 1; p4.n_ch = C; p4.sa_in = in; p4.imp_stride = impulse_stride_b;
+    p4.impulse = impulse; p4.X = reinterpret_cast<float2*>(ws + o_X); p4.H = reinterpret_cast<float2*>(ws + o_H);
+    p4.part_energy = nullptr; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
+    return launch_reverb(pl, p4, B, stream);
 }
 
 }  // namespace mixfe

@@ -17,7 +17,7 @@
 //   are formed from the sub-block energies, sorted in shared memory (bitonic), and the two quantiles read off.
 #pragma once
 
-#include "k3_augment.cuh"
+#include "biquad_f64.cuh"
 
 namespace mixfe {
 
@@ -96,8 +96,8 @@ __global__ void __launch_bounds__(kLoudSignals * 32) k7_kweight_energy(const __g
         double v[kAugV];
 #pragma unroll
         for (int n = 0; n < kAugV; ++n) v[n] = (double)x[n];
-        biquad_block(v, p.sos[0], tables[sig][0], lane);
-        biquad_block(v, p.sos[1], tables[sig][1], lane);
+        biquad_block64(v, p.sos[0], tables[sig][0], lane);
+        biquad_block64(v, p.sos[1], tables[sig][1], lane);
         if (blk + kAugBlock > c0) {                        // the block reaches into the chunk: bin its squares
             const long long first = blk > c0 ? blk : c0;
             const int bA = (int)((first - c0) / p.sub);

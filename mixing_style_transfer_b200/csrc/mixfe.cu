@@ -270,6 +270,26 @@ int build_generic_tables(mixfe_plan* pl) {
     return MIXFE_OK;
 }
 
+// Twiddles of the one-warp 1024-point transform (K1, K4) and of the 2^20-point four-step FFT of the reverb (K4).
+int upload_fft_twiddles(mixfe_plan* pl) {
+    std::vector<float2> tw(1024), twf(1024), twl(1024);
+    for (int k1 = 0; k1 < 32; ++k1)
+        for (int n2 = 0; n2 < 32; ++n2) {
+            const double a = -2.0 * M_PI * (double)(k1 * n2) / 1024.0;
+            tw[k1 * 32 + n2] = make_float2((float)std::cos(a), (float)std::sin(a));
+        }
+    for (int e = 0; e < 1024; ++e) {
+        const double a = -2.0 * M_PI * (double)e / 1048576.0;
+        twf[e] = make_float2((float)std::cos(a), (float)std::sin(a));
+        const double c = -2.0 * M_PI * (double)e / 1024.0;
+        twl[e] = make_float2((float)std::cos(c), (float)std::sin(c));
+    }
+    int rc = upload(&pl->d_tw, tw);
+    if (!rc) rc = upload(&pl->d_twfine, twf);
+    if (!rc) rc = upload(&pl->d_twlin, twl);
+    return rc;
+}
+
 // Which kernel serves the plan: K1 for n_fft = 1024 when its shared-memory map fits, else K1G.
 int build_tables(mixfe_plan* pl) {
     int rc = build_generic_tables(pl);
@@ -286,6 +306,7 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
                  int T, float* features, float* logmel, long long lm_stride_b, float* melpow,
                  long long mp_stride_b, cudaStream_t stream) {
     if (!pl || !stems) return fail(MIXFE_EINVAL, "null plan or stems");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     for (int s = 0; s < 4; ++s)
         if (!stems[s]) return fail(MIXFE_EINVAL, "stems[%d] is NULL", s);
     if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
@@ -373,6 +394,7 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
                         const float* grad_logmel, long long g_stride_b, float* const grad_stems[4], long long ostride_b,
                         long long ostride_c, cudaStream_t stream) {
     if (!pl || !stems || !grad_stems || !grad_logmel) return fail(MIXFE_EINVAL, "null plan, stems or gradients");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     for (int s = 0; s < 4; ++s)
         if (!stems[s] || !grad_stems[s]) return fail(MIXFE_EINVAL, "stems[%d] or grad_stems[%d] is NULL", s, s);
     if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
@@ -429,6 +451,7 @@ void k_weighting(double fs, double (&sos)[2][5]) {
 int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B, int T,
                        float* out, float* out_iqr, cudaStream_t stream) {
     if (!pl || !stems || (!out && !out_iqr)) return fail(MIXFE_EINVAL, "null plan, stems or output");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     for (int s = 0; s < 4; ++s)
         if (!stems[s]) return fail(MIXFE_EINVAL, "stems[%d] is NULL", s);
     if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
@@ -475,6 +498,7 @@ int run_gated_loudness(mixfe_plan* pl, const float* const stems[4], long long st
 int stft_loss_common(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long xs_b, long long xs_c,
                      long long ys_b, long long ys_c, K8Params& p) {
     if (!pl || !x || !y) return fail(MIXFE_EINVAL, "null plan, x or y");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     if (B < 0 || C <= 0 || T < 0) return fail(MIXFE_EINVAL, "bad B, C or T");
     if (T <= pl->n_fft / 2)
         return fail(MIXFE_ESHORT, "Argument #4: Padding size should be less than the corresponding input dimension, "
@@ -585,22 +609,30 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     const int sd = n_spectral_bins > 0 ? n_spectral_bins + 2 : 5;
     pl->D = 4 * (6 + sd + 3) + 4 + 4;
     pl->fb = default_filterbank(sample_rate, n_fft, n_mels);
-    std::vector<float2> tw(1024), twf(1024), twl(1024);
-    for (int k1 = 0; k1 < 32; ++k1)
-        for (int n2 = 0; n2 < 32; ++n2) {
-            const double a = -2.0 * M_PI * (double)(k1 * n2) / 1024.0;
-            tw[k1 * 32 + n2] = make_float2((float)std::cos(a), (float)std::sin(a));
-        }
-    for (int e = 0; e < 1024; ++e) {
-        const double a = -2.0 * M_PI * (double)e / 1048576.0;
-        twf[e] = make_float2((float)std::cos(a), (float)std::sin(a));
-        const double c = -2.0 * M_PI * (double)e / 1024.0;
-        twl[e] = make_float2((float)std::cos(c), (float)std::sin(c));
-    }
-    int rc = upload(&pl->d_tw, tw);
-    if (!rc) rc = upload(&pl->d_twfine, twf);
-    if (!rc) rc = upload(&pl->d_twlin, twl);
+    int rc = upload_fft_twiddles(pl);
     if (!rc) rc = build_tables(pl);
+    if (rc) { mixfe_plan_destroy(pl); return rc; }
+    *out = pl;
+    return MIXFE_OK;
+}
+
+int mixfe_plan_create_augment(mixfe_plan** out, int device, int sample_rate) {
+    if (!out) return fail(MIXFE_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (sample_rate <= 0) return fail(MIXFE_EINVAL, "bad plan arguments");
+    int ndev = 0;
+    MIXFE_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(MIXFE_EINVAL, "device %d out of range (%d visible)", device, ndev);
+    DeviceGuard guard(device);
+    cudaDeviceProp prop;
+    MIXFE_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(MIXFE_EUNSUPPORTED, "device %d is sm_%d%d; libmixfe is built for sm_100a only", device,
+                    prop.major, prop.minor);
+    mixfe_plan* pl = new mixfe_plan();
+    pl->n_sms = prop.multiProcessorCount;
+    pl->device = device; pl->sr = sample_rate;              // n_fft = 0 marks the plan as augmentation-only
+    const int rc = upload_fft_twiddles(pl);
     if (rc) { mixfe_plan_destroy(pl); return rc; }
     *out = pl;
     return MIXFE_OK;
@@ -620,6 +652,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
 
 int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
     if (!pl || !fb_host) return fail(MIXFE_EINVAL, "null plan or filterbank");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     DeviceGuard guard(pl->device);
     MIXFE_CUDA(cudaDeviceSynchronize());            // tables may be in use by queued launches
     pl->fb.assign(fb_host, fb_host + (size_t)pl->n_freq * pl->n_mels);
@@ -666,7 +699,9 @@ int mixfe_plan_kernel_time(mixfe_plan* pl, int which, double* total_ms, long lon
 
 int mixfe_feature_dim(const mixfe_plan* pl) { return pl ? pl->D : fail(MIXFE_EINVAL, "null plan"); }
 
-int mixfe_num_frames(const mixfe_plan* pl, int T) { return pl ? 1 + T / pl->hop : fail(MIXFE_EINVAL, "null plan"); }
+int mixfe_num_frames(const mixfe_plan* pl, int T) {
+    return pl && pl->hop ? 1 + T / pl->hop : fail(MIXFE_EINVAL, "null or augmentation-only plan");
+}
 
 size_t mixfe_workspace_bytes(const mixfe_plan* pl) { return pl ? pl->ws_bytes : 0; }
 
@@ -735,6 +770,17 @@ int mixfe_augment(mixfe_plan* pl, const float* const in[MIXFE_NUM_STEMS], float*
                   const float* impulse, int L, void* cuda_stream) {
     return run_augment(pl, in, out, stride_b, stride_c, B, T, params, impulse, L,
                        static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_effects(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                  int T, const mixfe_aug_params* params, void* cuda_stream) {
+    return run_effects(pl, in, out, stride_b, stride_c, B, C, T, params, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_reverb(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                 int T, const float* impulse, long long impulse_stride_b, int L, void* cuda_stream) {
+    return run_reverb(pl, in, out, stride_b, stride_c, B, C, T, impulse, impulse_stride_b, L,
+                      static_cast<cudaStream_t>(cuda_stream));
 }
 
 }  // extern "C"

@@ -232,9 +232,39 @@ def butter_sos(order: int, cutoff_hz: float, btype: str, fs: float) -> List[List
     return sos
 
 
+def butter_sos_batch(order: int, cutoff_hz, btype: str, fs: float):
+    """butter_sos for an array of cutoffs at once (numpy): (n, order // 2, 6).  Same arithmetic, vectorised; used by
+    AudioAugmenter.draw_batch so that a batch's filter design costs one numpy pass."""
+    import numpy as np
+    if order % 2 or btype not in ("low", "high"):
+        raise ValueError("butter_sos: even order and btype in {'low','high'} only")
+    wn = 2.0 * np.asarray(cutoff_hz, dtype=np.float64).reshape(-1) / float(fs)
+    if wn.size and not ((wn > 0.0) & (wn < 1.0)).all():
+        raise ValueError("Digital filter critical frequencies must be 0 < Wn < 1")
+    k_warp = 4.0 * np.tan(np.pi * wn / 2.0)                                   # (n,)
+    m = np.arange(-order + 1, order, 2)
+    p = -np.exp(1j * np.pi * m / (2 * order))                                 # (order,) prototype poles
+    ps = k_warp[:, None] * p[None, :] if btype == "low" else k_warp[:, None] / p[None, :]
+    pz = (4.0 + ps) / (4.0 - ps)
+    gain_den = np.prod(4.0 - ps, axis=1)
+    if btype == "low":
+        gain = (k_warp ** order) * (1.0 / gain_den).real
+        zsign = 1.0
+    else:
+        gain = (1.0 / np.prod(-p)).real * ((4.0 ** order) / gain_den).real
+        zsign = -1.0
+    sos = np.zeros((wn.size, order // 2, 6))
+    for i in range(wn.size):
+        upper = sorted([q for q in pz[i] if q.imag > 0], key=abs)
+        for j, q in enumerate(upper):
+            sos[i, j] = [1.0, 2.0 * zsign, 1.0, 1.0, -2.0 * q.real, abs(q) ** 2]
+        sos[i, 0, :3] *= gain[i]
+    return sos
+
+
 class ClipAugmentation:
     """The random decisions augment_stems makes for one clip, drawn in the reference's order."""
-    __slots__ = ("gain_db", "tilt", "compress", "cutoff_hz", "impulse")
+    __slots__ = ("gain_db", "tilt", "compress", "cutoff_hz", "impulse", "comp_threshold", "comp_ratio")
 
     def __init__(self):
         self.gain_db: Dict[str, Optional[torch.Tensor]] = {}
@@ -242,6 +272,27 @@ class ClipAugmentation:
         self.compress: Dict[str, bool] = {}
         self.cutoff_hz: Dict[str, Optional[float]] = {}
         self.impulse: Optional[torch.Tensor] = None
+        self.comp_threshold: float = -20.0           # apply_compression's defaults (:435), what augment_stems uses
+        self.comp_ratio: float = 4.0
+
+
+class BatchAugmentation:
+    """Decisions for n clips drawn in ONE pass (AudioAugmenter.draw_batch): packed mixfe_aug_params + impulses."""
+    __slots__ = ("n", "params", "impulse", "reverb_rows", "arrays")
+
+    def __init__(self, n, params, impulse, reverb_rows, arrays):
+        self.n, self.params, self.impulse, self.reverb_rows, self.arrays = n, params, impulse, reverb_rows, arrays
+
+    def __len__(self):
+        return self.n
+
+
+def _aug_dtype():
+    import numpy as np
+    return np.dtype([("gain_lin", np.float32, (4,)), ("tilt_on", np.int32, (4,)), ("tilt_sos", np.float64, (4, 6)),
+                     ("comp_on", np.int32, (4,)), ("comp_threshold_db", np.float32, (4,)), ("comp_ratio", np.float32, (4,)),
+                     ("bw_on", np.int32, (4,)), ("bw_sos", np.float64, (4, 12)), ("reverb_on", np.int32),
+                     ("_pad", np.int32)], align=True)
 
 
 class AudioAugmenter:
@@ -253,6 +304,8 @@ class AudioAugmenter:
         self.prob = prob
         self._device = torch.device(device) if device is not None else None
         self._plans: Dict[int, Plan] = {}
+        self._tilt_sos = {k: butter_sos(2, fc, k, self.sr)[0] for k, fc in (("high", 2000), ("low", 500))}   # :426-429
+        self._env: Dict[tuple, torch.Tensor] = {}
 
     # -- decisions (host RNG, identical draw order to the reference) ---------------------------
     def draw(self, stem_names=STEMS, impulse_device="cpu") -> ClipAugmentation:
@@ -273,11 +326,63 @@ class AudioAugmenter:
             if torch.rand(1) < self.prob:
                 d.cutoff_hz[name] = (torch.rand(1) * 8000 + 4000).item()
         if torch.rand(1) < self.prob:
-            decay = 0.5
-            n = int(self.sr * decay)
-            t = torch.linspace(0, decay, n, device=impulse_device)
-            d.impulse = torch.exp(-t / (decay / 4)) * torch.randn(n, device=impulse_device) * 0.1
+            d.impulse = self._draw_impulse(0.5, impulse_device)
         return d
+
+    def _draw_impulse(self, decay: float, device) -> torch.Tensor:
+        """:460-463 -- exp(-t / (decay/4)) * randn * 0.1 with t = linspace(0, decay, int(sr*decay)), on `device`."""
+        n = int(self.sr * decay)
+        t = torch.linspace(0, decay, n, device=device)
+        return torch.exp(-t / (decay / 4)) * torch.randn(n, device=device) * 0.1
+
+    def draw_batch(self, n: int, impulse_device="cpu") -> BatchAugmentation:
+        """Decisions for n clips from ONE torch.rand call (global CPU generator) and one randn for the impulses.
+
+        ADDITIVE API.  Same distributions and gates as augment_stems (:385-409), but the uniforms are consumed as a
+        block u[n, 4, 7] = (gain gate, gain, tilt gate, tilt kind, compressor gate, band-limit gate, cutoff) followed
+        by v[n] (reverb gate) instead of the reference's data-dependent sequence, so the stream differs from n calls
+        of draw(); use draw() when the reference's RNG stream matters.  The filter design runs vectorised in numpy;
+        the result is already packed for the kernels (no per-clip Python)."""
+        import numpy as np
+        u = torch.rand(n, 4, 7).numpy()
+        v = torch.rand(n).numpy()
+        arr = (AugParams * n)()
+        a = np.frombuffer(arr, dtype=_aug_dtype())
+        gain_on = u[:, :, 0] < self.prob
+        gain_db = (torch.from_numpy(u[:, :, 1].copy()) * 2 * self.gain_range - self.gain_range)
+        a["gain_lin"] = np.where(gain_on, (10 ** (gain_db / 20)).numpy(), np.float32(1.0))
+        tilt_on = u[:, :, 2] < self.prob
+        high = u[:, :, 3] < 0.5
+        a["tilt_on"] = tilt_on
+        hi, lo = np.asarray(self._tilt_sos["high"]), np.asarray(self._tilt_sos["low"])
+        a["tilt_sos"] = np.where(tilt_on[..., None], np.where(high[..., None], hi, lo), 0.0)
+        a["comp_on"] = u[:, :, 4] < self.prob
+        a["comp_threshold_db"] = -20.0
+        a["comp_ratio"] = 4.0
+        bw_on = u[:, :, 5] < self.prob
+        a["bw_on"] = bw_on
+        fc = (torch.from_numpy(u[:, :, 6].copy()) * 8000 + 4000).numpy().astype(np.float64)
+        if bw_on.any():
+            sos = butter_sos_batch(4, fc[bw_on], "low", self.sr).reshape(-1, 12)
+            full = np.zeros((n, 4, 12))
+            full[bw_on] = sos
+            a["bw_sos"] = full
+        rev = v < self.prob
+        a["reverb_on"] = rev
+        rows = np.nonzero(rev)[0]
+        impulse = None
+        if rows.size:
+            L = int(self.sr * 0.5)
+            key = (L, str(impulse_device))
+            env = self._env.get(key)
+            if env is None:
+                t = torch.linspace(0, 0.5, L, device=impulse_device)
+                env = self._env[key] = torch.exp(-t / (0.5 / 4))
+            impulse = torch.zeros((n, L), dtype=torch.float32, device=impulse_device)
+            impulse[torch.from_numpy(rows).to(impulse_device)] = env * torch.randn(rows.size, L, device=impulse_device) * 0.1
+        return BatchAugmentation(n, arr, impulse, rows, {"gain_on": gain_on, "gain_db": gain_db.numpy(), "tilt_on": tilt_on,
+                                                         "tilt_high": high, "comp_on": np.asarray(a["comp_on"]).astype(bool),
+                                                         "bw_on": bw_on, "cutoff_hz": fc, "reverb_on": rev})
 
     def _pack(self, decisions: List[ClipAugmentation]):
         arr = (AugParams * len(decisions))()
@@ -290,10 +395,12 @@ class AudioAugmenter:
                 tilt = d.tilt.get(name)
                 p.tilt_on[i] = 1 if tilt else 0
                 if tilt:
-                    sos = butter_sos(2, 2000, "high", self.sr) if tilt == "high" else butter_sos(2, 500, "low", self.sr)
+                    sos = self._tilt_sos[tilt]
                     for j in range(6):
-                        p.tilt_sos[i][j] = sos[0][j]
+                        p.tilt_sos[i][j] = sos[j]
                 p.comp_on[i] = 1 if d.compress.get(name) else 0
+                p.comp_threshold_db[i] = float(d.comp_threshold)
+                p.comp_ratio[i] = float(d.comp_ratio)
                 fc = d.cutoff_hz.get(name)
                 p.bw_on[i] = 1 if fc is not None else 0
                 if fc is not None:
@@ -307,7 +414,7 @@ class AudioAugmenter:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         pl = self._plans.get(idx)
         if pl is None:
-            pl = Plan(torch.device("cuda", idx), self.sr, 1024, 256, 128, 0)
+            pl = Plan(torch.device("cuda", idx), self.sr)          # augmentation-only plan: no mel / STFT tables
             self._plans[idx] = pl
         return pl
 
@@ -322,10 +429,11 @@ class AudioAugmenter:
         decisions = [self.draw(tuple(stems_dict.keys()), imp_dev) for _ in range(B)]
         return self.apply(stems_dict, decisions)
 
-    def apply(self, stems_dict, decisions: List[ClipAugmentation], out=None):
-        """Run the augmentation kernels with explicit decisions (one per clip).  `out`: optional dict of
-        preallocated CUDA tensors (same shapes and strides as the inputs, e.g. the negatives' slice of the
-        batch the anchors live in) that receive the augmented stems -- no extra copy."""
+    def apply(self, stems_dict, decisions, out=None):
+        """Run the augmentation kernels with explicit decisions: a list of ClipAugmentation (one per clip) or the
+        BatchAugmentation of draw_batch.  `out`: optional dict of preallocated CUDA tensors (same shapes and
+        strides as the inputs, e.g. the negatives' slice of the batch the anchors live in) that receive the
+        augmented stems -- no extra copy."""
         first = stems_dict[STEMS[0]]
         src_device = first.device
         device = _resolve_device(first, self._device)
@@ -334,19 +442,25 @@ class AudioAugmenter:
         if len(decisions) != B:
             raise ValueError(f"{len(decisions)} decisions for {B} clips")
         impulse = None
-        lens = {int(d.impulse.shape[0]) for d in decisions if d.impulse is not None}
-        if lens:
-            if len(lens) != 1:
-                raise ValueError("impulses of different lengths in one batch")
-            L = lens.pop()
-            impulse = torch.zeros((B, L), dtype=torch.float32, device=device)
-            for b, d in enumerate(decisions):
-                if d.impulse is not None:
-                    impulse[b].copy_(d.impulse.to(device, torch.float32), non_blocking=True)
+        if isinstance(decisions, BatchAugmentation):
+            params = decisions.params
+            if decisions.impulse is not None:
+                impulse = decisions.impulse.to(device, non_blocking=True)
+        else:
+            params = self._pack(decisions)
+            lens = {int(d.impulse.shape[0]) for d in decisions if d.impulse is not None}
+            if lens:
+                if len(lens) != 1:
+                    raise ValueError("impulses of different lengths in one batch")
+                L = lens.pop()
+                impulse = torch.zeros((B, L), dtype=torch.float32, device=device)
+                for b, d in enumerate(decisions):
+                    if d.impulse is not None:
+                        impulse[b].copy_(d.impulse.to(device, torch.float32), non_blocking=True)
         pre = None
         if out is not None:
             pre = [out[n] if out[n].dim() == 3 else out[n].unsqueeze(0) for n in STEMS]
-        outs = self._plan(device).augment(stems, self._pack(decisions), impulse, pre)
+        outs = self._plan(device).augment(stems, params, impulse, pre)
         if out is not None:
             return {k: out[k] for k in stems_dict.keys()}
         result = {}
@@ -357,35 +471,77 @@ class AudioAugmenter:
         # keep the caller's key order (the reference builds the new dict in stems_dict order)
         return {k: result[k] for k in stems_dict.keys()}
 
-    # -- the four single-effect methods of the reference (each on one (2,T) / (B,2,T) tensor) ------
-    def _single(self, audio: torch.Tensor, fill):
-        d = ClipAugmentation()
-        for n in STEMS:
-            d.gain_db[n] = None; d.tilt[n] = None; d.compress[n] = False; d.cutoff_hz[n] = None
-        fill(d)
-        B = audio.shape[0] if audio.dim() == 3 else 1
-        zeros = torch.zeros_like(audio)
-        stems = {"vocals": audio, "bass": zeros, "drums": zeros, "other": zeros}
-        return self.apply(stems, [d] * B)["vocals"]
+    # -- the four single-effect methods of the reference: one (C,T) tensor, or (B,C,T) ------------------------
+    def _one(self, audio: torch.Tensor):
+        """(C,T) | (B,C,T) on any device -> ((B,C,T) CUDA fp32, was_batched, source device)."""
+        if audio.dim() not in (2, 3):
+            raise ValueError(f"audio must be (C,T) or (B,C,T), got {tuple(audio.shape)}")
+        device = _resolve_device(audio, self._device)
+        x = audio.detach()
+        if x.device != device:
+            x = x.to(device, non_blocking=True)
+        return (x if x.dim() == 3 else x.unsqueeze(0)), audio.dim() == 3, audio.device, device
+
+    def _finish(self, y: torch.Tensor, batched: bool, src_device) -> torch.Tensor:
+        if not batched:
+            y = y[0]
+        return y if y.device == src_device else y.to(src_device)
+
+    def _effect(self, audio, fill):
+        x, batched, src, device = self._one(audio)
+        arr = (AugParams * x.shape[0])()
+        for b in range(x.shape[0]):
+            arr[b].gain_lin[0] = 1.0
+            arr[b].comp_threshold_db[0] = -20.0
+            arr[b].comp_ratio[0] = 4.0
+            fill(arr[b])
+        return self._finish(self._plan(device).effects(x, arr), batched, src)
 
     def apply_spectral_tilt(self, audio):
-        """:421-433 -- draws the high/low decision from the global RNG like the reference."""
-        kind = "high" if torch.rand(1) < 0.5 else "low"
-        return self._single(audio, lambda d: d.tilt.__setitem__("vocals", kind))
+        """:421-433 -- draws the high/low decision from the global RNG like the reference (once per call)."""
+        sos = self._tilt_sos["high" if torch.rand(1) < 0.5 else "low"]
+
+        def fill(p):
+            p.tilt_on[0] = 1
+            for j in range(6):
+                p.tilt_sos[0][j] = sos[j]
+        return self._effect(audio, fill)
 
     def apply_compression(self, audio, threshold=-20, ratio=4):
-        """:435-447 (the kernel implements the reference's fixed threshold=-20 dB, ratio=4)."""
-        if threshold != -20 or ratio != 4:
-            raise NotImplementedError("libmixfe's compressor is fixed at threshold=-20 dB, ratio=4 (the values "
-                                      "augment_stems uses)")
-        return self._single(audio, lambda d: d.compress.__setitem__("vocals", True))
+        """:435-447 -- memoryless dB-domain compressor with the reference's two arguments."""
+        if not ratio > 0:
+            raise ValueError(f"ratio must be positive, got {ratio}")
+
+        def fill(p):
+            p.comp_on[0] = 1
+            p.comp_threshold_db[0] = float(threshold)
+            p.comp_ratio[0] = float(ratio)
+        return self._effect(audio, fill)
 
     def apply_bandwidth_limit(self, audio):
-        """:449-456."""
-        fc = (torch.rand(1) * 8000 + 4000).item()
-        return self._single(audio, lambda d: d.cutoff_hz.__setitem__("vocals", fc))
+        """:449-456 -- one cutoff drawn from the global RNG per call, like the reference."""
+        sos = butter_sos(4, (torch.rand(1) * 8000 + 4000).item(), "low", self.sr)
 
-    def apply_reverb(self, audio, decay=0.5):
-        """:458-479."""
-        raise NotImplementedError("standalone apply_reverb: use augment_stems / apply (the reverb kernel works on "
-                                  "the mixture and redistributes by stem energy, :409-417)")
+        def fill(p):
+            p.bw_on[0] = 1
+            for j in range(12):
+                p.bw_sos[0][j] = sos[j // 6][j % 6]
+        return self._effect(audio, fill)
+
+    def apply_reverb(self, audio, decay=0.5, impulse: Optional[torch.Tensor] = None):
+        """:458-479 -- 0.7 * audio + 0.3 * conv1d(audio, impulse, padding=L//2)[:, :T] per channel, with
+        L = int(sr * decay) taps drawn on the audio's device like the reference (one impulse per call, shared by the
+        channels; for a (B,C,T) batch one impulse per clip, clip 0 first).  `impulse` (additive): use these taps
+        ((L,) or (B,L)) instead of drawing."""
+        x, batched, src, device = self._one(audio)
+        B, C, T = x.shape
+        if impulse is None:
+            imp_dev = audio.device
+            rows = [self._draw_impulse(decay, imp_dev) for _ in range(B)]
+            impulse = rows[0] if B == 1 else torch.stack(rows)
+        plan = self._plan(device)
+        if C <= 2:
+            y = plan.reverb(x, impulse)
+        else:                                        # the kernel packs two channels per transform
+            y = torch.cat([plan.reverb(x[:, c:c + 2], impulse) for c in range(0, C, 2)], dim=1)
+        return self._finish(y, batched, src)

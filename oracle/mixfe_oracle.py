@@ -391,6 +391,39 @@ def compress_static(x: torch.Tensor, threshold: float = -20, ratio: float = 4) -
     return torch.sign(x) * (10 ** (out_db / 20))
 
 
+def reverb_standalone(x: torch.Tensor, h: torch.Tensor, fft: bool = True) -> torch.Tensor:
+    """:458-479 with the impulse made explicit: 0.7 x + 0.3 conv1d(x, h, padding=L//2)[:, :T] per channel."""
+    xc = xcorr_same_fft if fft else xcorr_same_direct
+    hn = h.numpy()
+    rev = torch.stack([torch.from_numpy(np.asarray(xc(x[c].numpy(), hn))).float() for c in range(x.shape[0])])
+    return x * (1 - 0.3) + rev * 0.3
+
+
+def draw_impulse(decay: float = 0.5, sample_rate: int = 44100, device="cpu") -> torch.Tensor:
+    """:460-463 -- consumes torch's global generator of `device` like apply_reverb does."""
+    L = int(sample_rate * decay)
+    t = torch.linspace(0, decay, L, device=device)
+    return torch.exp(-t / (decay / 4)) * torch.randn(L, device=device) * 0.1
+
+
+def spectral_tilt(x: torch.Tensor, kind: str, sample_rate: int = 44100) -> torch.Tensor:
+    """:421-433 with the high/low draw made explicit."""
+    sos = butter_sos(2, 2000, "high", sample_rate) if kind == "high" else butter_sos(2, 500, "low", sample_rate)
+    return _filter(x, sos)
+
+
+def bandwidth_limit(x: torch.Tensor, cutoff_hz: float, sample_rate: int = 44100) -> torch.Tensor:
+    """:449-456 with the cutoff draw made explicit."""
+    return _filter(x, butter_sos(4, cutoff_hz, "low", sample_rate))
+
+
+def song_a_clip(pcm: np.ndarray, T: int = 441000) -> Dict[str, torch.Tensor]:
+    """BASELINE config 1 / SURVEY section 8d: the 4-stem clip cut from assets/song_A.wav (int16 (frames, 2)):
+    vocals, bass, drums, other = the asset from 0, 1.5, 3.0 and 4.5 s."""
+    x = torch.from_numpy(pcm.astype(np.float32) / 32768.0).t().contiguous()
+    return {n: x[:, o:o + T].contiguous() for n, o in zip(STEMS, (0, 66150, 132300, 198450))}
+
+
 def _filter(x: torch.Tensor, sos: np.ndarray) -> torch.Tensor:
     return torch.from_numpy(sosfilt_df2t(sos, x.numpy())).float()     # fp64 inside, .float() after
 

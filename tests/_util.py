@@ -34,3 +34,17 @@ def assert_melpower_close(got: torch.Tensor, ref: torch.Tensor, what=""):
     n_bad = int((d > tol).sum())
     assert n_bad == 0, f"{what}: {n_bad} mel-power entries out of tolerance, worst ratio {float((d / tol).max()):.3g}"
     return float((d / tol).max())
+
+
+def assert_logmel_close(got: torch.Tensor, ref64: torch.Tensor, what="", loose=5e-3, tight=2e-4, window=9.0):
+    """Log-mel against the fp64 oracle: |d| <= `loose` everywhere, and |d| <= `tight` on every bin within `window`
+    nepers of its frame's maximum (quiet bins next to loud ones are where the fp32 reference itself is only good to
+    ~1e-3).  Returns (max abs, max abs on the loud bins)."""
+    got, ref = got.detach().cpu().double(), ref64.detach().cpu().double()
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    d = (got - ref).abs()
+    loud = ref >= ref.amax(dim=-2, keepdim=True) - window
+    worst, worst_loud = float(d.max()), float(d[loud].max())
+    assert worst <= loose, f"{what}: log-mel max abs error {worst:.3g} > {loose}"
+    assert worst_loud <= tight, f"{what}: log-mel error {worst_loud:.3g} > {tight} on bins within {window} Np of the frame maximum"
+    return worst, worst_loud

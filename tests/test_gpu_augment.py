@@ -1,6 +1,8 @@
 """GPU parity of the augmentation kernels (K3 scan + K4/K5 FFT reverb) against the CPU oracle and the
 golden waveforms recorded from the real reference.  Waveform tolerance:
-|d| <= 1e-4 * max|ref|; the asserted bound is tighter and the achieved error is printed."""
+|d| <= 1e-4 * max|ref|; the asserted bound (2e-5) is five times tighter and the achieved error is printed.
+(K3 runs the 16 samples of a lane in fp32 and only the scanned states in fp64: the 500 Hz low-pass, poles at
+r = 0.951, reaches 6e-6; everything else stays under 1e-6.)"""
 import numpy as np
 import pytest
 import torch
@@ -11,6 +13,7 @@ from tests._util import golden
 
 pytestmark = pytest.mark.gpu
 G = golden()
+TOL = 2e-5
 
 
 def _decisions_from_oracle(par: O.ClipAug) -> pkg.ClipAugmentation:
@@ -63,7 +66,7 @@ def test_single_effects(cuda_device, effect, T):
     ref = O.apply_clip_aug(clip, par)
     err = _rel_err(got, ref)
     print(f"{effect} T={T}: rel max err {err:.3g}")
-    assert err < 2e-6, err
+    assert err < TOL, err
     for n in O.STEMS:
         assert got[n].shape == clip[n].shape and got[n].dtype == torch.float32
     if effect == "none":
@@ -103,7 +106,7 @@ def test_reverb_only_and_energy_shares(cuda_device):
     ref = O.apply_clip_aug(clip, par, fft_reverb=True)
     err = _rel_err(got, ref)
     print(f"reverb only: rel max err {err:.3g}")
-    assert err < 5e-6, err
+    assert err < TOL, err
 
 
 def test_full_length_clip_chunked_scan_is_exact_enough(cuda_device):
@@ -116,7 +119,7 @@ def test_full_length_clip_chunked_scan_is_exact_enough(cuda_device):
     ref = O.apply_clip_aug(clip, par, fft_reverb=True)
     err = _rel_err(got, ref)
     print(f"10 s clip, all effects: rel max err {err:.3g}")
-    assert err < 5e-6, err
+    assert err < TOL, err
 
 
 def test_long_clip_two_reverb_segments(cuda_device):
@@ -130,7 +133,7 @@ def test_long_clip_two_reverb_segments(cuda_device):
     ref = O.apply_clip_aug(clip, par, fft_reverb=True)
     err = _rel_err(got, ref)
     print(f"two segments: rel max err {err:.3g}")
-    assert err < 5e-6, err
+    assert err < TOL, err
 
 
 def test_batched_clips_with_individual_decisions(cuda_device):
@@ -151,7 +154,7 @@ def test_batched_clips_with_individual_decisions(cuda_device):
     for i, (c, p) in enumerate(zip(clips, pars)):
         ref = O.apply_clip_aug(c, p, fft_reverb=True)
         err = _rel_err({n: got[n][i] for n in O.STEMS}, ref)
-        assert err < 5e-6, (i, err)
+        assert err < TOL, (i, err)
 
 
 def test_apply_writes_into_a_slice_of_the_batch(cuda_device):
@@ -236,7 +239,7 @@ def test_random_decisions_lengths_and_unaligned_views(cuda_device, seed, T):
     got = aug.apply(views, [_decisions_from_oracle(par)])
     ref = O.apply_clip_aug(clip, par, fft_reverb=True)
     err = _rel_err(got, ref)
-    assert err < 5e-6, f"T={T} off={off}: rel max err {err:.3g}"
+    assert err < TOL, f"T={T} off={off}: rel max err {err:.3g}"
     for n in O.STEMS:                                              # inputs untouched, padding untouched
         assert torch.equal(wide[n][:, off:off + T].cpu(), clip[n])
         assert float(wide[n][:, :off].abs().max()) == 0.0 and float(wide[n][:, off + T:].abs().max()) == 0.0

@@ -11,7 +11,7 @@ import torch
 
 import mixing_style_transfer_b200 as pkg
 from oracle import mixfe_oracle as O
-from tests._util import assert_features_close, assert_melpower_close
+from tests._util import assert_features_close, assert_logmel_close, assert_melpower_close
 
 pytestmark = pytest.mark.gpu
 
@@ -43,9 +43,8 @@ def test_features_melpower_logmel_vs_oracle(cuda_device, n_fft, hop, n_mels, T):
     assert_melpower_close(mp, ref, f"{n_fft}/{hop}/{n_mels} T={T}")
     pre = pkg.MelSpectrogramPreprocessor(44100, n_fft, hop, n_mels)
     lm = pre({n: v[None] for n, v in dclip.items()})
-    ref_lm = O.log_mel({n: v[None] for n, v in clip.items()}, cfg)
-    assert lm.shape == ref_lm.shape
-    assert float((lm.cpu() - ref_lm).abs().max()) < 5e-3
+    assert_logmel_close(lm, O.log_mel({n: v[None] for n, v in clip.items()}, cfg, dtype=torch.float64),
+                        f"{n_fft}/{hop}/{n_mels} T={T}")
 
 
 def _fuzz_cases():

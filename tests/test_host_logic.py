@@ -25,8 +25,14 @@ def test_library_builds_and_exports_every_declared_symbol():
     assert declared == set(_native.EXPORTS), declared ^ set(_native.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.mixfe_abi_version() == 1
-    assert ctypes.sizeof(_native.AugParams) == 4 * 4 + 4 * 4 + 4 * 6 * 8 + 4 * 4 + 4 * 4 + 4 * 12 * 8 + 8
+    assert L.mixfe_abi_version() == _native.ABI_VERSION == 2
+    # mixfe_aug_params: gain, tilt gate, tilt sos, comp gate, comp threshold, comp ratio, bw gate, bw sos, reverb gate + pad
+    assert ctypes.sizeof(_native.AugParams) == 4 * 4 + 4 * 4 + 4 * 6 * 8 + 4 * 4 + 4 * 4 + 4 * 4 + 4 * 4 + 4 * 12 * 8 + 8
+    from mixing_style_transfer_b200.mixing_utils import _aug_dtype
+    dt = _aug_dtype()                         # the numpy view draw_batch fills must match the C struct field by field
+    assert dt.itemsize == ctypes.sizeof(_native.AugParams)
+    for name, _ in _native.AugParams._fields_:
+        assert dt.fields[name][1] == getattr(_native.AugParams, name).offset, name
 
 
 def test_sass_is_sm100a_only():
