@@ -1,14 +1,16 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the DSP front end (BASELINE.json: audio-sec/sec, features + mel + aug).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload features_mel|features_mel_aug]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload features_mel_aug|features_mel|sweep30s]
   python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
 
-A "step" is one pass of the hot path over one batch of synthetic input: 72 clips (24 triplets) of
-10 s / 44.1 kHz / 8 channels per GPU (BASELINE.json configs[1]; configs[2] with --workload
-features_mel_aug adds the augmentation chain that makes the 24 negatives).  Under torchrun every
-rank processes its own 72 clips (weak scaling, no data-path collective); the all-gather into the
-global contrastive batch is timed separately and reported under "allgather".
+A "step" is one pass of the hot path over one batch of synthetic input.  Default workload = BASELINE.json
+configs[2], the configuration the metric is quoted on: 24 triplets of 10 s / 44.1 kHz / 8 channels per GPU; the 24
+negatives are made by the augmentation chain (gain, tilt EQ, compressor, band-limit, stereo reverb + redistribution)
+from the 24 anchors with decisions drawn INSIDE the step, then features + log-mel of all 72 clips.
+`--workload features_mel` is configs[1] (no augmentation), `--workload sweep30s` is configs[3] (30 s clips, strong
+scaling, sharded by clip).  Under torchrun every rank processes its own batch (weak scaling, no data-path
+collective); the all-gather into the global contrastive batch (configs[4]) is timed separately under "allgather".
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -25,11 +27,16 @@ if ROOT not in sys.path:
 
 SR, CLIP_S, T = 44100, 10.0, 441000
 N_CLIPS = 72                           # 24 triplets: anchor / positive / negative
+N_TRI = N_CLIPS // 3
 N_MELS, HOP, NFFT = 128, 256, 1024
 F = 1 + T // HOP
 ALG_BYTES_PER_CLIP = 8 * T * 4 + 8 * N_MELS * F * 4 + 64 * 4          # 21 169 664 B
-METRIC = "audio-sec/sec features+mel+aug"
 UNIT = "audio-s/s"
+METRICS = {"features_mel_aug": "audio-sec/sec features+mel+aug",
+           "features_mel": "audio-sec/sec features+mel",
+           "sweep30s": "audio-sec/sec features+mel (offline sweep)"}
+SEED_DECISIONS = 1234
+PARITY_REPORT = os.path.join(ROOT, "profiles", "parity_report.json")
 
 
 def parse():
@@ -38,23 +45,35 @@ def parse():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("MIXFE_BENCH_WORKLOAD", "features_mel"),
-                    choices=["features_mel", "features_mel_aug"])
+    ap.add_argument("--workload", default=os.environ.get("MIXFE_BENCH_WORKLOAD", "features_mel_aug"),
+                    choices=["features_mel_aug", "features_mel", "sweep30s"])
     ap.add_argument("--e2e-steps", type=int, default=4)
-    ap.add_argument("--ref-clips", type=int, default=0, help="clips per reference step (0 = one per worker, max 24)")
+    ap.add_argument("--sweep-clips", type=int, default=4096, help="sweep30s: clips in the whole job")
+    ap.add_argument("--sweep-batch", type=int, default=24, help="sweep30s: resident clips per batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-comparator", action="store_true")
+    ap.add_argument("--no-allgather", action="store_true")
     return ap.parse_args()
 
 
-def config_dict(workload, n_gpus, extra=None):
-    c = {"workload": ("24-triplet batch (72 clips x 10 s, 44.1 kHz, 8 ch) features + 8ch 128-mel log-mel"
-                      + (" + augmentation chain for the 24 negatives" if workload == "features_mel_aug" else "")),
+def config_dict(workload, n_gpus, args=None):
+    if workload == "sweep30s":
+        n = args.sweep_clips if args else 4096
+        return {"workload": f"offline sweep: {n} synthetic clips x 30 s x 8 ch (T = 1 323 000, F = 5168) features + 8ch 128-mel "
+                            f"log-mel, sharded contiguously by clip over the ranks, resident batches of "
+                            f"{args.sweep_batch if args else 24} clips regenerated on device from seed = clip index",
+                "clips": n, "clip_seconds": 30.0, "sample_rate": SR, "n_fft": NFFT, "hop": HOP, "n_mels": N_MELS,
+                "parallelism": f"clip-sharded dp{n_gpus}",
+                "l2": "one batch (1.02 GB in) exceeds the 126 MB L2; no explicit flush"}
+    c = {"workload": ("24-triplet batch (72 clips x 10 s, 44.1 kHz, 8 ch): "
+                      + ("augmentation chain (gain, tilt EQ, compressor, band-limit, stereo reverb, prob 0.5, decisions drawn "
+                         "per step) makes the 24 negatives from the 24 anchors, then " if workload == "features_mel_aug" else "")
+                      + "mixing features + 8ch 128-mel log-mel of all 72 clips"),
          "clips_per_gpu": N_CLIPS, "clip_seconds": CLIP_S, "sample_rate": SR, "n_fft": NFFT, "hop": HOP,
          "n_mels": N_MELS, "parallelism": f"clip-sharded dp{n_gpus}",
          "l2": "inputs (1.02 GB per step) exceed the 126 MB L2; no explicit flush"}
-    if extra:
-        c.update(extra)
     return c
 
 
@@ -65,12 +84,12 @@ def config_dict(workload, n_gpus, extra=None):
 _WORKER_CLIPS = None
 
 
-def _ref_worker_init(seed_base, n_local, workload):
+def _ref_worker_init(seed_base, n_local, T_clip):
     global _WORKER_CLIPS
     import torch
     torch.set_num_threads(1)
     from oracle import mixfe_oracle as O
-    _WORKER_CLIPS = [O.synthetic_clip(seed_base + i, T) for i in range(n_local)]
+    _WORKER_CLIPS = [O.synthetic_clip(seed_base + i, T_clip) for i in range(n_local)]
     O.MelFrontEnd(O.FrontEndConfig())          # warm the filterbank code path
 
 
@@ -80,8 +99,9 @@ def _ref_worker_run(job):
     from oracle import mixfe_oracle as O
     clip = _WORKER_CLIPS[idx % len(_WORKER_CLIPS)]
     t0 = time.perf_counter()
-    if workload == "features_mel_aug" and idx % 3 == 2:          # every third clip is a negative
-        torch.manual_seed(1234 + idx)
+    if workload == "features_mel_aug" and idx >= 2 * N_TRI:       # clips 48..71 are the negatives
+        torch.manual_seed(SEED_DECISIONS + idx)
+        # the reference's 22 050-tap conv1d (src/mixing_utils.py:468) takes 22.8 s per call; the port uses its FFT form
         clip = O.apply_clip_aug(clip, O.draw_clip_aug(prob=0.5), fft_reverb=True)
     f = O.mixing_features(clip)
     lm = O.log_mel({n: v[None] for n, v in clip.items()})
@@ -99,6 +119,10 @@ def emit(line: dict) -> None:
         os.write(_REAL_STDOUT, data)
 
 
+def host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -106,12 +130,15 @@ def run_reference(args):
     import multiprocessing as mp
     import torch
     torch.set_num_threads(1)
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = host_cores()
     workers = max(1, min(cores, 64))
-    clips = args.ref_clips or min(N_CLIPS, 2 * workers)
+    sweep = args.workload == "sweep30s"
+    T_clip, clip_s = (3 * T, 30.0) if sweep else (T, CLIP_S)
+    # one step = the same 72-clip batch the native arm processes (sweep30s: one resident batch of the sweep)
+    clips = args.sweep_batch if sweep else N_CLIPS
     workers = min(workers, clips)
     ctx = mp.get_context("fork")
-    pool = ctx.Pool(workers, initializer=_ref_worker_init, initargs=(100, 2, args.workload))
+    pool = ctx.Pool(workers, initializer=_ref_worker_init, initargs=(100, 2, T_clip))
     jobs = [(i, args.workload) for i in range(clips)]
     try:
         for _ in range(max(1, args.warmup)):
@@ -123,18 +150,138 @@ def run_reference(args):
     finally:
         pool.terminate()
     ms = dt / args.steps * 1e3
-    value = clips * CLIP_S / (ms / 1e3)
-    sample = (f"{clips} clips x 10 s per step ({clips * CLIP_S:.0f} audio-s), {workers} worker processes x 1 torch thread "
-              f"(the reference's DataLoader-worker deployment, scripts/train_baseline.sh:13-19)")
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": max(1, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+    value = clips * clip_s / (ms / 1e3)
+    sample = (f"{clips} clips x {clip_s:.0f} s per step ({clips * clip_s:.0f} audio-s), {workers} worker processes x 1 torch "
+              f"thread (the reference's DataLoader-worker deployment, scripts/train_baseline.sh:13-19)"
+              + ("; reverb in its FFT form (the reference's direct 22 050-tap conv1d takes 22.8 s per clip)"
+                 if args.workload == "features_mel_aug" else ""))
+    line = {"metric": METRICS[args.workload], "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": max(1, args.warmup), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong" if sweep else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": config_dict(args.workload, args.gpus, {"reference_sample_clips_per_step": clips}),
+            "config": config_dict(args.workload, args.gpus, args),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port", "sample": sample,
                              "host_cores_visible": cores},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
+
+
+# =================================================================================================
+# parity of the timed batch (checker side: oracle on the host cores, outside every timed region)
+# =================================================================================================
+_PAR = {}
+
+
+def _parity_worker(i):
+    """Clip i of the timed batch against the fp32 and the fp64 oracle: 64 feature errors, mel power, log-mel."""
+    import numpy as np
+    import torch
+    torch.set_num_threads(1)
+    from oracle import mixfe_oracle as O
+    clip = {n: _PAR["stems"][s][i] for s, n in enumerate(O.STEMS)}
+    out = {"i": i}
+    f32 = O.mixing_features(clip)
+    f64 = O.mixing_features(clip, dtype=torch.float64)
+    got = _PAR["feat"][i]
+    out["f_err32"] = (got.double() - f32.double()).abs().numpy()
+    out["f_err64"] = (got.double() - f64).abs().numpy()
+    out["f_ref"] = f32.numpy()
+    out["f_ref_err"] = (f32.double() - f64).abs().numpy()           # how far the fp32 reference itself is from fp64
+    fe32, fe64 = O.MelFrontEnd(O.FrontEndConfig()), O.MelFrontEnd(O.FrontEndConfig(), torch.float64)
+    mp32 = torch.cat([fe32.mel_power(clip[n]) for n in O.STEMS])                    # (8, n_mels, F)
+    mp64 = torch.cat([fe64.mel_power(clip[n].double()) for n in O.STEMS])
+    lm = _PAR["lm"][i].double()
+    mp_got = torch.exp(lm) - 1e-10                                                   # the kernel's mel power, from its log-mel
+    tol = 1e-4 * mp32.double().abs() + 1e-6 * mp32.double().amax(dim=-2, keepdim=True) + 1e-30
+    # exp(log) adds ~1e-6 relative of its own, far inside the tolerance; frames of digital silence (max <= 1e-9) have
+    # no scale to compare against and are skipped
+    live = (mp32.double().amax(dim=-2, keepdim=True) > 1e-9).expand_as(tol)
+    out["mel_worst_ratio"] = float((((mp_got - mp32.double()).abs() / tol)[live]).max()) if bool(live.any()) else 0.0
+    ref_lm64 = torch.log(mp64 + 1e-10)
+    d = (lm - ref_lm64).abs()
+    loud = ref_lm64 >= ref_lm64.amax(dim=-2, keepdim=True) - 9.0
+    out["lm_max_abs"] = float(d.max())
+    out["lm_max_abs_loud"] = float(d[loud].max())
+    out["lm_max_abs_vs_fp32"] = float((lm - torch.log(mp32.double() + 1e-10)).abs().max())
+    return out
+
+
+def _parity_aug_worker(j):
+    """Negative j: the oracle's augment_stems with the step's decisions against the waveforms the kernels wrote."""
+    import torch
+    torch.set_num_threads(1)
+    from oracle import mixfe_oracle as O
+    anchor = {n: _PAR["stems"][s][j] for s, n in enumerate(O.STEMS)}
+    ref = O.apply_clip_aug(anchor, _PAR["decisions"][j], fft_reverb=True)
+    scale = max(float(ref[n].abs().max()) for n in O.STEMS) + 1e-30
+    err = max(float((_PAR["stems"][s][2 * N_TRI + j] - ref[n]).abs().max()) for s, n in enumerate(O.STEMS))
+    return {"j": j, "rel_err": err / scale, "reverb": _PAR["decisions"][j].impulse is not None}
+
+
+def oracle_decisions(batch):
+    """BatchAugmentation (draw_batch) -> the oracle's ClipAug objects."""
+    import torch
+    from oracle import mixfe_oracle as O
+    a = batch.arrays
+    imp = batch.impulse.cpu() if batch.impulse is not None else None
+    out = []
+    for b in range(batch.n):
+        c = O.ClipAug()
+        for s, n in enumerate(O.STEMS):
+            c.stems[n] = O.StemAug(
+                gain_db=torch.tensor([a["gain_db"][b, s]]) if a["gain_on"][b, s] else None,
+                tilt=("high" if a["tilt_high"][b, s] else "low") if a["tilt_on"][b, s] else None,
+                compress=bool(a["comp_on"][b, s]),
+                cutoff_hz=float(a["cutoff_hz"][b, s]) if a["bw_on"][b, s] else None)
+        c.impulse = imp[b] if a["reverb_on"][b] else None
+        out.append(c)
+    return out
+
+
+def parity_check(stems_cpu, feat_cpu, lm_cpu, decisions, names, with_aug):
+    """Runs the oracle over the 72 clips the timed region just processed (fork pool: the children never touch CUDA)."""
+    import multiprocessing as mp
+    import numpy as np
+    _PAR.update(stems=stems_cpu, feat=feat_cpu, lm=lm_cpu, decisions=decisions)
+    cores = max(1, min(host_cores(), 64))
+    t0 = time.perf_counter()
+    ctx = mp.get_context("fork")
+    with ctx.Pool(min(cores, N_CLIPS)) as pool:                   # bounded waits: a wedged child must not hang the bench
+        res = pool.map_async(_parity_worker, range(N_CLIPS), chunksize=1).get(timeout=900)
+        aug = pool.map_async(_parity_aug_worker, range(N_TRI), chunksize=1).get(timeout=600) if with_aug else []
+    e32 = np.stack([r["f_err32"] for r in res]); e64 = np.stack([r["f_err64"] for r in res])
+    ref = np.stack([r["f_ref"] for r in res]); eref = np.stack([r["f_ref_err"] for r in res])
+    tol = 1e-4 * np.abs(ref) + 1e-5
+    feat_ok = bool((e32 <= tol).all())
+    per_feature = [{"index": k, "name": names[k], "max_abs_err_vs_fp32_oracle": float(e32[:, k].max()),
+                    "max_abs_err_vs_fp64_oracle": float(e64[:, k].max()),
+                    "fp32_oracle_own_err_vs_fp64": float(eref[:, k].max()),
+                    "max_abs_ref": float(np.abs(ref[:, k]).max()),
+                    "worst_err_over_tolerance": float((e32[:, k] / tol[:, k]).max())} for k in range(ref.shape[1])]
+    mel_ratio = max(r["mel_worst_ratio"] for r in res)
+    lm_abs = max(r["lm_max_abs"] for r in res)
+    lm_loud = max(r["lm_max_abs_loud"] for r in res)
+    wave = max((a["rel_err"] for a in aug), default=None)
+    ok = feat_ok and mel_ratio <= 1.0 and lm_loud <= 2e-4 and (wave is None or wave <= 1e-4)
+    report = {"what": "the 72 clips of the last timed step of bench.py against the oracle on the host cores "
+                      "(features, mel power, log-mel; augmented waveforms of the 24 negatives against the oracle's "
+                      "augment_stems with the same decisions)",
+              "tolerances": {"features": "|d| <= 1e-4 |ref| + 1e-5 (fp32 oracle)",
+                             "mel_power": "|d| <= 1e-4 |ref| + 1e-6 frame max (fp32 oracle; from exp(log-mel))",
+                             "logmel": "|d| <= 2e-4 on bins within 9 Np of the frame maximum (fp64 oracle)",
+                             "waveform": "|d| <= 1e-4 max|ref| (oracle: fp64 sosfilt, fp64 FFT reverb)"},
+              "ok": ok, "features_ok": feat_ok, "clips": N_CLIPS,
+              "features_max_abs_err": float(e32.max()), "features_worst_err_over_tolerance": float((e32 / tol).max()),
+              "mel_power_worst_err_over_tolerance": mel_ratio, "logmel_max_abs_err_vs_fp64": lm_abs,
+              "logmel_max_abs_err_loud_bins_vs_fp64": lm_loud,
+              "logmel_max_abs_err_vs_fp32": max(r["lm_max_abs_vs_fp32"] for r in res),
+              "augmented_waveform_max_rel_err": wave,
+              "augmented_clips_with_reverb": sum(1 for a in aug if a["reverb"]),
+              "oracle_seconds": time.perf_counter() - t0, "oracle_workers": min(cores, N_CLIPS),
+              "per_feature": per_feature}
+    _PAR.clear()
+    return report
 
 
 # =================================================================================================
@@ -212,10 +359,10 @@ def measured_peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_baseline_subprocess(workload):
+def cpu_baseline_subprocess(args):
     """The oracle timed on this box's host cores, before CUDA is initialised in this process."""
     cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "2", "--warmup", "1",
-           "--workload", workload]
+           "--workload", args.workload, "--sweep-batch", str(args.sweep_batch)]
     env = dict(os.environ)
     for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE"):
         env.pop(k, None)
@@ -229,19 +376,133 @@ def cpu_baseline_subprocess(workload):
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e}"}
 
 
+def timed_loop(torch, fn, n, warm=0):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def torch_cuda_comparator(torch, dev, stems):
+    """The reference's own math on CUDA tensors on this GPU (checker side, like cpu_baseline): torch.stft -> cuFFT,
+    dense (F x 513) @ (513 x 128) -> cuBLAS, ATen elementwise; src/model.py:54-65, src/mixing_utils.py:71-105 run
+    device-agnostically, restated in oracle/.  Never on the product path."""
+    from oracle import mixfe_oracle as O
+    fe = O.MelFrontEnd(O.FrontEndConfig(), torch.float32, device=dev)
+    d = dict(zip(O.STEMS, stems))
+    lm_ms = timed_loop(torch, lambda: O.log_mel(d, fe=fe), 5, warm=2)
+    n_feat = 12                                     # per-clip Python loop with host syncs, as the reference: a sample of 12 clips
+
+    def feats():
+        for i in range(n_feat):
+            O.mixing_features({n: v[i] for n, v in d.items()}, fe=fe)
+    f_ms = timed_loop(torch, feats, 2, warm=1) * (N_CLIPS / n_feat)
+    return {"logmel_ms": lm_ms, "features_ms": f_ms,
+            "what": "reference math on CUDA tensors of the same 72-clip batch: log-mel batched per stem (torch.stft/cuFFT + dense "
+                    "cuBLAS matmul + log); features per clip as the reference loops (12 clips timed, scaled to 72)"}
+
+
+def run_sweep(args, torch, dist, pkg, dev, rank, world, cpu_base):
+    """BASELINE config 4: N clips x 30 s sharded contiguously by clip index, resident batches regenerated on device."""
+    from mixing_style_transfer_b200.distributed import shard_bounds
+    Ts = 3 * T
+    fe = pkg.MixingFeatureExtractor()
+    plan = fe._plan(dev)
+    Fs = 1 + Ts // HOP
+    lo, hi = shard_bounds(args.sweep_clips, rank, world)
+    nb = args.sweep_batch
+    stems = [torch.empty(nb, 2, Ts, device=dev) for _ in pkg.STEMS]
+    feats = torch.zeros(max(1, hi - lo), plan.feature_dim, device=dev)
+    lm = torch.empty(nb, 8, N_MELS, Fs, device=dev)
+    g = torch.Generator(device=dev)
+
+    def fill(first, n):
+        for j in range(n):
+            g.manual_seed(first + j)
+            for s in stems:
+                gain = 10 ** (-12.0 * torch.rand(1, device=dev, generator=g) / 20)
+                torch.rand(2, Ts, device=dev, generator=g, out=s[j])
+                s[j].mul_(0.5).sub_(0.25).mul_(gain)
+
+    n = min(nb, hi - lo)
+    fill(lo, n)
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    if rank == 0:
+        sampler.start()
+    for _ in range(max(3, args.warmup)):
+        plan.features_logmel([s[:n] for s in stems], True, True, features_out=feats[:n], logmel_out=lm[:n])
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    plan.enable_timing(True)
+    sampler.mark_begin()
+    n0 = pkg.launch_count()
+    events, t_wall = [], time.perf_counter()
+    for first in range(lo, hi, nb):
+        n = min(nb, hi - first)
+        if first != lo:
+            fill(first, n)                       # regeneration of the next batch: outside the timed kernels
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        plan.features_logmel([s[:n] for s in stems], True, True, features_out=feats[first - lo:first - lo + n], logmel_out=lm[:n])
+        e1.record()
+        events.append((e0, e1))
+    torch.cuda.synchronize()
+    sampler.mark_end()
+    wall = time.perf_counter() - t_wall
+    launches = pkg.launch_count() - n0
+    k1_ms, k1_n = plan.kernel_time("features")
+    ms = sum(a.elapsed_time(b) for a, b in events)
+    t = torch.tensor([ms, wall * 1e3], device=dev, dtype=torch.float64)
+    chk = feats[:hi - lo].double().sum(0)
+    finite = torch.isfinite(feats).all().to(torch.float64).reshape(1)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(chk)
+        dist.all_reduce(finite, op=dist.ReduceOp.MIN)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank == 0:
+        ms, wall_ms = float(t[0]), float(t[1])
+        audio_s = args.sweep_clips * 30.0
+        alg_clip = 8 * Ts * 4 + 8 * N_MELS * Fs * 4 + plan.feature_dim * 4
+        peak, peak_src = measured_peak_hbm()
+        k1 = k1_ms / max(1, k1_n)
+        n_first = min(nb, hi - lo)
+        line = {"metric": METRICS["sweep30s"], "value": audio_s / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": len(events), "warmup": max(3, args.warmup), "ms_per_step": ms / max(1, len(events)),
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config_dict("sweep30s", world, args),
+                "job_ms_max_over_ranks": ms, "wall_ms_with_regeneration": wall_ms,
+                "roofline": {"bound": "hbm", "achieved": n_first * alg_clip / (k1 / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": n_first * alg_clip / (k1 / 1e3) / 1e9 / peak, "traffic": None, "kernel": "k1_features",
+                             "kernel_ms": k1, "peak_source": peak_src, "algorithmic_bytes_per_launch": n_first * alg_clip},
+                "gpu_launches": launches, "clocks": clocks, "all_finite": bool(finite.item() == 1.0),
+                "checksum_sum": float(chk.sum()), "checksum_head": [float(v) for v in chk[:6]]}
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        emit(line)
+
+
 def run_native(args):
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_base = cpu_baseline_subprocess(args.workload)
+        cpu_base = cpu_baseline_subprocess(args)
 
     import torch
     import torch.distributed as dist
     import mixing_style_transfer_b200 as pkg
     from mixing_style_transfer_b200.distributed import GlobalBatch
-    from mixing_style_transfer_b200.pipeline import HostPipeline
+    from mixing_style_transfer_b200.pipeline import HostPipeline, TripletPipeline
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (native arm) needs a CUDA device; there is no CPU fallback")
@@ -255,7 +516,14 @@ def run_native(args):
         if world > 1:
             dist.barrier()
 
-    # ---- synthetic batch, HBM-resident --------------------------
+    if args.workload == "sweep30s":
+        run_sweep(args, torch, dist, pkg, dev, rank, world, cpu_base)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- synthetic batch, HBM-resident -----------------------
+    # clips 0..23 anchors, 24..47 positives, 48..71 negatives (= augment_stems(anchors), rewritten every step)
     g = torch.Generator(device=dev).manual_seed(20261104 + rank)
     stems = []
     for _ in pkg.STEMS:
@@ -264,22 +532,22 @@ def run_native(args):
     fe = pkg.MixingFeatureExtractor()
     plan = fe._plan(dev)
     aug = pkg.AudioAugmenter(prob=0.5)
+    aug_plan = aug._plan(dev)
     with_aug = args.workload == "features_mel_aug"
-    decisions = None
-    if with_aug:
-        torch.manual_seed(1234)
-        decisions = [aug.draw(impulse_device=dev) for _ in range(N_CLIPS // 3)]
-        aug_plan = aug._plan(dev)
     gb = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True)
     f_out, lm_out = gb.local_views()
+    anchors = {n: s[0:N_TRI] for n, s in zip(pkg.STEMS, stems)}
+    negatives = {n: s[2 * N_TRI:] for n, s in zip(pkg.STEMS, stems)}
+    last = {}
 
     def step():
         if with_aug:
-            # negatives (clips 48..71) = augment_stems(anchors 0..23), written in place into the batch
-            anchors = {n: s[0:N_CLIPS // 3] for n, s in zip(pkg.STEMS, stems)}
-            aug.apply(anchors, decisions, out={n: s[2 * N_CLIPS // 3:] for n, s in zip(pkg.STEMS, stems)})
+            # decisions of this step: one vectorised draw on the host (global CPU generator), impulses on the device
+            last["dec"] = aug.draw_batch(N_TRI, impulse_device=dev)
+            aug.apply(anchors, last["dec"], out=negatives)
         plan.features_logmel(stems, True, True, features_out=f_out, logmel_out=lm_out)
 
+    torch.manual_seed(SEED_DECISIONS + rank)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -287,8 +555,7 @@ def run_native(args):
         step()
     torch.cuda.synchronize()
     plan.enable_timing(True)
-    if with_aug:
-        aug_plan.enable_timing(True)
+    aug_plan.enable_timing(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     torch.cuda.synchronize()
@@ -308,20 +575,37 @@ def run_native(args):
     k2_ms, k2_n = plan.kernel_time("finalize")
     plan.enable_timing(False)
     kernels = {"k1_features_ms": k1_ms / max(1, k1_n), "k2_finalize_ms": k2_ms / max(1, k2_n)}
+    a_ms, a_n = aug_plan.kernel_time("augment")
+    r_ms, _ = aug_plan.kernel_time("reverb")
+    aug_plan.enable_timing(False)
     if with_aug:
-        a_ms, a_n = aug_plan.kernel_time("augment")
-        r_ms, r_n = aug_plan.kernel_time("reverb")
-        aug_plan.enable_timing(False)
-        kernels.update({"k3_augment_ms": a_ms / max(1, a_n), "k4_reverb_ms_per_step": r_ms / max(1, args.steps)})
+        kernels.update({"k3_augment_ms": a_ms / max(1, a_n), "k4_reverb_ms_per_step": r_ms / max(1, args.steps),
+                        "launches_per_step": launches / max(1, args.steps)})
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = world * N_CLIPS * CLIP_S / (ms / 1e3)
 
+    # ---- what the timed region produced, kept for the parity check (before anything else touches the batch) ----
+    parity_in = None
+    if rank == 0 and not args.no_parity:
+        parity_in = ([s.cpu() for s in stems], f_out.cpu(), lm_out.cpu(),
+                     oracle_decisions(last["dec"]) if with_aug else None)
+
+    # ---- configs[1] figure beside it: the same batch without the augmentation chain --------------------
+    features_mel_ms = None
+    if with_aug:
+        features_mel_ms = timed_loop(torch, lambda: plan.features_logmel(stems, True, True, features_out=f_out, logmel_out=lm_out),
+                                     max(5, min(args.steps, 20)), warm=2)
+        if world > 1:
+            t = torch.tensor([features_mel_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            features_mel_ms = float(t.item())
+
     # ---- all-gather into the global contrastive batch, timed on its own -----
     allgather = None
-    if world > 1:
+    if world > 1 and not args.no_allgather:
         ggb = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True)
         gf, glm = ggb.local_views()
         gf.copy_(f_out); glm.copy_(lm_out)
@@ -351,77 +635,148 @@ def run_native(args):
         both = {}
         ref_gb = extract_global_batch(fe, stems_d, n_chunks=4, comm_stream=comm)
         torch.cuda.synchronize()
-        for label, nch, sym in (("nccl_serial_ms", 1, False), ("nccl_pipelined_4_chunks_ms", 4, False),
-                                ("symmetric_ce_serial_ms", 1, True), ("symmetric_ce_pipelined_4_chunks_ms", 4, True),
-                                ("multicast_ce_serial_ms", 1, "multicast"), ("multicast_ce_pipelined_4_chunks_ms", 4, "multicast")):
-            gbx = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True, n_chunks=nch, symmetric=sym)
-            for _ in range(2):
-                extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
-            torch.cuda.synchronize(); barrier()
-            a0.record()
-            for _ in range(reps):
-                extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
-            a1.record(); torch.cuda.synchronize(); barrier()
-            t = torch.tensor([a0.elapsed_time(a1) / reps], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            both[label] = float(t.item())
-            if nch == 4:
-                both[label.replace("_ms", "_equals_nccl")] = bool(torch.equal(gbx.logmel, ref_gb.logmel)
-                                                                  and torch.equal(gbx.features, ref_gb.features))
-            del gbx
+        variants = [("nccl_serial_ms", 1, False, 0), ("nccl_pipelined_4_chunks_ms", 4, False, 0),
+                    ("nccl_pipelined_4_chunks_reserve8_ms", 4, False, 8), ("nccl_pipelined_4_chunks_reserve16_ms", 4, False, 16),
+                    ("nccl_pipelined_4_chunks_reserve24_ms", 4, False, 24), ("nccl_pipelined_8_chunks_reserve16_ms", 8, False, 16),
+                    ("symmetric_ce_serial_ms", 1, True, 0), ("symmetric_ce_pipelined_4_chunks_ms", 4, True, 0),
+                    ("multicast_ce_serial_ms", 1, "multicast", 0), ("multicast_ce_pipelined_4_chunks_ms", 4, "multicast", 0)]
+        for label, nch, sym, reserve in variants:
+            try:
+                gbx = GlobalBatch(N_CLIPS, plan.feature_dim, N_MELS, F, dev, with_logmel=True, n_chunks=nch, symmetric=sym)
+                plan.reserve_sms(reserve)
+                for _ in range(2):
+                    extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
+                torch.cuda.synchronize(); barrier()
+                a0.record()
+                for _ in range(reps):
+                    extract_global_batch(fe, stems_d, n_chunks=nch, comm_stream=comm, out=gbx)
+                a1.record(); torch.cuda.synchronize(); barrier()
+                t = torch.tensor([a0.elapsed_time(a1) / reps], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                both[label] = float(t.item())
+                if nch == 4 and reserve == 0:
+                    both[label.replace("_ms", "_equals_nccl")] = bool(torch.equal(gbx.logmel, ref_gb.logmel)
+                                                                      and torch.equal(gbx.features, ref_gb.features))
+                del gbx
+            finally:
+                plan.reserve_sms(0)
         del ref_gb
+        best = min((v, k) for k, v in both.items() if k.endswith("_ms"))
+        both["best"] = {"variant": best[1], "ms": best[0]}
         allgather["extract_plus_gather"] = both
 
     # ---- end to end from pinned host memory through the public pipeline ---------------------------
     e2e = None
     if not args.no_e2e:
-        host = {n: HostPipeline.pinned_like((N_CLIPS, 2, T)) for n in pkg.STEMS}
-        for n, s in zip(pkg.STEMS, stems):
-            host[n].copy_(s)
         hf = HostPipeline.pinned_like((N_CLIPS, plan.feature_dim))
         hl = HostPipeline.pinned_like((N_CLIPS, 8, N_MELS, F))
-        pipe = HostPipeline(fe, N_CLIPS, T, chunk=12, device=dev, with_logmel=True)
-        pipe.run(host, hf, hl)
+        if with_aug:
+            host = {n: HostPipeline.pinned_like((2 * N_TRI, 2, T)) for n in pkg.STEMS}
+            for n, s in zip(pkg.STEMS, stems):
+                host[n].copy_(s[:2 * N_TRI])
+            pipe = TripletPipeline(fe, pkg.AudioAugmenter(prob=0.5), N_TRI, T, chunk=4, device=dev, with_logmel=True)
+
+            def e2e_step():
+                pipe.run(host, pipe.aug.draw_batch(N_TRI, impulse_device=dev), hf, hl)
+            api = ("TripletPipeline.run: pinned host anchors + positives -> chunked H2D -> augmentation kernels make the "
+                   "negatives on the device (decisions drawn per step) -> features_and_logmel kernels -> D2H of the 72 "
+                   "feature vectors and log-mels")
+        else:
+            host = {n: HostPipeline.pinned_like((N_CLIPS, 2, T)) for n in pkg.STEMS}
+            for n, s in zip(pkg.STEMS, stems):
+                host[n].copy_(s)
+            pipe = HostPipeline(fe, N_CLIPS, T, chunk=12, device=dev, with_logmel=True)
+
+            def e2e_step():
+                pipe.run(host, hf, hl)
+            api = ("HostPipeline.run: pinned host stems -> chunked H2D -> features_and_logmel kernels -> D2H of features "
+                   "and log-mels")
+        e2e_step()
         torch.cuda.synchronize(); barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
-            pipe.run(host, hf, hl)
+            e2e_step()
         torch.cuda.synchronize()
         e_ms = (time.perf_counter() - t0) / args.e2e_steps * 1e3
         if world > 1:
             t = torch.tensor([e_ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e_ms = float(t.item())
-        ok = bool(torch.allclose(hf, f_out.cpu(), rtol=0, atol=0)) if not with_aug else True
+        # anchors and positives do not depend on the step's decisions: their rows must equal the resident run's
+        same = bool(torch.equal(hf[:2 * N_TRI], f_out[:2 * N_TRI].cpu()) and torch.equal(hl[:2 * N_TRI], lm_out[:2 * N_TRI].cpu()))
         e2e = {"value": world * N_CLIPS * CLIP_S / (e_ms / 1e3), "unit": UNIT, "ms_per_step": e_ms,
                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-               "steps": args.e2e_steps, "matches_resident_run": ok,
-               "api": "HostPipeline.run: pinned host stems -> chunked H2D -> features_and_logmel kernels -> D2H of "
-                      "features and log-mels (features + mel only; augmentation decisions are host-side)"}
+               "steps": args.e2e_steps, "workload": args.workload, "anchors_positives_match_resident_run": same, "api": api}
+
+    # ---- same-box GPU comparator: the reference's math on CUDA tensors (cuFFT + cuBLAS + ATen) ------------
+    comparator = None
+    if rank == 0 and not args.no_comparator:
+        try:
+            comparator = torch_cuda_comparator(torch, dev, stems)
+        except Exception as e:                                              # noqa: BLE001
+            comparator = {"error": str(e)[:300]}
+    barrier()
+
+    # ---- parity of the timed batch against the oracle (host cores) ---------------------------------------
+    parity = None
+    if parity_in is not None:
+        try:
+            report = parity_check(*parity_in, fe.feature_names(), with_aug)
+            for path in (PARITY_REPORT, os.path.join(ROOT, "gpurun_out", "parity_report.json")):
+                try:                             # profiles/ is the committed copy; gpurun_out/ is what travels back from a GPU box
+                    if os.path.isdir(os.path.dirname(path)):
+                        with open(path, "w") as f:
+                            json.dump(report, f, indent=1)
+                except OSError:
+                    pass
+            worst = max(report["per_feature"], key=lambda r: r["worst_err_over_tolerance"])
+            parity = {k: report[k] for k in ("ok", "features_ok", "clips", "features_max_abs_err",
+                                             "features_worst_err_over_tolerance", "mel_power_worst_err_over_tolerance",
+                                             "logmel_max_abs_err_vs_fp64", "logmel_max_abs_err_loud_bins_vs_fp64",
+                                             "augmented_waveform_max_rel_err", "augmented_clips_with_reverb",
+                                             "oracle_seconds")}
+            parity["worst_feature"] = {"name": worst["name"], "max_abs_err": worst["max_abs_err_vs_fp32_oracle"],
+                                       "err_over_tolerance": worst["worst_err_over_tolerance"]}
+            parity["per_feature_report"] = "profiles/parity_report.json (64 features: max abs err vs the fp32 and the fp64 oracle)"
+        except Exception as e:                                              # noqa: BLE001
+            parity = {"ok": False, "error": str(e)[:300]}
+    barrier()
 
     if rank == 0:
         peak, peak_src = measured_peak_hbm()
         k1 = kernels["k1_features_ms"]
-        achieved = N_CLIPS * ALG_BYTES_PER_CLIP / (k1 / 1e3) / 1e9
+        alg = N_CLIPS * ALG_BYTES_PER_CLIP
+        achieved = alg / (k1 / 1e3) / 1e9
         traffic = None
         try:
             with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
                 traffic = json.load(f).get("dram_bytes_per_launch")
         except Exception:
             pass
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        line = {"metric": METRICS[args.workload], "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config_dict(args.workload, world),
+                "config": config_dict(args.workload, world, args),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "kernel": "k1_features", "kernel_ms": k1, "peak_source": peak_src,
-                             "algorithmic_bytes_per_launch": N_CLIPS * ALG_BYTES_PER_CLIP,
-                             "note": "K1 is FP32-issue-bound (20 FLOP/B), the HBM fraction is what BASELINE.json asks for"},
+                             "algorithmic_bytes_per_launch": alg,
+                             "note": "K1 is bound by issue slots at 25 % occupancy (20 FLOP/B, no wasted DRAM traffic); the HBM "
+                                     "fraction is what BASELINE.json asks for"},
+                "roofline_step": {"algorithmic_bytes_per_step": alg, "achieved": alg / (ms / 1e3) / 1e9, "peak": peak,
+                                  "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / peak,
+                                  "note": "SURVEY.md section 8d: config 3 has the same compulsory traffic as config 2 (48 clips "
+                                          "read, 24 negatives written and read back, 72 log-mels written)"},
                 "kernels": kernels, "gpu_launches": launches, "clocks": clocks}
+        if features_mel_ms is not None:
+            line["features_mel_ms"] = features_mel_ms
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         if e2e is not None:
             line["e2e"] = e2e
+        if comparator is not None:
+            line["torch_cuda_comparator"] = comparator
+        if parity is not None:
+            line["parity"] = parity
         if allgather is not None:
             line["allgather"] = allgather
         emit(line)

@@ -6,9 +6,9 @@ Public surface = the reference's three hot-path classes, same names and signatur
 CUDA kernels of ``csrc/`` through the C ABI declared in ``include/mixfe.h``.
 """
 from ._native import STEMS, Plan, build, launch_count, lib
-from .mixing_utils import AudioAugmenter, ClipAugmentation, MixingFeatureExtractor, butter_sos
+from .mixing_utils import AudioAugmenter, BatchAugmentation, ClipAugmentation, MixingFeatureExtractor, butter_sos
 from .model import MelSpectrogramPreprocessor
 from .loss import MultiResolutionSTFTLoss
 
 __all__ = ["STEMS", "Plan", "build", "lib", "launch_count", "MixingFeatureExtractor", "AudioAugmenter",
-           "ClipAugmentation", "MelSpectrogramPreprocessor", "MultiResolutionSTFTLoss", "butter_sos"]
+           "ClipAugmentation", "BatchAugmentation", "MelSpectrogramPreprocessor", "MultiResolutionSTFTLoss", "butter_sos"]

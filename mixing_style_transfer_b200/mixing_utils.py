@@ -286,6 +286,15 @@ class BatchAugmentation:
     def __len__(self):
         return self.n
 
+    def slice(self, lo: int, hi: int) -> "BatchAugmentation":
+        """Decisions of clips [lo, hi) (views: no copy of the packed parameters or the impulses)."""
+        import numpy as np
+        n = hi - lo
+        params = (AugParams * n).from_buffer(self.params, lo * ctypes.sizeof(AugParams))
+        rows = self.reverb_rows[(self.reverb_rows >= lo) & (self.reverb_rows < hi)] - lo
+        imp = self.impulse[lo:hi] if (self.impulse is not None and rows.size) else None
+        return BatchAugmentation(n, params, imp, rows, {k: v[lo:hi] for k, v in self.arrays.items()})
+
 
 def _aug_dtype():
     import numpy as np
@@ -378,8 +387,9 @@ class AudioAugmenter:
             if env is None:
                 t = torch.linspace(0, 0.5, L, device=impulse_device)
                 env = self._env[key] = torch.exp(-t / (0.5 / 4))
-            impulse = torch.zeros((n, L), dtype=torch.float32, device=impulse_device)
-            impulse[torch.from_numpy(rows).to(impulse_device)] = env * torch.randn(rows.size, L, device=impulse_device) * 0.1
+            # noise for every row (the kernels read row b only when reverb_on[b]): no host-dependent indexing, so the
+            # draw stays asynchronous when impulse_device is the GPU
+            impulse = env * torch.randn(n, L, device=impulse_device) * 0.1
         return BatchAugmentation(n, arr, impulse, rows, {"gain_on": gain_on, "gain_db": gain_db.numpy(), "tilt_on": tilt_on,
                                                          "tilt_high": high, "comp_on": np.asarray(a["comp_on"]).astype(bool),
                                                          "bw_on": bw_on, "cutoff_hz": fc, "reverb_on": rev})

@@ -1,5 +1,9 @@
 """Host-resident batches: chunked H2D -> kernels -> D2H with the three legs overlapped.
 
+Two entry points: `HostPipeline.run` (features + log-mel of N clips) and `TripletPipeline.run` (the training batch:
+anchors and positives come from the host, the negatives are made ON THE DEVICE by the augmentation kernels from the
+anchors that were just uploaded, then features + log-mel of all three -- BASELINE config 3).
+
 The reference computes features in DataLoader workers on CPU tensors (src/data.py:231-265) and ships
 stems to the GPU afterwards (src/train.py:231).  With the front end on the GPU the stems cross PCIe
 first; this helper is the user-facing call for that case: pinned host stems in, pinned host features
@@ -89,6 +93,91 @@ class HostPipeline:
                 feat_out[lo:hi].copy_(slot["feat"][:m], non_blocking=True)
                 if self.with_logmel:
                     lm_out[lo:hi].copy_(slot["lm"][:m], non_blocking=True)
+                slot["drained"].record(self.s_down)
+        self.s_down.synchronize()
+        self.s_run.synchronize()
+
+
+class TripletPipeline:
+    """The contrastive training batch from host memory (BASELINE.json config 3): G anchors and G positives cross
+    PCIe, the G negatives are augment_stems(anchors) computed on the device (reference: src/data.py:231-265 calls
+    AudioAugmenter in the DataLoader worker and ships three waveforms), then features + log-mel of all 3G clips.
+    Outputs are ordered anchors | positives | negatives.  The extractor's and the augmenter's kernels run on this
+    object's private stream, on private plans."""
+
+    def __init__(self, extractor, augmenter, n_triplets: int, T: int, chunk: int = 4, device=None, with_logmel: bool = True):
+        self.fe, self.aug = extractor, augmenter
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.plan = extractor._new_plan(self.device)
+        self.G, self.T = n_triplets, T
+        self.chunk = max(1, min(chunk, n_triplets))
+        self.with_logmel = with_logmel
+        sizes, left = [], n_triplets
+        if n_triplets > 2 * self.chunk:                  # short first / last chunks: the legs nothing overlaps
+            head = max(1, self.chunk // 2)
+            sizes.append(head); left -= 2 * head
+        while left > 0:
+            m = min(self.chunk, left)
+            sizes.append(m); left -= m
+        if n_triplets > 2 * self.chunk:
+            sizes.append(max(1, self.chunk // 2))
+        self.bounds, lo = [], 0
+        for m in sizes:
+            self.bounds.append((lo, lo + m)); lo += m
+        assert lo == n_triplets
+        F = self.plan.num_frames(T)
+        c3 = 3 * self.chunk
+        self.slots = []
+        for _ in range(2):
+            self.slots.append({
+                "stems": [torch.empty((c3, 2, T), dtype=torch.float32, device=self.device) for _ in STEMS],
+                "feat": torch.empty((c3, self.plan.feature_dim), dtype=torch.float32, device=self.device),
+                "lm": torch.empty((c3, 8, self.plan.n_mels, F), dtype=torch.float32, device=self.device) if with_logmel else None,
+                "uploaded": torch.cuda.Event(), "computed": torch.cuda.Event(), "drained": torch.cuda.Event(),
+            })
+        self.s_up = torch.cuda.Stream(self.device)
+        self.s_run = torch.cuda.Stream(self.device)
+        self.s_down = torch.cuda.Stream(self.device)
+        self.h2d_bytes = 4 * 2 * T * 4 * 2 * n_triplets
+        self.d2h_bytes = 4 * 3 * n_triplets * (self.plan.feature_dim + (8 * self.plan.n_mels * F if with_logmel else 0))
+
+    def run(self, host_stems: Dict[str, torch.Tensor], decisions, feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
+        """host_stems: dict of pinned (2G,2,T), anchors then positives; decisions: G augmentation decisions (a list of
+        ClipAugmentation or the BatchAugmentation of AudioAugmenter.draw_batch); feat_out pinned (3G,D); lm_out pinned
+        (3G,8,n_mels,F) or None.  Returns after everything has landed in host memory."""
+        G = self.G
+        if len(decisions) != G:
+            raise ValueError(f"{len(decisions)} decisions for {G} anchors")
+        cur = torch.cuda.current_stream(self.device)
+        for s in (self.s_up, self.s_run, self.s_down):
+            s.wait_stream(cur)
+        for i, (lo, hi) in enumerate(self.bounds):
+            m = hi - lo
+            slot = self.slots[i & 1]
+            with torch.cuda.stream(self.s_up):
+                if i >= 2:
+                    self.s_up.wait_event(slot["computed"])
+                for d, name in zip(slot["stems"], STEMS):
+                    d[:m].copy_(host_stems[name][lo:hi], non_blocking=True)
+                    d[m:2 * m].copy_(host_stems[name][G + lo:G + hi], non_blocking=True)
+                slot["uploaded"].record(self.s_up)
+            with torch.cuda.stream(self.s_run):
+                self.s_run.wait_event(slot["uploaded"])
+                if i >= 2:
+                    self.s_run.wait_event(slot["drained"])
+                dec = decisions.slice(lo, hi) if hasattr(decisions, "slice") else decisions[lo:hi]
+                self.aug.apply({n: d[:m] for n, d in zip(STEMS, slot["stems"])}, dec,
+                               out={n: d[2 * m:3 * m] for n, d in zip(STEMS, slot["stems"])})
+                self.plan.features_logmel([d[:3 * m] for d in slot["stems"]], True, self.with_logmel,
+                                          features_out=slot["feat"][:3 * m],
+                                          logmel_out=slot["lm"][:3 * m] if self.with_logmel else None)
+                slot["computed"].record(self.s_run)
+            with torch.cuda.stream(self.s_down):
+                self.s_down.wait_event(slot["computed"])
+                for part in range(3):
+                    feat_out[part * G + lo:part * G + hi].copy_(slot["feat"][part * m:(part + 1) * m], non_blocking=True)
+                    if self.with_logmel:
+                        lm_out[part * G + lo:part * G + hi].copy_(slot["lm"][part * m:(part + 1) * m], non_blocking=True)
                 slot["drained"].record(self.s_down)
         self.s_down.synchronize()
         self.s_run.synchronize()

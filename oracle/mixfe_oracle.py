@@ -88,11 +88,13 @@ def htk_mel_filterbank(sample_rate: int, n_fft: int, n_mels: int) -> torch.Tenso
 class MelFrontEnd:
     """power-mel of (..., T) audio: reflect-pad n_fft/2, periodic Hann, rfft, |.|^2, @fb."""
 
-    def __init__(self, cfg: FrontEndConfig, dtype=torch.float32):
+    def __init__(self, cfg: FrontEndConfig, dtype=torch.float32, device="cpu"):
+        # device: "cpu" for the oracle proper; a CUDA device only for bench.py's torch_cuda_comparator, which times
+        # this same reference math (torch.stft -> cuFFT, dense matmul -> cuBLAS) on the GPU the kernels run on
         self.cfg = cfg
         self.dtype = dtype
-        self.window = hann_periodic(cfg.n_fft).to(dtype)
-        self.fb = htk_mel_filterbank(cfg.sample_rate, cfg.n_fft, cfg.n_mels).to(dtype)
+        self.window = hann_periodic(cfg.n_fft).to(dtype).to(device)
+        self.fb = htk_mel_filterbank(cfg.sample_rate, cfg.n_fft, cfg.n_mels).to(dtype).to(device)
 
     def power_spectrogram(self, x: torch.Tensor) -> torch.Tensor:
         c = self.cfg
@@ -133,15 +135,15 @@ def dynamics_features(x: torch.Tensor) -> torch.Tensor:
     crest = 20 * torch.log10(peak / (rms + 1e-8))
     ld = loudness(x)
     # the reference round-trips the loudness through a Python float (:134) -- exact
-    ld2 = torch.tensor([ld.item(), ld.item()], dtype=x.dtype)
+    ld2 = torch.tensor([ld.item(), ld.item()], dtype=x.dtype, device=x.device)
     return torch.cat([rms, crest, ld2])
 
 
 def _pearson_vs_index(curve: torch.Tensor) -> torch.Tensor:
     """tilt: 0 when the unbiased std is < 1e-6 (:187,:222), else corrcoef with arange (:190)."""
     if curve.std() < 1e-6:
-        return torch.tensor(0.0, dtype=curve.dtype)
-    idx = torch.arange(curve.shape[0], dtype=curve.dtype)
+        return torch.tensor(0.0, dtype=curve.dtype, device=curve.device)
+    idx = torch.arange(curve.shape[0], dtype=curve.dtype, device=curve.device)
     return torch.corrcoef(torch.stack([idx, curve]))[0, 1]
 
 
@@ -164,9 +166,9 @@ def spectral_features(x: torch.Tensor, fe: MelFrontEnd) -> torch.Tensor:
     # the reference correlates against arange(n_spectral_bins) even when curve has n_mels entries
     # (:220); corrcoef would raise on a length mismatch, which only happens for n_bins > n_mels.
     if curve.std() < 1e-6:
-        tilt = torch.tensor(0.0, dtype=curve.dtype)
+        tilt = torch.tensor(0.0, dtype=curve.dtype, device=curve.device)
     else:
-        idx = torch.arange(c.n_spectral_bins, dtype=curve.dtype)
+        idx = torch.arange(c.n_spectral_bins, dtype=curve.dtype, device=curve.device)
         tilt = torch.corrcoef(torch.stack([idx, curve]))[0, 1]
     return torch.cat([curve, torch.stack([tilt, flat])]).to(x.dtype)
 
