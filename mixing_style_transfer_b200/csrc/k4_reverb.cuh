@@ -24,10 +24,21 @@
 
 namespace mixfe {
 
-constexpr int kRevN1 = 1024, kRevN2 = 1024;
-constexpr int kRevN = kRevN1 * kRevN2;           // 2^20
-constexpr int kColsPerCta = 8;
-constexpr int kColStride = kRevN1 + 4;           // float2 elements per staged column
+// The transform length is N = N1 * 1024 with N1 = 512 (N = 2^19: a 10 s clip plus the 0.5 s impulse fits one
+// circular correlation) or N1 = 1024 (N = 2^20, longer clips, overlap-save segments).  Element n = r * 1024 + c sits in
+// row r (of N1) and column c (of 1024); "columns" are the stride-1024 transforms of length N1, "rows" the contiguous
+// transforms of length 1024.
+constexpr int kRevN2 = 1024;
+constexpr int kRevMaxN = 1024 * kRevN2;          // 2^20
+constexpr int kColWarps = 8;
+
+template <int LOG1> struct RevGeom {
+    static constexpr int N1 = 1 << LOG1;                      // column length
+    static constexpr int kColsPerWarp = 1024 / N1;            // a warp transforms 1024 points: one column of 1024 or two of 512
+    static constexpr int kCols = kColWarps * kColsPerWarp;    // columns per CTA tile
+    static constexpr int kStride = N1 + 4;                    // float2 elements per staged column
+    static constexpr int kTwShift = 10 - LOG1;                // exp(-2 pi i e / N) = table entry e << kTwShift of the 2^20 tables
+};
 
 // One warp, 1024 points: in v[n1] = x[32 n1 + lane]; out v[k2] = X[lane + 32 k2].
 // exw: 1024 float2 of warp-private shared memory; tw[k1*32 + n2] = exp(-2 pi i n2 k1/1024) in shared memory.
@@ -62,6 +73,50 @@ __device__ __forceinline__ void warp_fft1024(float (&re)[32], float (&im)[32], f
     for (int k2 = 0; k2 < 32; ++k2) { re[k2] = tr[k2]; im[k2] = ti[k2]; }
 }
 
+// One warp, TWO 512-point transforms (columns A and B) at once, 512 = 16 x 32:
+//   in  re[n1], im[n1]          = x_A[32 n1 + lane], n1 < 16;  re[16 + n1], im[16 + n1] = x_B[32 n1 + lane]
+//   out re[k2], im[k2], k2 < 32 = X_A[lane + 16 k2] for lane < 16,  X_B[(lane - 16) + 16 k2] for lane >= 16.
+// Every lane runs two 16-point DFTs (its 16 samples of each column), the inter-pass twiddle W_512^(n2 k1) comes from
+// the even rows of the 1024-point table, the exchange buffer holds 32 rows (k1 of A, then k1 of B) of 32 entries with
+// the XOR swizzle of warp_fft1024, and every lane finishes one 32-point DFT.
+__device__ __forceinline__ void warp_fft512x2(float (&re)[32], float (&im)[32], float2* exw, const float2* tw, int lane) {
+#pragma unroll
+    for (int col = 0; col < 2; ++col) {
+        float ar[16], ai[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { ar[i] = re[16 * col + i]; ai[i] = im[16 * col + i]; }
+        dft16_dif(ar, ai);
+#pragma unroll
+        for (int k1 = 0; k1 < 16; ++k1) {
+            const float yr = ar[brev4(k1)], yi = ai[brev4(k1)];
+            float2 o;
+            if (k1 == 0) {
+                o = make_float2(yr, yi);
+            } else {
+                const float2 t = tw[(2 * k1) * 32 + lane];            // exp(-2 pi i lane k1 / 512)
+                o.x = fmaf(yr, t.x, -yi * t.y);
+                o.y = fmaf(yr, t.y, yi * t.x);
+            }
+            const int row = 16 * col + k1;
+            exw[row * 32 + (lane ^ row)] = o;
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int n2 = 0; n2 < 32; ++n2) {
+        const float2 v = exw[lane * 32 + (n2 ^ lane)];
+        re[n2] = v.x;
+        im[n2] = v.y;
+    }
+    __syncwarp();
+    dft32_dif(re, im);
+    float tr[32], ti[32];
+#pragma unroll
+    for (int k2 = 0; k2 < 32; ++k2) { tr[k2] = re[brev5(k2)]; ti[k2] = im[brev5(k2)]; }
+#pragma unroll
+    for (int k2 = 0; k2 < 32; ++k2) { re[k2] = tr[k2]; im[k2] = ti[k2]; }
+}
+
 // exp(-2 pi i e / 2^20) from two 1024-entry tables: e = 1024 hi + lo.
 __device__ __forceinline__ float2 twiddle_long(const float2* __restrict__ tw_lin, const float2* __restrict__ tw_fine, unsigned e) {
     const float2 a = __ldg(tw_lin + (e >> 10)), c = __ldg(tw_fine + (e & 1023u));
@@ -79,8 +134,8 @@ struct K4Params {
     long long imp_stride;                  // floats between the impulses of consecutive clips (0: one impulse for all)
     const int* slot_clip;                  // [n_slots] clip index of each reverb slot
     const float* impulse;                  // [B][L] (row b at impulse + b * imp_stride)
-    float2* X;                             // [n_slots][n_seg][2^20]
-    float2* H;                             // [n_slots][2^20]
+    float2* X;                             // [n_slots][n_seg][N]
+    float2* H;                             // [n_slots][N]
     const double* part_energy;             // [B][4][2][n_chunks]
     const float2* tw;                      // [1024] 32x32 twiddles
     const float2* tw_lin;                  // [1024] exp(-2 pi i j/1024)
@@ -89,19 +144,21 @@ struct K4Params {
 
 enum { kColsX = 0, kColsH = 1, kColsInv = 2 };
 
-// grid (128 column groups, n_seg, n_slots); 8 warps, warp w transforms column 8*group + w.
-template <int MODE>
+// grid (1024 / kCols column groups, n_seg, n_slots); 8 warps, warp w transforms column(s) kColsPerWarp * w (+ 1) of the group.
+template <int MODE, int LOG1>
 __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params p) {
+    using G = RevGeom<LOG1>;
+    constexpr int N = G::N1 * kRevN2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* const tile = reinterpret_cast<float2*>(smem_raw);                   // [8][kColStride]
-    float2* const tw = tile + kColsPerCta * kColStride;                          // [1024]
+    float2* const tile = reinterpret_cast<float2*>(smem_raw);                   // [kCols][kStride]
+    float2* const tw = tile + G::kCols * G::kStride;                             // [1024]
     __shared__ float share[kNumStems];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int col0 = blockIdx.x * kColsPerCta, seg = blockIdx.y, slot = blockIdx.z;
+    const int col0 = blockIdx.x * G::kCols, seg = blockIdx.y, slot = blockIdx.z;
     const int b = p.slot_clip[slot];
     const long long seg0 = (long long)seg * p.seg_len;
-    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * kRevN;
-    float2* const Hs = p.H + (long long)slot * kRevN;
+    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * N;
+    float2* const Hs = p.H + (long long)slot * N;
 
     for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
     if (MODE == kColsInv && !p.standalone) {
@@ -119,10 +176,10 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
             for (int s = 0; s < kNumStems; ++s) share[s] = share[s] / tot;
         }
     }
-    // ---- stage 1024 rows x 8 columns ------------------------------------------------------------
+    // ---- stage N1 rows x kCols columns ------------------------------------------------------------
     {
-        const int c = tid & 7;
-        for (int r = tid >> 3; r < kRevN1; r += 32) {
+        const int c = tid % G::kCols;
+        for (int r = tid / G::kCols; r < G::N1; r += 256 / G::kCols) {
             const long long n = (long long)r * kRevN2 + col0 + c;
             float2 v = make_float2(0.0f, 0.0f);
             if (MODE == kColsX) {
@@ -147,43 +204,71 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
             } else {
                 v = Xs[n];
             }
-            tile[c * kColStride + r] = v;
+            tile[c * G::kStride + r] = v;
         }
     }
     __syncthreads();
-    // ---- one column per warp ----------------------------------------------------------------------
+    // ---- one (N1 = 1024) or two (N1 = 512) columns per warp -----------------------------------------
     {
-        float2* const colbuf = tile + warp * kColStride;
         float re[32], im[32];
+        if (G::kColsPerWarp == 1) {
+            float2* const colbuf = tile + warp * G::kStride;
 #pragma unroll
-        for (int n1 = 0; n1 < 32; ++n1) {
-            const float2 v = colbuf[32 * n1 + lane];
-            re[n1] = v.x;
-            im[n1] = v.y;
-        }
-        __syncwarp();
-        warp_fft1024(re, im, colbuf, tw, lane);                   // the column's own storage is the exchange buffer
-        const unsigned n2 = (unsigned)(col0 + warp);
-#pragma unroll
-        for (int k2 = 0; k2 < 32; ++k2) {
-            const unsigned k1 = (unsigned)(lane + 32 * k2);       // output index of the column transform
-            float2 o;
-            if (MODE == kColsInv) {
-                o = make_float2(re[k2] * (1.0f / (float)kRevN), -im[k2] * (1.0f / (float)kRevN));
-            } else {
-                const float2 w = twiddle_long(p.tw_lin, p.tw_fine, (n2 * k1) & (unsigned)(kRevN - 1));
-                o = make_float2(fmaf(re[k2], w.x, -im[k2] * w.y), fmaf(re[k2], w.y, im[k2] * w.x));
+            for (int n1 = 0; n1 < 32; ++n1) {
+                const float2 v = colbuf[32 * n1 + lane];
+                re[n1] = v.x;
+                im[n1] = v.y;
             }
-            colbuf[k1] = o;
+            __syncwarp();
+            warp_fft1024(re, im, colbuf, tw, lane);                   // the column's own storage is the exchange buffer
+            const unsigned n2 = (unsigned)(col0 + warp);
+#pragma unroll
+            for (int k2 = 0; k2 < 32; ++k2) {
+                const unsigned k1 = (unsigned)(lane + 32 * k2);       // output index of the column transform
+                float2 o;
+                if (MODE == kColsInv) {
+                    o = make_float2(re[k2] * (1.0f / (float)N), -im[k2] * (1.0f / (float)N));
+                } else {
+                    const float2 w = twiddle_long(p.tw_lin, p.tw_fine, ((n2 * k1) << G::kTwShift) & (unsigned)(kRevMaxN - 1));
+                    o = make_float2(fmaf(re[k2], w.x, -im[k2] * w.y), fmaf(re[k2], w.y, im[k2] * w.x));
+                }
+                colbuf[k1] = o;
+            }
+        } else {
+            // columns 2 warp (A) and 2 warp + 1 (B); their two staged columns (2 x 516 float2 >= 1024) are the exchange buffer
+            float2* const bufA = tile + (2 * warp) * G::kStride;
+            float2* const bufB = bufA + G::kStride;
+#pragma unroll
+            for (int n1 = 0; n1 < 16; ++n1) {
+                const float2 va = bufA[32 * n1 + lane], vb = bufB[32 * n1 + lane];
+                re[n1] = va.x; im[n1] = va.y;
+                re[16 + n1] = vb.x; im[16 + n1] = vb.y;
+            }
+            __syncwarp();
+            warp_fft512x2(re, im, bufA, tw, lane);
+            float2* const mine = lane < 16 ? bufA : bufB;
+            const unsigned n2 = (unsigned)(col0 + 2 * warp + (lane >> 4));
+#pragma unroll
+            for (int k2 = 0; k2 < 32; ++k2) {
+                const unsigned k1 = (unsigned)((lane & 15) + 16 * k2);
+                float2 o;
+                if (MODE == kColsInv) {
+                    o = make_float2(re[k2] * (1.0f / (float)N), -im[k2] * (1.0f / (float)N));
+                } else {
+                    const float2 w = twiddle_long(p.tw_lin, p.tw_fine, ((n2 * k1) << G::kTwShift) & (unsigned)(kRevMaxN - 1));
+                    o = make_float2(fmaf(re[k2], w.x, -im[k2] * w.y), fmaf(re[k2], w.y, im[k2] * w.x));
+                }
+                mine[k1] = o;
+            }
         }
     }
     __syncthreads();
-    // ---- write back (coalesced 64-byte runs) / reverb epilogue --------------------------------------
+    // ---- write back (coalesced runs of kCols elements) / reverb epilogue ------------------------------
     {
-        const int c = tid & 7;
-        for (int r = tid >> 3; r < kRevN1; r += 32) {
+        const int c = tid % G::kCols;
+        for (int r = tid / G::kCols; r < G::N1; r += 256 / G::kCols) {
             const long long n = (long long)r * kRevN2 + col0 + c;
-            const float2 v = tile[c * kColStride + r];
+            const float2 v = tile[c * G::kStride + r];
             if (MODE == kColsX) {
                 Xs[n] = v;
             } else if (MODE == kColsH) {
@@ -219,16 +304,18 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
 
 enum { kRowsX = 0, kRowsH = 1 };
 
-// grid (128 row groups, n_seg, n_slots); 8 warps, warp w transforms row 8*group + w.
-template <int MODE>
+// grid (N1 / 8 row groups, n_seg, n_slots); 8 warps, warp w transforms row 8*group + w (1024 points).
+template <int MODE, int LOG1>
 __global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params p) {
+    using G = RevGeom<LOG1>;
+    constexpr int N = G::N1 * kRevN2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* const exall = reinterpret_cast<float2*>(smem_raw);                  // [8][1024]
     float2* const tw = exall + 8 * 1024;                                        // [1024]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int row = blockIdx.x * 8 + warp, seg = blockIdx.y, slot = blockIdx.z;
-    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * kRevN + (long long)row * kRevN2;
-    float2* const Hs = p.H + (p.imp_stride == 0 ? 0ll : (long long)slot * kRevN) + (long long)row * kRevN2;
+    float2* const Xs = p.X + ((long long)slot * p.n_seg + seg) * N + (long long)row * kRevN2;
+    float2* const Hs = p.H + (p.imp_stride == 0 ? 0ll : (long long)slot * N) + (long long)row * kRevN2;
     for (int i = tid; i < 1024; i += 256) tw[i] = p.tw[i];
     __syncthreads();
     float2* const exw = exall + warp * 1024;
@@ -258,7 +345,7 @@ __global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params 
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
         const unsigned n2 = (unsigned)(lane + 32 * j);
-        const float2 w = twiddle_long(p.tw_lin, p.tw_fine, (n2 * (unsigned)row) & (unsigned)(kRevN - 1));
+        const float2 w = twiddle_long(p.tw_lin, p.tw_fine, ((n2 * (unsigned)row) << G::kTwShift) & (unsigned)(kRevMaxN - 1));
         Xs[n2] = make_float2(fmaf(re[j], w.x, -im[j] * w.y), fmaf(re[j], w.y, im[j] * w.x));
     }
 }
@@ -356,31 +443,47 @@ inline int prepare_augment(const mixfe_aug_params* params, int B, int T, int n_s
     return MIXFE_OK;
 }
 
-struct ReverbLayout { int n_seg = 0, seg_len = 0; };
+// Transform length for a clip of T samples and an impulse of L taps: 2^19 when one circular correlation of that size
+// holds the whole clip (T + L - 1 <= 2^19: the 10 s clips of the training batch), else 2^20 with overlap-save segments.
+struct ReverbLayout { int log1 = 10, n = kRevMaxN, n_seg = 0, seg_len = 0; };
+
+inline ReverbLayout reverb_layout(int T, int L) {
+    ReverbLayout r;
+    if ((long long)T + L - 1 <= (1 << 19)) { r.log1 = 9; r.n = 1 << 19; }
+    r.seg_len = r.n - L + 1;
+    r.n_seg = (T + r.seg_len - 1) / r.seg_len;
+    return r;
+}
 
 // the five launches of the FFT-domain correlation for the slots listed in p4.slot_clip
-inline int launch_reverb(mixfe_plan* pl, K4Params& p4, int n_slots, cudaStream_t stream) {
-    const int smem_cols = (kColsPerCta * kColStride + 1024) * (int)sizeof(float2);
+template <int LOG1>
+inline int launch_reverb_n(mixfe_plan* pl, K4Params& p4, int n_slots, cudaStream_t stream) {
+    using G = RevGeom<LOG1>;
+    const int smem_cols = (G::kCols * G::kStride + 1024) * (int)sizeof(float2);
     const int smem_rows = (8 * 1024 + 1024) * (int)sizeof(float2);
     int rc;
-    if ((rc = smem_optin(k4_cols<kColsX>, pl->device, smem_cols)) || (rc = smem_optin(k4_cols<kColsH>, pl->device, smem_cols)) ||
-        (rc = smem_optin(k4_cols<kColsInv>, pl->device, smem_cols)) || (rc = smem_optin(k4_rows<kRowsX>, pl->device, smem_rows)) ||
-        (rc = smem_optin(k4_rows<kRowsH>, pl->device, smem_rows)))
+    if ((rc = smem_optin(k4_cols<kColsX, LOG1>, pl->device, smem_cols)) || (rc = smem_optin(k4_cols<kColsH, LOG1>, pl->device, smem_cols)) ||
+        (rc = smem_optin(k4_cols<kColsInv, LOG1>, pl->device, smem_cols)) || (rc = smem_optin(k4_rows<kRowsX, LOG1>, pl->device, smem_rows)) ||
+        (rc = smem_optin(k4_rows<kRowsH, LOG1>, pl->device, smem_rows)))
         return rc;
     {
         KernelTimer timer(pl, MIXFE_KERNEL_REVERB, stream);
         // one impulse for all clips (imp_stride 0): its spectrum is computed once and every slot reads slot 0's
         const int h_slots = p4.imp_stride == 0 ? 1 : n_slots;
-        const dim3 g1(kRevN2 / kColsPerCta, 1, h_slots), gs(kRevN2 / kColsPerCta, p4.n_seg, n_slots);
-        k4_cols<kColsH><<<g1, 256, smem_cols, stream>>>(p4);
-        k4_rows<kRowsH><<<dim3(kRevN1 / 8, 1, h_slots), 256, smem_rows, stream>>>(p4);
-        k4_cols<kColsX><<<gs, 256, smem_cols, stream>>>(p4);
-        k4_rows<kRowsX><<<dim3(kRevN1 / 8, p4.n_seg, n_slots), 256, smem_rows, stream>>>(p4);
-        k4_cols<kColsInv><<<gs, 256, smem_cols, stream>>>(p4);
+        const dim3 g1(kRevN2 / G::kCols, 1, h_slots), gs(kRevN2 / G::kCols, p4.n_seg, n_slots);
+        k4_cols<kColsH, LOG1><<<g1, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsH, LOG1><<<dim3(G::N1 / 8, 1, h_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsX, LOG1><<<gs, 256, smem_cols, stream>>>(p4);
+        k4_rows<kRowsX, LOG1><<<dim3(G::N1 / 8, p4.n_seg, n_slots), 256, smem_rows, stream>>>(p4);
+        k4_cols<kColsInv, LOG1><<<gs, 256, smem_cols, stream>>>(p4);
     }
     MIXFE_CUDA(cudaGetLastError());
     launch_counter() += 5;
     return MIXFE_OK;
+}
+
+inline int launch_reverb(mixfe_plan* pl, K4Params& p4, const ReverbLayout& lay, int n_slots, cudaStream_t stream) {
+    return lay.log1 == 9 ? launch_reverb_n<9>(pl, p4, n_slots, stream) : launch_reverb_n<10>(pl, p4, n_slots, stream);
 }
 
 inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* const out[kNumStems],
@@ -415,20 +518,20 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
 
     // ---- workspace -------------------------------------------------------------------------------------
     const int n_slots = (int)slot_clip.size();
-    int n_seg = 0, seg_len = 0;
+    ReverbLayout lay;
     if (n_slots) {
-        if (L > kRevN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevN / 2);
-        seg_len = kRevN - L + 1;
-        n_seg = (T + seg_len - 1) / seg_len;
+        if (L > kRevMaxN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevMaxN / 2);
+        lay = reverb_layout(T, L);
     }
+    const int n_seg = lay.n_seg, seg_len = lay.seg_len;
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_clips = carve(sizeof(AugClipDev) * B);
     const size_t o_sections = carve(sizeof(AugSection) * al.sections.size());
     const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
     const size_t o_slots = carve(sizeof(int) * (size_t)std::max(1, n_slots));
-    const size_t o_X = carve(sizeof(float2) * (size_t)kRevN * n_slots * std::max(1, n_seg));
-    const size_t o_H = carve(sizeof(float2) * (size_t)kRevN * n_slots);
+    const size_t o_X = carve(sizeof(float2) * (size_t)lay.n * n_slots * std::max(1, n_seg));
+    const size_t o_H = carve(sizeof(float2) * (size_t)lay.n * n_slots);
     rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
@@ -459,7 +562,7 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     p4.standalone = 0; p4.n_ch = 2; p4.sa_in = nullptr; p4.imp_stride = L;
     p4.impulse = impulse; p4.X = reinterpret_cast<float2*>(ws + o_X); p4.H = reinterpret_cast<float2*>(ws + o_H);
     p4.part_energy = p3.part_energy; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
-    return launch_reverb(pl, p4, n_slots, stream);
+    return launch_reverb(pl, p4, lay, n_slots, stream);
 }
 
 // AudioAugmenter.apply_spectral_tilt / apply_compression / apply_bandwidth_limit (:421-456) and the gain of :389-392 on
@@ -512,16 +615,17 @@ inline int run_reverb(mixfe_plan* pl, const float* in, float* out, long long str
     if (B > 65535) return fail(MIXFE_EINVAL, "B > 65535 clips per call");
     if ((C > 1 && stride_c < T) || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
     if (impulse_stride_b != 0 && impulse_stride_b < L) return fail(MIXFE_EINVAL, "impulse stride smaller than L");
-    if (L > kRevN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevN / 2);
+    if (L > kRevMaxN / 2) return fail(MIXFE_EUNSUPPORTED, "impulse of %d taps (max %d)", L, kRevMaxN / 2);
     DeviceGuard guard(pl->device);
-    const int seg_len = kRevN - L + 1, n_seg = (T + seg_len - 1) / seg_len;
+    const ReverbLayout lay = reverb_layout(T, L);
+    const int seg_len = lay.seg_len, n_seg = lay.n_seg;
     std::vector<int> slot_clip(B);
     for (int b = 0; b < B; ++b) slot_clip[b] = b;
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_slots = carve(sizeof(int) * (size_t)B);
-    const size_t o_X = carve(sizeof(float2) * (size_t)kRevN * B * n_seg);
-    const size_t o_H = carve(sizeof(float2) * (size_t)kRevN * (impulse_stride_b == 0 ? 1 : B));
+    const size_t o_X = carve(sizeof(float2) * (size_t)lay.n * B * n_seg);
+    const size_t o_H = carve(sizeof(float2) * (size_t)lay.n * (impulse_stride_b == 0 ? 1 : B));
     int rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
@@ -533,7 +637,7 @@ inline int run_reverb(mixfe_plan* pl, const float* in, float* out, long long str
     p4.standalone = 1; p4.n_ch = C; p4.sa_in = in; p4.imp_stride = impulse_stride_b;
     p4.impulse = impulse; p4.X = reinterpret_cast<float2*>(ws + o_X); p4.H = reinterpret_cast<float2*>(ws + o_H);
     p4.part_energy = nullptr; p4.tw = pl->d_tw; p4.tw_lin = pl->d_twlin; p4.tw_fine = pl->d_twfine;
-    return launch_reverb(pl, p4, B, stream);
+    return launch_reverb(pl, p4, lay, B, stream);
 }
 
 }  // namespace mixfe
