@@ -43,19 +43,19 @@ constexpr int kTF = 8;             // frames per CTA tile
 constexpr int kK1Threads = 256;    // 8 warps, one frame each
 constexpr int kNfft = 1024;
 constexpr int kNfreq = 513;
-constexpr int kTdN = 40;           // floats per record of time-domain partials (two records per tile)
+constexpr int kTdN = 56;           // floats per record of time-domain partials (two records per tile)
+constexpr int kTdMask = 40;        // first of the 16 masking slots of a record (4 warps x 4 stems)
 constexpr int kMaxMels = 128;
-// warp-private shared region (8 KB): [0, 8192) exchange during the FFT; afterwards
+// warp-private shared region: the 32 x 32 exchange of the FFT, element (row, col) at byte
+//   264 row + 8 col                     (row stride 264 bytes = 66 words: the transposed read, lane = row, touches 16
+//                                        different bank pairs per half-warp; every offset is an immediate, no XOR swizzle)
+// i.e. 8440 bytes; afterwards
 //   [skew, skew + 8 * 544)        (L, R) power column of the warp's frame, bins 0..512 + zero-weight overshoot;
 //                                 skew = 64 bytes for frames 2, 3, 6, 7 (the frame pairs that are read in the
 //                                 same half-warp phase of the mel walk then sit 16 banks apart)
-//   [kLogOff + 576 ch + 8 t, +512) row (ch, t = frame) of the CTA's log tile, 128 mel values; word offset
-//                                 = 2 * (8 ch + t) mod 32, so the transposed read of the store phase is conflict-free
-constexpr int kWarpRegion = 8192;
+constexpr int kWarpRegion = 8448;                   // a multiple of 128 bytes: all regions start on bank 0
+constexpr int kExRow = 264;                         // bytes per exchange row
 constexpr int kPvEntries = 544;
-constexpr int kPvBytes = (kPvEntries + 8) * 8;      // 4416
-constexpr int kLogOff = kPvBytes;
-constexpr int kLogChStride = 576;
 
 struct K1Params {
     const float* stem[kNumStems];
@@ -75,7 +75,7 @@ struct K1Params {
     float* part_td;                  // [B][n_tiles][2][kTdN]
     const float2* tw;                // [1024] tw[k1*32+n2] = exp(-2 pi i n2 k1 / 1024)
     const float* wsteps;             // per group of 8 filters: [steps][8] weights
-    const int* flo;                  // [kMaxMels] byte offset (8 * first walked bin) of each filter in the power column
+    const unsigned short* flo;       // [kMaxMels] byte offset (8 * first walked bin) of each filter in the power column
     int n_wt;                        // floats in wsteps
     int wmeta[8][2][4];              // per warp, per group slot: steps (even), weight offset, group index, 0
     int want_stats;
@@ -387,11 +387,10 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);              // [31][32], rows k1 = 1..31
     float4* const S = reinterpret_cast<float4*>(smem + p.off_s);              // [3][256]: thread-private S values of stems 0..2
     float* const wsteps = reinterpret_cast<float*>(smem + p.off_wsteps);      // [n_wt]
-    int* const flo = reinterpret_cast<int*>(smem + p.off_flo);                // [kMaxMels]
-    float* const red = reinterpret_cast<float*>(smem + p.off_red);            // [8][4]
-    const unsigned bar = smem_u32(smem + p.off_red + 128);                    // mbarrier of the TMA staging
-    int* const arrivals = reinterpret_cast<int*>(smem + p.off_red + 136);     // warps done reading xs
-    const unsigned bar2 = smem_u32(smem + p.off_red + 144);                   // mbarrier of the statistics rows
+    unsigned short* const flo = reinterpret_cast<unsigned short*>(smem + p.off_flo);   // [kMaxMels]
+    const unsigned bar = smem_u32(smem + p.off_red);                          // mbarrier of the TMA staging
+    int* const arrivals = reinterpret_cast<int*>(smem + p.off_red + 8);       // warps done reading xs
+    const unsigned bar2 = smem_u32(smem + p.off_red + 16);                    // mbarrier of the statistics rows
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long item = blockIdx.x;
@@ -436,7 +435,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 mbar_wait(bar, tma_parity);
                 tma_parity ^= 1u;
             }
-            __syncthreads();                 // B0: xs holds (tile, s); the previous store phase is over
+            __syncthreads();                 // B0: xs holds (tile, s); the mel walk of the previous stem has left the power columns
             bool stats_rows = false;
             if (s == 0 && p.want_stats) {
                 // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
@@ -548,9 +547,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     dft32_dif_packed(z);
                     if (pass == 0) {
                         // inter-pass twiddles in batches of 8, the next batch in flight while this one is used;
-                        // element (k1, lane) of the exchange goes to k1*32 + (lane ^ k1)  (256-byte rows, XOR swizzle)
+                        // element (k1, lane) of the exchange goes to row k1, column lane of the padded layout
                         const unsigned twa = smem_u32(tw + lane) - 256;            // the table starts at row k1 = 1
-                        const unsigned wa = smem_u32(exw) ^ (lane * 8);           // region is 8 KB aligned
+                        const unsigned wa = smem_u32(exw) + lane * 8;
                         float2 tq[2][8];
 #pragma unroll
                         for (int q = 1; q < 8; ++q) tq[0][q] = lds64<0>(twa + q * 256);
@@ -569,14 +568,14 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                                     float yr, yi;
                                     cunpack(z[brev5(k1)], yr, yi);
                                     const float2 t = tq[g & 1][q];
-                                    sts64<0>((wa ^ (k1 * 8)) + k1 * 256, fmaf(yr, t.x, -yi * t.y), fmaf(yr, t.y, yi * t.x));
+                                    sts64<0>(wa + k1 * kExRow, fmaf(yr, t.x, -yi * t.y), fmaf(yr, t.y, yi * t.x));
                                 }
                             }
                         }
                         __syncwarp();
-                        const unsigned ra = smem_u32(exw) + lane * 264;           // lane*256 + lane*8
+                        const unsigned ra = smem_u32(exw) + lane * kExRow;
 #pragma unroll
-                        for (int n2 = 0; n2 < 32; ++n2) z[n2] = lds_c<0>(ra ^ (n2 * 8));
+                        for (int n2 = 0; n2 < 32; ++n2) z[n2] = lds_c<0>(ra + n2 * 8);
                         __syncwarp();            // the exchange buffer becomes the power column
                     }
                 }
@@ -614,6 +613,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 const bool ok0 = 2 * q < nvalid, ok1 = 2 * q + 1 < nvalid;
                 const unsigned char* col = ex + 2 * q * kWarpRegion + (q & 1) * 64;
                 const long long tile_id = (long long)b * p.n_tiles + tile;
+                float* const lm_tile = p.logmel + (long long)b * p.lm_stride_b + t0 + 2 * q;      // + (ch n_mels + m) F
                 float sc[4];                                  // S = (mel_L + mel_R) / 2 of (group a, b) x (frame 2q, 2q+1)
 #pragma unroll
                 for (int ab = 0; ab < 2; ++ab) {
@@ -644,13 +644,14 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     float lg[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) lg[k] = ln_fast(v[k] + 1e-10f);
-                    if (m < p.n_mels_pad) {
-                        // row (ch, t) of the log tile lives in region t
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const int t = 2 * q + (k >> 1), ch = k & 1;
-                            *reinterpret_cast<float*>(ex + t * kWarpRegion + kLogOff + ch * kLogChStride + t * 8 + m * 4) = lg[k];
-                        }
+                    if (p.logmel && m < p.n_mels) {
+                        // The thread's two frames are neighbours in time and the 4 quarters of the warp cover the tile's 8
+                        // frames: one store instruction writes 8 filters x 32 contiguous bytes (whole sectors), straight
+                        // from the registers -- no staging tile, no store phase, no barrier.
+                        float* d0 = lm_tile + ((long long)(2 * s) * p.n_mels + m) * p.F;
+                        float* d1 = d0 + (long long)p.n_mels * p.F;
+                        if (ok0) { d0[0] = lg[0]; d1[0] = lg[1]; }
+                        if (ok1) { d0[1] = lg[2]; d1[1] = lg[3]; }
                     }
                     if (p.melpow && m < p.n_mels) {
 #pragma unroll
@@ -695,32 +696,10 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                         }
 #pragma unroll
                         for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
-                        if (lane == 0) {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) red[warp * 4 + i] = msum[i];
-                        }
+                        if (lane == 0)           // the warp's own slots of the tile's records: no CTA-wide reduction
+                            *reinterpret_cast<float4*>(p.part_td + tile_id * (2 * kTdN) + (warp >> 2) * kTdN + kTdMask + (warp & 3) * 4) =
+                                make_float4(msum[0], msum[1], msum[2], msum[3]);
                     }
-                }
-            }
-            __syncthreads();                 // B2: log tile complete (and `red` when s == 3)
-
-            // ---- epilogue B: coalesced store of the log-mel tile (32-byte runs along time) --------
-            {
-                const int col = tid & 15, ch = col >> 3, t = col & 7, m0 = tid >> 4;
-                if (t < nvalid) {
-                    const long long o = ((long long)(2 * s + ch) * p.n_mels + m0) * p.F + t0 + t;
-                    const long long step = 16ll * p.F;
-                    if (p.logmel) {
-                        float* dst = p.logmel + (long long)b * p.lm_stride_b + o;
-                        const float* src = reinterpret_cast<const float*>(ex + t * kWarpRegion + kLogOff + ch * kLogChStride + t * 8) + m0;
-#pragma unroll 8
-                        for (int m = m0; m < p.n_mels; m += 16, dst += step, src += 16) *dst = *src;
-                    }
-                }
-                if (s == kNumStems - 1 && p.want_stats && tid < 4) {
-                    float v = 0.0f;
-                    for (int w = 0; w < 8; ++w) v += red[w * 4 + tid];
-                    p.part_td[((long long)b * p.n_tiles + tile) * (2 * kTdN) + 33 + tid] = v;
                 }
             }
         }
@@ -741,6 +720,7 @@ struct K2Params {
     int B, T, F, n_mels, n_mels_pad, n_tiles;
     int n_bins;                      // 0: low/mid/high bands, else detailed curve of n_bins points
     int D;
+    int mask_per_warp;               // masking sums: 1 = slots kTdMask.. of both records (K1), 0 = slots 33..36 of record 0 (K1G)
 };
 
 __device__ __forceinline__ void put_feature(float* out, int idx, double v) {
@@ -790,9 +770,10 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         const int q = tid >> 3, sub = tid & 7;
         const bool is_max = q < 32 && (q & 7) >= 6;
         double v = 0.0;
-        if (q < 37) {
+        const bool used = p.mask_per_warp ? (q < 33 || q >= kTdMask) : q < 37;
+        if (used) {
             const float* src = p.part_td + (long long)b * p.n_tiles * (2 * kTdN);
-            const int n_rec = 2 * p.n_tiles, step = (q >= 33) ? 2 : 1;          // masking sums live in record 0 only
+            const int n_rec = 2 * p.n_tiles, step = (q >= 33 && q < 37) ? 2 : 1;          // K1G's masking sums live in record 0 only
             for (int t = sub * step; t < n_rec; t += 8 * step) {
                 const float* r = src + (long long)t * kTdN;
                 double u = (double)__ldg(r + q);
@@ -911,7 +892,9 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
     }
     if (tid >= 160 && tid < 160 + kNumStems) {
         const int i = tid - 160;
-        put_feature(out, 2 * per + i, sTd[33 + i] / ((double)p.n_mels * (double)p.F));      // :296-306
+        const double msum = p.mask_per_warp ? sTd[kTdMask + i] + sTd[kTdMask + 4 + i] + sTd[kTdMask + 8 + i] + sTd[kTdMask + 12 + i]
+                                            : sTd[33 + i];
+        put_feature(out, 2 * per + i, msum / ((double)p.n_mels * (double)p.F));      // :296-306
     }
 }
 

@@ -74,7 +74,8 @@ int build_mel_tables(mixfe_plan* pl) {
             if (w(k, m) != 0.0f) { if (first < 0) first = k; last = k; }
         if (first >= 0) { lo[m] = first; len[m] = last - first + 1; }
     }
-    std::vector<int> fstart(kMaxMels, 0), gn(n_groups, 0), gwoff(n_groups, 0);
+    std::vector<unsigned short> fstart(kMaxMels, 0);
+    std::vector<int> gn(n_groups, 0), gwoff(n_groups, 0);
     std::vector<float> wt;
     int n_steps = 0;
     for (int g = 0; g < n_groups; ++g) {
@@ -131,7 +132,7 @@ int build_mel_tables(mixfe_plan* pl) {
         }
         gn[g] = n;
         gwoff[g] = (int)wt.size();
-        for (int i = 0; i < 8; ++i) fstart[8 * g + i] = 8 * start[i];
+        for (int i = 0; i < 8; ++i) fstart[8 * g + i] = (unsigned short)(8 * start[i]);
         for (int st = 0; st < n; ++st)
             for (int i = 0; i < 8; ++i) {
                 const int m = 8 * g + i, k = start[i] + st;
@@ -159,14 +160,13 @@ int build_mel_tables(mixfe_plan* pl) {
     if ((rc = upload(&pl->d_wsteps, wt))) return rc;
     // shared-memory map of K1
     pl->nxs = (kTF - 1) * pl->hop + kNfft;
-    pl->off_ex = (pl->nxs * 8 + 1023) & ~1023;        // the exchange regions are addressed with XOR swizzles of the low
-                                                      // address bits: their base must stay 1 KB aligned for every hop
+    pl->off_ex = (pl->nxs * 8 + 127) & ~127;          // exchange regions: bank 0, 16-byte aligned for the TMA statistics rows
     pl->off_tw = pl->off_ex + 8 * kWarpRegion;
     pl->off_s = pl->off_tw + 31 * 32 * 8;            // rows k1 = 1..31 of the twiddle table (row 0 is all ones)
     pl->off_wsteps = pl->off_s + 3 * kK1Threads * 16;   // S: one float4 per thread and stem 0..2
     pl->off_flo = align16(pl->off_wsteps + n_wt * 4);
-    pl->off_red = align16(pl->off_flo + kMaxMels * 4);
-    pl->smem_k1 = pl->off_red + 8 * 4 * 4 + 32;          // masking scratch, mbarrier, arrival counter
+    pl->off_red = align16(pl->off_flo + kMaxMels * 2);           // two mbarriers and the arrival counter
+    pl->smem_k1 = pl->off_red + 32;
     if (pl->smem_k1 > 227 * 1024)
         return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
     if (int rc = smem_optin(k1_features, pl->device, pl->smem_k1)) return rc;
@@ -379,7 +379,7 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         K2Params q{};
         q.part_spec = p.part_spec; q.part_td = p.part_td; q.features = features;
         q.B = B; q.T = T; q.F = F; q.n_mels = pl->n_mels; q.n_mels_pad = pl->n_mels_pad; q.n_tiles = n_tiles;
-        q.n_bins = pl->n_bins; q.D = pl->D;
+        q.n_bins = pl->n_bins; q.D = pl->D; q.mask_per_warp = pl->use_generic ? 0 : 1;
         {
             KernelTimer timer(pl, MIXFE_KERNEL_FINALIZE, stream);
             k2_finalize<<<B, kK2Threads, 0, stream>>>(q);

@@ -14,7 +14,7 @@ struct mixfe_plan {
     float2* d_tw = nullptr;
     float2* d_twlin = nullptr;          // exp(-2 pi i j / 1024), j in [0, 1024)
     float2* d_twfine = nullptr;         // exp(-2 pi i e / 2^20), e in [0, 1024): fine twiddles of the long FFT
-    int* d_flo = nullptr;               // [128] byte offset of each filter's first walked bin in the power column
+    unsigned short* d_flo = nullptr;    // [128] byte offset of each filter's first walked bin in the power column
     float* d_wsteps = nullptr;          // per group of 8 filters: [steps][8] weights walked by K1's mel projection
     int n_wsteps = 0;                   // total steps over all groups
     int wmeta[8][2][4] = {};            // per warp, per group slot: steps, weight offset, group index, 0
