@@ -139,6 +139,28 @@ int mixfe_gated_loudness(mixfe_plan* plan, const float* const stems[MIXFE_NUM_ST
 int mixfe_short_term_loudness_iqr(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                                   long long stride_b, long long stride_c, int B, int T, float* iqr, void* cuda_stream);
 
+/* EXTENSION (same status): the proposal's activity- and band-weighted inter-stem masking (PDF p.2 section 2.4; the
+ * reference implements only the un-weighted mean, src/mixing_utils.py:296-306):
+ *   M_i = sum_{k,t} a_i(t) A(k) sigmoid((beta - Delta_i(k,t)) / tau) / sum_{k,t} a_i(t) A(k),
+ *   Delta_i = S_i - max_{j != i} S_j on the channel-mean mel power S.  Choices the proposal leaves open: a_i(t) = E_i / (E_i + E_0)
+ * with E_i(t) the frame's mel energy and E_0 that of a -60 dBFS white-noise frame (0 under 1e-6 E_0); A(k) = band_weights[k] (device,
+ * n_mels floats; the Python layer passes the IEC 61672 A-weighting at the band centres), band_weight_sum their sum.
+ * logmel: device, the tensor mixfe_features_logmel wrote for the same clips (same addressing); out: device [B][4] fp32
+ * = vocals, bass, drums, other (0 for a stem that is never active).  beta = 0, tau = 1 are the reference's constants. */
+int mixfe_weighted_masking(mixfe_plan* plan, const float* logmel, long long logmel_stride_b, int B, int T,
+                           const float* band_weights, double band_weight_sum, float beta, float tau, float* out,
+                           void* cuda_stream);
+
+/* EXTENSION (same status): a compressor with an envelope follower, which the brief names and the reference does not have
+ * (its apply_compression is memoryless, src/mixing_utils.py:435-447).  Decoupled smooth peak detector (Giannoulis,
+ * Massberg, Reiss, JAES 2012): p[n] = max(|x[n]|, release_coeff p[n-1]); s[n] = attack_coeff s[n-1] + (1 - attack_coeff) p[n];
+ * the reference's static curve (threshold_db, ratio) is applied to the level of s and y[n] = x[n] gain(s[n]).  Coefficients
+ * are per sample, exp(-1 / (time_constant_seconds * sample_rate)), in [0, 1); both 0 gives the memoryless compressor.
+ * in/out: one tensor, element (b, c, t) at in[b*stride_b + c*stride_c + t]; every row is an independent detector. */
+int mixfe_envelope_compress(mixfe_plan* plan, const float* in, float* out, long long stride_b, long long stride_c,
+                            int B, int C, int T, float threshold_db, float ratio, float attack_coeff, float release_coeff,
+                            void* cuda_stream);
+
 /* Replaces ONE resolution of MultiResolutionSTFTLoss.forward (src/loss.py:332-448; the cycle loss of
  * src/train_style_transfer.py:239) and its autograd.  The plan's (n_fft, hop) is the resolution (win = n_fft, periodic
  * Hann, center=True, reflect).  x (prediction), y (target): device fp32, element (b, c, t) at
@@ -188,7 +210,8 @@ long long mixfe_launch_count(void);
 #define MIXFE_KERNEL_LOGMEL_BWD 4 /* K6: backward of the log-mel */
 #define MIXFE_KERNEL_LOUDNESS 5   /* K7: K-weighting scan + sub-block energies + gating */
 #define MIXFE_KERNEL_STFT_LOSS 6  /* K8: STFT-loss partials / finish / backward */
-#define MIXFE_NUM_KERNELS 7
+#define MIXFE_KERNEL_EXTENSION 7  /* K9 / K10: weighted masking, envelope-follower compressor */
+#define MIXFE_NUM_KERNELS 8
 int mixfe_plan_enable_timing(mixfe_plan* plan, int enable);
 int mixfe_plan_kernel_time(mixfe_plan* plan, int which, double* total_ms, long long* launches);
 

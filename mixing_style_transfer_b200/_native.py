@@ -79,7 +79,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
            "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
            "mixfe_stft_loss_forward", "mixfe_stft_loss_backward", "mixfe_plan_create_augment", "mixfe_effects",
-           "mixfe_reverb")
+           "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress")
 
 
 def lib() -> ctypes.CDLL:
@@ -117,6 +117,9 @@ def lib() -> ctypes.CDLL:
         L.mixfe_plan_create_augment.argtypes = [ctypes.POINTER(vp), ci, ci]
         L.mixfe_effects.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, ctypes.POINTER(AugParams), vp]
         L.mixfe_reverb.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, vp, ll, ci, vp]
+        L.mixfe_weighted_masking.argtypes = [vp, vp, ll, ci, ci, vp, ctypes.c_double, ctypes.c_float, ctypes.c_float, vp, vp]
+        L.mixfe_envelope_compress.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, ctypes.c_float, ctypes.c_float, ctypes.c_float,
+                                              ctypes.c_float, vp]
         L.mixfe_launch_count.restype = ll
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
@@ -129,6 +132,28 @@ def lib() -> ctypes.CDLL:
         L.mixfe_plan_kernel_time.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ll)]
         _lib = L
     return _lib
+
+
+# Tracing hook: MIXFE_NVTX=1 brackets every entry point of a Plan with an NVTX range
+# ("mixfe.features_logmel", "mixfe.augment", ...), so an nsys / ncu --nvtx timeline shows the front end's calls between the
+# caller's own ranges.  Off by default: the range push/pop is host work on the launch path.
+NVTX = os.environ.get("MIXFE_NVTX", "0") not in ("", "0")
+
+
+def _traced(fn):
+    if not NVTX:
+        return fn
+    import functools
+    name = "mixfe." + fn.__name__
+
+    @functools.wraps(fn)
+    def wrapper(*a, **k):
+        torch.cuda.nvtx.range_push(name)
+        try:
+            return fn(*a, **k)
+        finally:
+            torch.cuda.nvtx.range_pop()
+    return wrapper
 
 
 def launch_count() -> int:
@@ -243,6 +268,7 @@ class Plan:
         _check(lib().mixfe_debug_feature_kernel_config(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
         return {"ctas_per_sm": a.value, "smem_bytes": b.value, "mel_steps": c.value}
 
+    @_traced
     def features_logmel(self, stems: Sequence[torch.Tensor], want_features: bool = True,
                         want_logmel: bool = True, features_out: Optional[torch.Tensor] = None,
                         logmel_out: Optional[torch.Tensor] = None):
@@ -272,6 +298,7 @@ class Plan:
                                                0 if lm is None else lm.stride(0), _stream(self.device)))
         return feats, lm
 
+    @_traced
     def logmel_backward(self, stems: Sequence[torch.Tensor], grad_logmel: torch.Tensor) -> List[torch.Tensor]:
         """d loss / d stems (4 new (B,2,T) tensors) from d loss / d logmel (B,8,n_mels,F); the adjoint of the
         log-mel half of features_logmel (kernel K6)."""
@@ -299,6 +326,7 @@ class Plan:
             t = t.float()
         return t if t.stride(2) == 1 else t.contiguous()
 
+    @_traced
     def stft_loss_forward(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """One resolution (this plan's n_fft, hop) of the STFT loss on (B,C,T) CUDA tensors -> state (8 doubles on the
         device): [3] spectral convergence, [4] log-magnitude L1 (kernel K8)."""
@@ -310,6 +338,7 @@ class Plan:
                                                  y.stride(1), _ptr(state), _stream(self.device)))
         return state
 
+    @_traced
     def stft_loss_backward(self, x: torch.Tensor, y: torch.Tensor, state: torch.Tensor, grad_scale: torch.Tensor,
                            grad_x: torch.Tensor) -> None:
         """Adds grad_scale * d(sc + lm)/dx of this resolution into grad_x ((B,C,T) fp32, contiguous in T)."""
@@ -323,6 +352,7 @@ class Plan:
                                                   y.stride(1), _ptr(state), _ptr(grad_scale), _ptr(grad_x), grad_x.stride(0),
                                                   grad_x.stride(1), _stream(self.device)))
 
+    @_traced
     def gated_loudness(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
         """(B,5) BS.1770-4 integrated loudness [vocals, bass, drums, other, mixture] in LUFS (kernel K7; extension)."""
         st, sb, sc = unify_stems(stems)
@@ -333,6 +363,7 @@ class Plan:
             _check(lib().mixfe_gated_loudness(self._h, ptrs, sb, sc, B, T, _ptr(out), _stream(self.device)))
         return out
 
+    @_traced
     def short_term_loudness_iqr(self, stems: Sequence[torch.Tensor]) -> torch.Tensor:
         """(B,5) inter-quartile range of the short-term (3 s / 100 ms) K-weighted loudness in LU, same order (kernel K7;
         extension: the proposal's DR_IQR)."""
@@ -354,6 +385,7 @@ class Plan:
                                                _stream(self.device)))
         return out
 
+    @_traced
     def augment(self, stems: Sequence[torch.Tensor], params, impulse: Optional[torch.Tensor],
                 outs: Optional[Sequence[torch.Tensor]] = None):
         """stems: 4 CUDA tensors (B,2,T); params: ctypes array of B AugParams; impulse (B,L) or None.
@@ -385,6 +417,7 @@ class Plan:
                                        _stream(self.device)))
         return outs
 
+    @_traced
     def effects(self, x: torch.Tensor, params, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """x: CUDA (B,C,T); params: ctypes array of B AugParams whose stem index 0 holds the decisions (gain, tilt,
         compressor, band-limit) applied to every channel of clip b.  Returns a new tensor (or `out`)."""
@@ -407,6 +440,7 @@ class Plan:
                                        _stream(self.device)))
         return out
 
+    @_traced
     def reverb(self, x: torch.Tensor, impulse: torch.Tensor) -> torch.Tensor:
         """x: CUDA (B,C,T), C in {1, 2}; impulse (L,) shared by all clips or (B,L).  0.7 x + 0.3 corr(x, h) (kernel K4)."""
         if x.dtype != torch.float32:
@@ -427,7 +461,42 @@ class Plan:
                                       stride, L, _stream(self.device)))
         return out
 
-    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5, "stft_loss": 6}
+    @_traced
+    def weighted_masking(self, logmel: torch.Tensor, T: int, band_weights: torch.Tensor, beta: float, tau: float) -> torch.Tensor:
+        """(B,4) activity- and band-weighted masking from the log-mel tensor of the same clips (kernel K9; extension)."""
+        B = logmel.shape[0]
+        F = self.num_frames(T)
+        _check_out(logmel, (B, 8, self.n_mels, F), self.device, "logmel")
+        if logmel.stride(3) != 1 or logmel.stride(2) != F or logmel.stride(1) != self.n_mels * F:
+            logmel = logmel.contiguous()
+        bw = band_weights.to(self.device, torch.float32).contiguous()
+        if tuple(bw.shape) != (self.n_mels,):
+            raise ValueError(f"band_weights shape {tuple(bw.shape)}, expected ({self.n_mels},)")
+        out = torch.empty((B, 4), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_weighted_masking(self._h, _ptr(logmel), logmel.stride(0) if B else 0, B, T, _ptr(bw),
+                                                float(band_weights.double().sum()), float(beta), float(tau), _ptr(out),
+                                                _stream(self.device)))
+        return out
+
+    @_traced
+    def envelope_compress(self, x: torch.Tensor, threshold_db: float, ratio: float, attack_coeff: float,
+                          release_coeff: float) -> torch.Tensor:
+        """x: CUDA (B,C,T) -> envelope-follower compressor output (kernel K10; extension)."""
+        if x.dtype != torch.float32:
+            x = x.float()
+        if x.stride(2) != 1:
+            x = x.contiguous()
+        B, C, T = x.shape
+        out = torch.empty_strided(x.shape, x.stride(), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().mixfe_envelope_compress(self._h, _ptr(x), _ptr(out), x.stride(0), x.stride(1), B, C, T,
+                                                 float(threshold_db), float(ratio), float(attack_coeff), float(release_coeff),
+                                                 _stream(self.device)))
+        return out
+
+    KERNELS = {"features": 0, "finalize": 1, "augment": 2, "reverb": 3, "logmel_bwd": 4, "loudness": 5, "stft_loss": 6,
+               "extension": 7}
 
     def reserve_sms(self, n: int) -> None:
         """Leave n SMs out of K1's persistent grid (so a collective can run beside it); 0 = full grid."""

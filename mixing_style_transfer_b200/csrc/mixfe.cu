@@ -17,6 +17,7 @@
 #include "k4_reverb.cuh"
 #include "k7_loudness.cuh"
 #include "k8_mrstft.cuh"
+#include "k9_extensions.cuh"
 
 using namespace mixfe;
 
@@ -571,6 +572,64 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     return MIXFE_OK;
 }
 
+// EXTENSION: activity- and band-weighted masking from the log-mel tensor (k9_extensions.cuh)
+int run_weighted_masking(mixfe_plan* pl, const float* logmel, long long lm_stride_b, int B, int T, const float* band_weights,
+                         double band_weight_sum, float beta, float tau, float* out, cudaStream_t stream) {
+    if (!pl || !logmel || !band_weights || !out) return fail(MIXFE_EINVAL, "null plan, log-mel, band weights or output");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
+    if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
+    if (!(tau > 0.0f) || !(band_weight_sum > 0.0)) return fail(MIXFE_EINVAL, "tau and the band-weight sum must be positive");
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "weighted masking: B=%d > 65535 clips per call", B);
+    DeviceGuard guard(pl->device);
+    K9Params p{};
+    p.logmel = logmel; p.lm_stride_b = lm_stride_b; p.B = B; p.F = 1 + T / pl->hop; p.n_mels = pl->n_mels;
+    p.n_blocks = (p.F + kMaskThreads - 1) / kMaskThreads;
+    p.beta = beta; p.inv_tau = 1.0f / tau;
+    // E_0: mel energy of a -60 dBFS white-noise frame = sigma^2 * sum(hann^2) * n_freq, sum(hann^2) = 3 n_fft / 8
+    p.e0 = 1e-6f * (3.0f * (float)pl->n_fft / 8.0f) * (float)pl->n_freq;
+    p.aw = band_weights; p.aw_sum = band_weight_sum; p.out = out;
+    int rc = ensure_workspace(pl, sizeof(float) * 8 * (size_t)B * p.n_blocks, stream);
+    if (rc) return rc;
+    p.part = reinterpret_cast<float*>(pl->ws);
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_EXTENSION, stream);
+        k9_masking_partials<<<dim3(p.n_blocks, B), kMaskThreads, 0, stream>>>(p);
+        k9_masking_finish<<<B, 32, 0, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 2;
+    return MIXFE_OK;
+}
+
+// EXTENSION: envelope-follower compressor on one tensor (k9_extensions.cuh, K10)
+int run_envelope_compress(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                          int T, float threshold_db, float ratio, float attack_coeff, float release_coeff, cudaStream_t stream) {
+    if (!pl || !in || !out) return fail(MIXFE_EINVAL, "null argument");
+    if (in == out) return fail(MIXFE_EINVAL, "out must not alias in");
+    if (B < 0 || C <= 0 || T <= 0) return fail(MIXFE_EINVAL, "bad B, C or T");
+    if (!(ratio > 0.0f) || !std::isfinite(threshold_db)) return fail(MIXFE_EINVAL, "threshold %g dB, ratio %g", (double)threshold_db, (double)ratio);
+    if (!(attack_coeff >= 0.0f && attack_coeff < 1.0f && release_coeff >= 0.0f && release_coeff < 1.0f))
+        return fail(MIXFE_EINVAL, "attack / release coefficients must lie in [0, 1)");
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535 || C > 65535) return fail(MIXFE_EINVAL, "B or C > 65535 per call");
+    if ((C > 1 && stride_c < T) || (B > 1 && stride_b < T)) return fail(MIXFE_EINVAL, "strides smaller than T");
+    DeviceGuard guard(pl->device);
+    K10Params p{};
+    p.in = in; p.out = out; p.stride_b = stride_b; p.stride_c = stride_c; p.B = B; p.C = C; p.T = T;
+    p.a_rel = release_coeff; p.a_att = attack_coeff;
+    float c1;
+    compressor_constants(threshold_db, ratio, p.knee, p.c0, c1);
+    p.c1m1 = c1 - 1.0f;                                  // gain = compressed magnitude / a
+    {
+        KernelTimer timer(pl, MIXFE_KERNEL_EXTENSION, stream);
+        k10_envelope_compress<<<dim3(C, B), kEnvWarps * 32, 0, stream>>>(p);
+    }
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter()++;
+    return MIXFE_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -770,6 +829,19 @@ int mixfe_augment(mixfe_plan* pl, const float* const in[MIXFE_NUM_STEMS], float*
                   const float* impulse, int L, void* cuda_stream) {
     return run_augment(pl, in, out, stride_b, stride_c, B, T, params, impulse, L,
                        static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_weighted_masking(mixfe_plan* pl, const float* logmel, long long logmel_stride_b, int B, int T,
+                           const float* band_weights, double band_weight_sum, float beta, float tau, float* out,
+                           void* cuda_stream) {
+    return run_weighted_masking(pl, logmel, logmel_stride_b, B, T, band_weights, band_weight_sum, beta, tau, out,
+                                static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mixfe_envelope_compress(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
+                            int T, float threshold_db, float ratio, float attack_coeff, float release_coeff, void* cuda_stream) {
+    return run_envelope_compress(pl, in, out, stride_b, stride_c, B, C, T, threshold_db, ratio, attack_coeff, release_coeff,
+                                 static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_effects(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,

@@ -142,6 +142,33 @@ class MixingFeatureExtractor:
             out = out[0]
         return out if out.device == src_device else out.to(src_device)
 
+    def band_weights(self) -> torch.Tensor:
+        """(n_mels,) IEC 61672 A-weighting as a power ratio, normalised to its maximum, at the centre frequency of every
+        mel band (HTK scale, f_min = 0, f_max = sr // 2): the A(k) of weighted_masking."""
+        top = 2595.0 * math.log10(1.0 + float(self.sr // 2) / 700.0)
+        mel = torch.linspace(0.0, top, self.n_mels + 2, dtype=torch.float64)[1:-1]
+        f2 = (700.0 * (10.0 ** (mel / 2595.0) - 1.0)) ** 2
+        ra = (12194.0 ** 2 * f2 ** 2) / ((f2 + 20.6 ** 2) * torch.sqrt((f2 + 107.7 ** 2) * (f2 + 737.9 ** 2)) * (f2 + 12194.0 ** 2))
+        w = ra ** 2
+        return (w / w.max()).float()
+
+    def weighted_masking(self, stems_dict, beta=0.0, tau=1.0):
+        """EXTENSION (not in the reference's code; its proposal, p.2 section 2.4): activity- and band-weighted inter-stem
+        masking M_i = sum a_i(t) A(k) sigmoid((beta - Delta_i(k,t)) / tau) / sum a_i(t) A(k), (4,) or (B,4) in the order
+        vocals, bass, drums, other.  a_i(t): soft activity gate of the frame's mel energy at the level of -60 dBFS white
+        noise; A(k): band_weights().  beta = 0, tau = 1 are the constants of the reference's un-weighted feature
+        (src/mixing_utils.py:300-301), which stays what the 64-vector holds."""
+        first = stems_dict[STEMS[0]]
+        src_device = first.device
+        device = _resolve_device(first, self._device)
+        stems, batched = _gather_stems(stems_dict, device)
+        plan = self._plan(device)
+        _, lm = plan.features_logmel(stems, False, True)
+        out = plan.weighted_masking(lm, stems[0].shape[-1], self.band_weights(), beta, tau)
+        if not batched:
+            out = out[0]
+        return out if out.device == src_device else out.to(src_device)
+
     def feature_names(self) -> List[str]:
         """Names of the D entries in the reference's sorted-key order (src/mixing_utils.py:320-357)."""
         if self.use_detailed_spectral:
@@ -537,6 +564,17 @@ class AudioAugmenter:
             for j in range(12):
                 p.bw_sos[0][j] = sos[j // 6][j % 6]
         return self._effect(audio, fill)
+
+    def apply_envelope_compression(self, audio, threshold=-20, ratio=4, attack_ms=5.0, release_ms=50.0):
+        """EXTENSION (not in the reference, whose compressor is memoryless, :435-447): the same static curve driven by an
+        envelope follower -- instant-attack / exponential-release peak detector followed by a one-pole attack smoother
+        (decoupled smooth peak detector, Giannoulis et al., JAES 2012), time constants in milliseconds; both 0 gives
+        apply_compression.  One (C,T) tensor or a (B,C,T) batch; every row has its own detector."""
+        if not ratio > 0:
+            raise ValueError(f"ratio must be positive, got {ratio}")
+        coeff = [math.exp(-1.0 / (ms * 1e-3 * self.sr)) if ms > 0 else 0.0 for ms in (attack_ms, release_ms)]
+        x, batched, src, device = self._one(audio)
+        return self._finish(self._plan(device).envelope_compress(x, threshold, ratio, coeff[0], coeff[1]), batched, src)
 
     def apply_reverb(self, audio, decay=0.5, impulse: Optional[torch.Tensor] = None):
         """:458-479 -- 0.7 * audio + 0.3 * conv1d(audio, impulse, padding=L//2)[:, :T] per channel, with
