@@ -111,13 +111,16 @@ int mixfe_reverb(mixfe_plan* plan, const float* in, float* out, long long stride
                  int B, int C, int T, const float* impulse, long long impulse_stride_b, int L, void* cuda_stream);
 
 /* Replaces autograd through MelSpectrogramPreprocessor.forward (src/model.py:41-67), the path the style-transfer
- * loop differentiates (src/train_style_transfer.py:206-215): given d loss / d logmel, ADDS d loss / d stems into
- * grad_stems (which the caller zero-initialises).  stems: the forward inputs, addressed as in
- * mixfe_features_logmel; grad_logmel: device, same addressing as `logmel` there; grad_stems[s]: device, element
- * (b, c, t) at grad_stems[s][b*grad_stride_b + c*grad_stride_c + t].  The spectrum is recomputed; nothing is
- * saved by the forward.  Returns MIXFE_ESHORT when T <= n_fft/2. */
+ * loop differentiates (src/train_style_transfer.py:206-215): given d loss / d logmel, WRITES d loss / d stems into
+ * grad_stems (every sample of the T-long rows is overwritten; no initialisation needed).  stems: the forward inputs,
+ * addressed as in mixfe_features_logmel; logmel: the tensor the forward wrote for them (same addressing as there) or
+ * NULL -- with it, the (1024, 256) configuration runs the fast kernel K6F (dmel = g exp(-logmel), no mel recomputation,
+ * every gradient sample written once); without it, or for any other configuration, the generic kernel K6 recomputes
+ * the mel spectrum; grad_logmel: device, same addressing as logmel; grad_stems[s]: device, element (b, c, t) at
+ * grad_stems[s][b*grad_stride_b + c*grad_stride_c + t].  Returns MIXFE_ESHORT when T <= n_fft/2. */
 int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],
                           long long stride_b, long long stride_c, int B, int T,
+                          const float* logmel, long long logmel_stride_b,
                           const float* grad_logmel, long long grad_logmel_stride_b,
                           float* const grad_stems[MIXFE_NUM_STEMS], long long grad_stride_b,
                           long long grad_stride_c, void* cuda_stream);

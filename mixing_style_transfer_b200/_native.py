@@ -111,7 +111,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_workspace_bytes.restype = ctypes.c_size_t
         L.mixfe_features_logmel.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp, ll, vp]
         L.mixfe_debug_mel_power.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, vp]
-        L.mixfe_logmel_backward.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, ctypes.POINTER(vp), ll, ll, vp]
+        L.mixfe_logmel_backward.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, ll, vp, ll, ctypes.POINTER(vp), ll, ll, vp]
         L.mixfe_augment.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ll, ll, ci, ci,
                                     ctypes.POINTER(AugParams), vp, ci, vp]
         L.mixfe_plan_create_augment.argtypes = [ctypes.POINTER(vp), ci, ci]
@@ -299,25 +299,32 @@ class Plan:
         return feats, lm
 
     @_traced
-    def logmel_backward(self, stems: Sequence[torch.Tensor], grad_logmel: torch.Tensor) -> List[torch.Tensor]:
-        """d loss / d stems (4 new (B,2,T) tensors) from d loss / d logmel (B,8,n_mels,F); the adjoint of the
-        log-mel half of features_logmel (kernel K6)."""
+    def logmel_backward(self, stems: Sequence[torch.Tensor], grad_logmel: torch.Tensor,
+                        logmel: Optional[torch.Tensor] = None) -> List[torch.Tensor]:
+        """d loss / d stems (4 new (B,2,T) tensors) from d loss / d logmel (B,8,n_mels,F); the adjoint of the log-mel half
+        of features_logmel.  `logmel`: the forward's output for the same stems -- with it the (1024, 256) configuration
+        runs K6F (one write per gradient sample, no mel recomputation), else the generic K6."""
         st, sb, sc = unify_stems(stems)
         B, _, T = st[0].shape
         F = self.num_frames(T)
-        g = grad_logmel
-        if g.dtype != torch.float32 or g.device != self.device:
-            g = g.to(device=self.device, dtype=torch.float32)
-        if tuple(g.shape) != (B, 8, self.n_mels, F):
-            raise ValueError(f"grad_logmel shape {tuple(g.shape)}, expected {(B, 8, self.n_mels, F)}")
-        if g.stride(3) != 1 or g.stride(2) != F or g.stride(1) != self.n_mels * F:
-            g = g.contiguous()
-        outs = [torch.zeros((B, 2, T), dtype=torch.float32, device=self.device) for _ in range(4)]
+
+        def dense(x, name):
+            if x.dtype != torch.float32 or x.device != self.device:
+                x = x.to(device=self.device, dtype=torch.float32)
+            if tuple(x.shape) != (B, 8, self.n_mels, F):
+                raise ValueError(f"{name} shape {tuple(x.shape)}, expected {(B, 8, self.n_mels, F)}")
+            if x.stride(3) != 1 or x.stride(2) != F or x.stride(1) != self.n_mels * F:
+                x = x.contiguous()
+            return x
+        g = dense(grad_logmel, "grad_logmel")
+        lm = dense(logmel, "logmel") if logmel is not None else None
+        outs = [torch.empty((B, 2, T), dtype=torch.float32, device=self.device) for _ in range(4)]
         ptrs = (ctypes.c_void_p * 4)(*[s.data_ptr() for s in st])
         optrs = (ctypes.c_void_p * 4)(*[o.data_ptr() for o in outs])
         with torch.cuda.device(self.device):
-            _check(lib().mixfe_logmel_backward(self._h, ptrs, sb, sc, B, T, _ptr(g), g.stride(0), optrs,
-                                               outs[0].stride(0), outs[0].stride(1), _stream(self.device)))
+            _check(lib().mixfe_logmel_backward(self._h, ptrs, sb, sc, B, T, _ptr(lm), 0 if lm is None else lm.stride(0),
+                                               _ptr(g), g.stride(0), optrs, outs[0].stride(0), outs[0].stride(1),
+                                               _stream(self.device)))
         return outs
 
     @staticmethod

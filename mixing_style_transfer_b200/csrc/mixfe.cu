@@ -12,6 +12,7 @@
 #include "k1_features.cuh"
 #include "k1g_features.cuh"
 #include "k6_logmel_bwd.cuh"
+#include "k6f_logmel_bwd.cuh"
 #include "plan.cuh"
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
@@ -34,6 +35,12 @@ int upload(T** dst, const std::vector<T>& v) {
 }
 
 inline int align16(int x) { return (x + 15) & ~15; }
+
+inline float __int_as_float_host(int v) {
+    float f;
+    std::memcpy(&f, &v, sizeof f);
+    return f;
+}
 
 // torchaudio.functional.melscale_fbanks(n_freqs, 0, sr//2, n_mels, sr, norm=None, mel_scale='htk')
 // evaluated in double precision (the Python layer can override it with the exact fp32 matrix).
@@ -174,6 +181,36 @@ int build_mel_tables(mixfe_plan* pl) {
     int per_sm = 0;
     MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_features, kK1Threads, pl->smem_k1));
     pl->k1_ctas = std::max(1, per_sm) * pl->n_sms;
+    // K6F (backward on the one-warp transform): hop 256 and at most two ADJACENT filters per bin (any triangular bank)
+    if (pl->d_binw) { cudaFree(pl->d_binw); pl->d_binw = nullptr; }
+    if (pl->hop == 256) {
+        std::vector<float4> binw(nf);
+        bool ok = true;
+        for (int k = 0; k < nf && ok; ++k) {
+            int first = -1, last = -1;
+            for (int m = 0; m < nm; ++m)
+                if (w(k, m) != 0.0f) { if (first < 0) first = m; last = m; }
+            if (first < 0) { first = last = 0; }
+            if (last - first > 1) { ok = false; break; }
+            float4 e;
+            e.x = __int_as_float_host(first);
+            e.y = w(k, first);
+            e.z = last > first ? w(k, last) : 0.0f;
+            e.w = 0.0f;
+            binw[k] = e;
+        }
+        if (ok) {
+            if ((rc = upload(&pl->d_binw, binw))) return rc;
+            pl->f_off_ex = 0;
+            pl->f_off_tw = kBwWarps * kWarpRegion;
+            pl->f_off_binw = pl->f_off_tw + 31 * 32 * 8;
+            pl->f_off_dmel = align16(pl->f_off_binw + nf * 16);
+            pl->f_off_ola = align16(pl->f_off_dmel + kBwWarps * (nm + 1) * 8);
+            pl->smem_f = pl->f_off_ola + kBwSpan * 8;
+            if (pl->smem_f > 227 * 1024) { cudaFree(pl->d_binw); pl->d_binw = nullptr; }
+            else if ((rc = smem_optin(k6f_logmel_bwd, pl->device, pl->smem_f))) return rc;
+        }
+    }
     return MIXFE_OK;
 }
 
@@ -392,8 +429,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
 }
 
 int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long stride_b, long long stride_c, int B, int T,
-                        const float* grad_logmel, long long g_stride_b, float* const grad_stems[4], long long ostride_b,
-                        long long ostride_c, cudaStream_t stream) {
+                        const float* logmel, long long lm_stride_b, const float* grad_logmel, long long g_stride_b,
+                        float* const grad_stems[4], long long ostride_b, long long ostride_c, cudaStream_t stream) {
     if (!pl || !stems || !grad_stems || !grad_logmel) return fail(MIXFE_EINVAL, "null plan, stems or gradients");
     if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
     for (int s = 0; s < 4; ++s)
@@ -406,14 +443,47 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
                     pl->n_fft / 2, pl->n_fft / 2, T);
     if (stride_c < T || (B > 1 && stride_b < T) || ostride_c < T || (B > 1 && ostride_b < T))
         return fail(MIXFE_EINVAL, "strides smaller than T");
-    if (!pl->smem_b) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: hop=%d needs more shared memory than an SM has", pl->hop);
-    if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: B=%d > 65535 clips per call", B);
+    if (B > 32767) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: B=%d > 32767 clips per call", B);
     DeviceGuard guard(pl->device);
+    const int F = 1 + T / pl->hop;
+    const char* force = getenv("MIXFE_FORCE_GENERIC_BWD");
+    if (logmel && pl->d_binw && !pl->use_generic && !(force && atoi(force))) {
+        // K6F: every sample written once; only the reflect-fold strips at the row ends are zeroed and take atomics
+        K6FParams p{};
+        for (int s = 0; s < 4; ++s) { p.stem[s] = stems[s]; p.out[s] = grad_stems[s]; }
+        p.stride_b = stride_b; p.stride_c = stride_c; p.ostride_b = ostride_b; p.ostride_c = ostride_c;
+        p.g = grad_logmel; p.g_stride_b = g_stride_b; p.lm = logmel; p.lm_stride_b = lm_stride_b;
+        p.B = B; p.T = T; p.F = F; p.n_mels = pl->n_mels;
+        const int hlast = (T + 511) / 256;                           // last hop region the padded signal reaches
+        p.n_tiles = (hlast + 3 + kBwOwn - 1) / kBwOwn;
+        p.tw = pl->d_tw; p.binw = pl->d_binw;
+        p.off_ex = pl->f_off_ex; p.off_tw = pl->f_off_tw; p.off_binw = pl->f_off_binw; p.off_dmel = pl->f_off_dmel;
+        p.off_ola = pl->f_off_ola;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_LOGMEL_BWD, stream);
+            k6f_zero_edges<<<dim3(2 * B, kNumStems), 128, 0, stream>>>(p);
+            k6f_logmel_bwd<<<dim3(p.n_tiles, B, kNumStems), kBwThreads, pl->smem_f, stream>>>(p);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter() += 2;
+        return MIXFE_OK;
+    }
+    if (!pl->smem_b) return fail(MIXFE_EUNSUPPORTED, "log-mel backward: hop=%d needs more shared memory than an SM has", pl->hop);
+    // generic path: overlap-add across tiles with atomicAdd into zeroed gradients
+    for (int s = 0; s < 4; ++s) {
+        if (B == 1 || ostride_b == 2 * ostride_c) {            // rows evenly spaced: one 2-D memset per stem
+            MIXFE_CUDA(cudaMemset2DAsync(grad_stems[s], sizeof(float) * ostride_c, 0, sizeof(float) * T, 2 * (size_t)B, stream));
+        } else {
+            for (int b = 0; b < B; ++b)
+                MIXFE_CUDA(cudaMemset2DAsync(grad_stems[s] + (long long)b * ostride_b, sizeof(float) * ostride_c, 0,
+                                             sizeof(float) * T, 2, stream));
+        }
+    }
     K6Params p{};
     for (int s = 0; s < 4; ++s) { p.stem[s] = stems[s]; p.out[s] = grad_stems[s]; }
     p.stride_b = stride_b; p.stride_c = stride_c; p.ostride_b = ostride_b; p.ostride_c = ostride_c;
     p.g = grad_logmel; p.g_stride_b = g_stride_b;
-    p.B = B; p.T = T; p.F = 1 + T / pl->hop; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
+    p.B = B; p.T = T; p.F = F; p.hop = pl->hop; p.n_mels = pl->n_mels; p.n_mels_pad = pl->n_mels_pad;
     p.n_fft = pl->n_fft; p.log2n = pl->g_log2n; p.nf = pl->b_nf; p.span = pl->b_span; p.span_pad = pl->b_span_pad;
     p.twg = pl->d_twg; p.win = pl->d_win;
     p.mel_meta = pl->d_mel_meta; p.mel_w = pl->d_mel_w;
@@ -703,7 +773,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
-    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w);
+    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;
@@ -786,11 +856,13 @@ int mixfe_features_logmel(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STE
 }
 
 int mixfe_logmel_backward(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b,
-                          long long stride_c, int B, int T, const float* grad_logmel, long long grad_logmel_stride_b,
+                          long long stride_c, int B, int T, const float* logmel, long long logmel_stride_b,
+                          const float* grad_logmel, long long grad_logmel_stride_b,
                           float* const grad_stems[MIXFE_NUM_STEMS], long long grad_stride_b, long long grad_stride_c,
                           void* cuda_stream) {
-    return run_logmel_backward(pl, stems, stride_b, stride_c, B, T, grad_logmel, grad_logmel_stride_b, grad_stems,
-                               grad_stride_b, grad_stride_c, static_cast<cudaStream_t>(cuda_stream));
+    return run_logmel_backward(pl, stems, stride_b, stride_c, B, T, logmel, logmel_stride_b, grad_logmel,
+                               grad_logmel_stride_b, grad_stems, grad_stride_b, grad_stride_c,
+                               static_cast<cudaStream_t>(cuda_stream));
 }
 
 int mixfe_gated_loudness(mixfe_plan* pl, const float* const stems[MIXFE_NUM_STEMS], long long stride_b, long long stride_c,

@@ -30,6 +30,8 @@ struct mixfe_plan {
     float* d_mel_w = nullptr;
     int4* d_bin_meta = nullptr;         // CSR of the transposed filterbank (K6): (first filter, filters, weight offset, -) per bin
     float* d_bin_w = nullptr;
+    float4* d_binw = nullptr;           // K6F: per bin (first filter, its weight, the next filter's weight, -); null = K6F not usable
+    int f_off_ex = 0, f_off_tw = 0, f_off_binw = 0, f_off_dmel = 0, f_off_ola = 0, smem_f = 0;      // K6F shared-memory map
     int b_nf = 0, b_span = 0, b_span_pad = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)
     int g_nf = 0, g_log2n = 0, g_pw_stride = 0, g_off_pw = 0, g_off_mel = 0, g_off_S = 0, g_off_red = 0, smem_g = 0;
     // plan-owned workspace (grows to the high-water mark, then never reallocates)

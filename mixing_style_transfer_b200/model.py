@@ -79,7 +79,7 @@ class MelSpectrogramPreprocessor(nn.Module):
 
 
 class _LogMelFunction(torch.autograd.Function):
-    """log-mel with a hand-written backward (kernel K6); the forward saves only its inputs."""
+    """log-mel with a hand-written backward (kernels K6F / K6); the forward saves its inputs and its output."""
 
     @staticmethod
     def forward(ctx, plan, device, *stems):
@@ -87,12 +87,13 @@ class _LogMelFunction(torch.autograd.Function):
         _, lm = plan.features_logmel(gathered, want_features=False, want_logmel=True)
         ctx.plan = plan
         ctx.meta = [(x.dim(), x.device, x.dtype) for x in stems]
-        ctx.save_for_backward(*gathered)
+        ctx.save_for_backward(*gathered, lm)         # the output too: dmel = g * exp(-logmel), no mel recomputation (K6F)
         return lm
 
     @staticmethod
     def backward(ctx, grad_logmel):
-        grads = ctx.plan.logmel_backward(list(ctx.saved_tensors), grad_logmel)
+        *saved, lm = ctx.saved_tensors
+        grads = ctx.plan.logmel_backward(list(saved), grad_logmel, logmel=lm)
         out = []
         for g, (dim, dev, dt), need in zip(grads, ctx.meta, ctx.needs_input_grad[2:]):
             if not need:

@@ -31,8 +31,10 @@ for cfg in ((1024, 256, 128), (2048, 512, 80)):
     print(f"  features+logmel: {timed(lambda: plan.features_logmel(stems, True, True)):.3f} ms")
     print(f"  logmel only:     {timed(lambda: plan.features_logmel(stems, False, True)):.3f} ms")
     gl = torch.randn(B, 8, cfg[2], F, device=dev, generator=g)
-    plan.enable_timing(True)
-    total = timed(lambda: plan.logmel_backward(stems, gl))
-    ms, n = plan.kernel_time("logmel_bwd")
-    plan.enable_timing(False)
-    print(f"  logmel backward: kernel {ms / n:.3f} ms, with the zero-fill of the 4 gradient tensors {total:.3f} ms")
+    _, lm = plan.features_logmel(stems, False, True)
+    for label, kw in (("generic K6 (no forward output)", {}), ("with the forward's log-mel (K6F at 1024/256)", {"logmel": lm})):
+        plan.enable_timing(True)
+        total = timed(lambda: plan.logmel_backward(stems, gl, **kw))
+        ms, n = plan.kernel_time("logmel_bwd")
+        plan.enable_timing(False)
+        print(f"  logmel backward, {label}: kernels {ms / n:.3f} ms, call incl. allocation {total:.3f} ms")

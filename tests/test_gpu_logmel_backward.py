@@ -47,7 +47,8 @@ def test_backward_matches_autograd_through_oracle(cuda_device, n_fft, hop, n_mel
     lm = pre(leaves)
     assert lm.requires_grad
     (lm * gout.to(cuda_device)).sum().backward()
-    assert pkg.launch_count() == n0 + 2                          # forward kernel + K6
+    fast = (n_fft, hop) == (1024, 256)                           # K6F: edge-strip zeroing + the backward kernel
+    assert pkg.launch_count() == n0 + (3 if fast else 2)         # forward kernel + K6F / K6
     for n in O.STEMS:
         got = leaves[n].grad[0].cpu().double()
         assert got.shape == ref64[n].shape
@@ -99,3 +100,41 @@ def test_batched_backward_equals_per_clip(cuda_device):
         for n in O.STEMS:
             d = float((batch[n].grad[i] - one[n].grad[0]).abs().max())
             assert d <= 1e-6 * float(one[n].grad.abs().max())     # atomics: order-dependent only at the clip edges
+
+
+@pytest.mark.parametrize("T", [513, 700, 1025, 1536, 3327, 3328, 3329, 6655, 20000, 44100 + 17])
+def test_fast_backward_lengths_and_generic_agreement(cuda_device, T):
+    """K6F (1024/256, with the forward's log-mel) against the generic K6 on the same inputs, over clip lengths around
+    its tiling (13 hop regions = 3328 samples per CTA) and the reflect-fold strips (513 samples at each end), and
+    bitwise run-to-run determinism (every sample is written once; the strips take two commutative adds)."""
+    clip = _noisy_clip(T, T)
+    stems = [clip[n][None].to(cuda_device) for n in O.STEMS]
+    plan = pkg.MelSpectrogramPreprocessor()._plan(cuda_device)
+    _, lm = plan.features_logmel(stems, False, True)
+    g = torch.randn(lm.shape, generator=torch.Generator().manual_seed(T)).to(cuda_device)
+    slow = plan.logmel_backward(stems, g)
+    fast = plan.logmel_backward(stems, g, logmel=lm)
+    again = plan.logmel_backward(stems, g, logmel=lm)
+    for a, b_, c in zip(slow, fast, again):
+        scale = float(a.abs().max())
+        assert float((a - b_).abs().max()) <= 2e-4 * scale, (T, float((a - b_).abs().max()), scale)
+        assert torch.equal(b_, c)
+
+
+def test_fast_backward_batched_and_strided(cuda_device):
+    T = 9000
+    clips = [_noisy_clip(70 + i, T) for i in range(3)]
+    wide = torch.zeros(3, 8, T + 6, device=cuda_device)
+    for i, c in enumerate(clips):
+        for k, n in enumerate(O.STEMS):
+            wide[i, 2 * k:2 * k + 2, 2:2 + T] = c[n].to(cuda_device)
+    views = [wide[:, 2 * k:2 * k + 2, 2:2 + T] for k in range(4)]
+    plan = pkg.MelSpectrogramPreprocessor()._plan(cuda_device)
+    _, lm = plan.features_logmel(views, False, True)
+    g = torch.randn(lm.shape, generator=torch.Generator().manual_seed(1)).to(cuda_device)
+    fast = plan.logmel_backward(views, g, logmel=lm)
+    for i in range(3):
+        one = [v[i:i + 1].contiguous() for v in views]
+        ref = plan.logmel_backward(one, g[i:i + 1], logmel=lm[i:i + 1])
+        for a, b_ in zip(fast, ref):
+            assert torch.equal(a[i:i + 1], b_)
