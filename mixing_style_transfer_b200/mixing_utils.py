@@ -96,6 +96,7 @@ class MixingFeatureExtractor:
         self._device = torch.device(device) if device is not None else None
         self._fb = htk_mel_filterbank(sample_rate, n_fft, n_mels)
         self._plans: Dict[int, Plan] = {}
+        self._plans2: Dict[tuple, Plan] = {}          # plans of `second` configurations (features_and_logmel)
 
     # -- reference API ---------------------------------------------------------------------
     def get_feature_dim(self):
@@ -109,10 +110,49 @@ class MixingFeatureExtractor:
         return feats
 
     # -- additive API ----------------------------------------------------------------------
-    def features_and_logmel(self, stems_dict):
+    def features_and_logmel(self, stems_dict, second=None, chunk_clips: int = 4):
         """One fused pass: (features (D,)|(B,D), logmel (B,8,n_mels,F)) -- the encoder's
-        MelSpectrogramPreprocessor output (src/model.py:41-67) for the same (n_fft, hop, n_mels)."""
-        return self._run(stems_dict, True, True)
+        MelSpectrogramPreprocessor output (src/model.py:41-67) for the same (n_fft, hop, n_mels).
+
+        second = (n_fft2, hop2, n_mels2): ALSO the log-mel of a second STFT configuration -- the reference trains its
+        encoder on (2048, 512, 80) while the extractor keeps its own triple (src/train_style_transfer.py:523-533,
+        scripts/train_baseline.sh:42-44) -- from ONE read of the audio out of HBM: the batch is walked in chunks of
+        `chunk_clips` clips (56 MB of 10 s audio at the default, well inside the 126 MB L2) and the second
+        configuration's kernel runs on each chunk right behind the first one's, so its loads hit L2.  Returns
+        (features, logmel, logmel2 (B,8,n_mels2,F2)).  (Two kernels sharing the samples through L2, not one kernel
+        sharing them through shared memory; DESIGN.md section 4, K1G, says what that would take.)"""
+        if second is None:
+            return self._run(stems_dict, True, True)
+        first = stems_dict[STEMS[0]]
+        src_device = first.device
+        device = _resolve_device(first, self._device)
+        stems, batched = _gather_stems(stems_dict, device)
+        B, _, T = stems[0].shape
+        plan, plan2 = self._plan(device), self._second_plan(device, tuple(int(v) for v in second))
+        feats = torch.empty((B, plan.feature_dim), dtype=torch.float32, device=device)
+        lm = torch.empty((B, 8, plan.n_mels, plan.num_frames(T)), dtype=torch.float32, device=device)
+        lm2 = torch.empty((B, 8, plan2.n_mels, plan2.num_frames(T)), dtype=torch.float32, device=device)
+        step = max(1, int(chunk_clips))
+        for lo in range(0, B, step):
+            hi = min(B, lo + step)
+            part = [x[lo:hi] for x in stems]
+            plan.features_logmel(part, True, True, features_out=feats[lo:hi], logmel_out=lm[lo:hi])
+            plan2.features_logmel(part, False, True, logmel_out=lm2[lo:hi])
+        if not batched:
+            feats = feats[0]
+        if src_device != device:
+            feats, lm, lm2 = feats.to(src_device), lm.to(src_device), lm2.to(src_device)
+        return feats, lm, lm2
+
+    def _second_plan(self, device: torch.device, cfg) -> Plan:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        key = (idx,) + tuple(cfg)
+        pl = self._plans2.get(key)
+        if pl is None:
+            n_fft2, hop2, n_mels2 = cfg
+            pl = self._plans2[key] = Plan(torch.device("cuda", idx), self.sr, n_fft2, hop2, n_mels2, 0,
+                                          fb=htk_mel_filterbank(self.sr, n_fft2, n_mels2))
+        return pl
 
     def gated_loudness(self, stems_dict):
         """EXTENSION (not in the reference): ITU-R BS.1770-4 integrated loudness --

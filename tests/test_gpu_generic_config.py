@@ -143,3 +143,27 @@ def test_detailed_spectral_mode_on_other_configurations(cuda_device, n_fft, hop,
     assert fe.get_feature_dim() == cfg.feature_dim
     got = fe.extract_all_features(_to(clip, cuda_device))
     assert_features_close(got, O.mixing_features(clip, cfg), fe.feature_names(), f"{n_fft}/{hop}/{n_mels} detailed {nb}")
+
+
+def test_second_configuration_from_one_read_of_the_audio(cuda_device):
+    """features_and_logmel(..., second=(2048, 512, 80)): the extractor's own configuration plus the frozen encoder's,
+    chunked so that the second kernel reads the samples out of L2.  Same numbers as two
+    separate calls, bit for bit, and the reference's golden log-mel of the second configuration."""
+    import numpy as np
+    from tests._util import golden
+    G = golden()
+    clips = [O.musical_clip(4, 20000)] + [O.musical_clip(90 + i, 20000) for i in range(4)]
+    batch = {n: torch.stack([c[n] for c in clips]).to(cuda_device) for n in O.STEMS}
+    fe = pkg.MixingFeatureExtractor()
+    f, lm, lm2 = fe.features_and_logmel(batch, second=(2048, 512, 80), chunk_clips=2)
+    f0, lm0 = fe.features_and_logmel(batch)
+    assert torch.equal(f, f0) and torch.equal(lm, lm0)
+    sep = pkg.MelSpectrogramPreprocessor(44100, 2048, 512, 80)(batch)
+    assert lm2.shape == sep.shape == (5, 8, 80, 1 + 20000 // 512) and torch.equal(lm2, sep)
+    ref_sub = torch.from_numpy(G["logmel_2048_512_80/musical_clip/4/20000/sub"])
+    d = (lm2[0:1, :, ::2, ::4].cpu() - ref_sub).abs()
+    assert float(d.mean()) < 2e-5
+    cfg = O.FrontEndConfig(n_fft=2048, hop_length=512, n_mels=80)
+    assert_logmel_close(lm2[0:1], O.log_mel({n: v[None] for n, v in clips[0].items()}, cfg, dtype=torch.float64), "second config")
+    one = fe.features_and_logmel({n: v.to(cuda_device) for n, v in clips[1].items()}, second=(2048, 512, 80))
+    assert one[0].shape == (64,) and torch.equal(one[0], f[1]) and torch.equal(one[2][0], lm2[1])
