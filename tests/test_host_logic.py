@@ -128,3 +128,65 @@ def test_host_fft_kernel_math():
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "host", "test_fft32.cpp")])
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0 and "OK" in out.stdout, out.stdout + out.stderr
+
+
+def test_draw_batch_packs_what_per_clip_packing_packs():
+    """draw_batch's vectorised decisions + numpy packing against the per-clip path (ClipAugmentation + _pack) fed with
+    the same decisions: identical mixfe_aug_params, byte for byte (the vectorised butter_sos_batch included)."""
+    import numpy as np
+    aug = pkg.AudioAugmenter(prob=0.5)
+    torch.manual_seed(7)
+    batch = aug.draw_batch(16)
+    assert len(batch) == 16 and batch.impulse is not None and batch.impulse.shape == (16, 22050)
+    a = batch.arrays
+    clips = []
+    for b in range(16):
+        d = pkg.ClipAugmentation()
+        for s, n in enumerate(pkg.STEMS):
+            d.gain_db[n] = torch.tensor([a["gain_db"][b, s]]) if a["gain_on"][b, s] else None
+            d.tilt[n] = ("high" if a["tilt_high"][b, s] else "low") if a["tilt_on"][b, s] else None
+            d.compress[n] = bool(a["comp_on"][b, s])
+            d.cutoff_hz[n] = float(a["cutoff_hz"][b, s]) if a["bw_on"][b, s] else None
+        d.impulse = batch.impulse[b] if a["reverb_on"][b] else None
+        clips.append(d)
+    ref = aug._pack(clips)
+    assert ctypes.sizeof(batch.params) == ctypes.sizeof(ref)
+    g = np.frombuffer(batch.params, dtype=_aug_dtype_for_test())
+    w = np.frombuffer(ref, dtype=_aug_dtype_for_test())
+    for name in g.dtype.names:
+        if name == "_pad":
+            continue
+        if name == "gain_lin":                       # 10 ** (g / 20) on a vector vs on (1,) tensors: same fp32 kernel
+            assert np.allclose(g[name], w[name], rtol=2e-7, atol=0), name
+        elif name == "bw_sos":                       # numpy's vectorised complex arithmetic vs cmath: last-bit differences
+            assert np.allclose(g[name], w[name], rtol=1e-13, atol=1e-16), name
+        else:
+            assert np.array_equal(g[name], w[name]), name
+    # gates follow prob: about half of the 16 * 4 * 4 stem gates and of the 16 reverb gates fire
+    fired = sum(int(a[k].sum()) for k in ("gain_on", "tilt_on", "comp_on", "bw_on"))
+    assert 80 < fired < 176
+    # a slice is a view of the same packed parameters
+    sl = batch.slice(4, 9)
+    assert len(sl) == 5 and sl.params[0].gain_lin[:] == batch.params[4].gain_lin[:]
+    assert list(sl.reverb_rows) == [int(r) - 4 for r in batch.reverb_rows if 4 <= r < 9]
+    # same seed, same decisions
+    torch.manual_seed(7)
+    again = aug.draw_batch(16)
+    assert bytes(again.params) == bytes(batch.params) and torch.equal(again.impulse, batch.impulse)
+
+
+def _aug_dtype_for_test():
+    from mixing_style_transfer_b200.mixing_utils import _aug_dtype
+    return _aug_dtype()
+
+
+def test_butter_sos_batch_equals_scalar_design():
+    import numpy as np
+    from mixing_style_transfer_b200.mixing_utils import butter_sos_batch
+    fcs = [4000.0, 5123.4, 8000.0, 11999.9]
+    got = butter_sos_batch(4, fcs, "low", 44100)
+    for i, fc in enumerate(fcs):
+        assert np.allclose(got[i], np.asarray(pkg.butter_sos(4, fc, "low", 44100)), rtol=1e-13, atol=1e-16)
+        assert np.allclose(got[i], O.butter_sos(4, fc, "low", 44100), rtol=1e-13, atol=1e-15)
+    hp = butter_sos_batch(2, [2000.0], "high", 44100)
+    assert np.allclose(hp[0], O.butter_sos(2, 2000, "high", 44100), rtol=1e-13, atol=1e-15)
