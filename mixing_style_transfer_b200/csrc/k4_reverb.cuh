@@ -377,6 +377,9 @@ inline void build_section(const double (&c)[5], AugSection& out) {
     for (int n = 0; n < kAugV; ++n) mat2_mul(P, A, P);
     for (int i = 0; i < 4; ++i) out.mp[0][i] = P[i];       // M = A^16
     for (int d = 1; d < 5; ++d) mat2_mul(out.mp[d - 1], out.mp[d - 1], out.mp[d]);
+    for (int d = 0; d < 5; ++d)
+        for (int i = 0; i < 4; ++i) out.mpf[d][i] = (float)out.mp[d][i];
+    out.scan64 = std::pow(pole_radius(a1, a2), (double)kAugV) > 0.2 ? 1 : 0;
 }
 
 // Static compressor constants (k3_augment.cuh): the knee in the amplitude domain and 2^(c0 + c1 lg2 a).
