@@ -195,6 +195,12 @@ int mixfe_debug_feature_kernel_config(const mixfe_plan* plan, int* ctas_per_sm, 
  * the all-gather of BASELINE config 5 without kernels). */
 int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream);
 
+/* The all-gather of BASELINE config 5 driven by SMs: copies `bytes` (a multiple of 16) from src to the same position of
+ * n_peers peer buffers (dst: HOST array of device pointers that are NVLink peer mappings of this process, e.g. torch
+ * symmetric-memory buffers; <= 15), 128-bit loads and stores, n_ctas CTAs of 512 threads, stream-ordered.  Meant to run beside
+ * K1 with mixfe_plan_reserve_sms(n_ctas) so that the gather of one chunk overlaps the kernels of the next. */
+int mixfe_push_peers(void* const* dst, int n_peers, const void* src, size_t bytes, int n_ctas, void* cuda_stream);
+
 /* K1 runs as a persistent grid that fills every SM; a collective launched beside it (the all-gather of the
  * previous chunk, distributed.extract_global_batch) cannot start until CTAs retire.  Leaving n_sms SMs out
  * of K1's grid lets it run concurrently.  0 restores the full grid. */

@@ -79,7 +79,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
            "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
            "mixfe_stft_loss_forward", "mixfe_stft_loss_backward", "mixfe_plan_create_augment", "mixfe_effects",
-           "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress")
+           "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress", "mixfe_push_peers")
 
 
 def lib() -> ctypes.CDLL:
@@ -124,6 +124,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
+        L.mixfe_push_peers.argtypes = [ctypes.POINTER(vp), ci, vp, ctypes.c_size_t, ci, vp]
         L.mixfe_gated_loudness.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
         L.mixfe_short_term_loudness_iqr.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
         L.mixfe_stft_loss_forward.argtypes = [vp, vp, vp, ci, ci, ci, ll, ll, ll, ll, vp, vp]
@@ -219,6 +220,13 @@ def copy_async(dst_ptr: int, src: torch.Tensor, nbytes: int) -> None:
     """Copy-engine D2D copy of `nbytes` from the (contiguous) tensor `src` to the raw device address `dst_ptr` on the
     current stream of src's device; dst_ptr may be an NVSwitch multicast address."""
     _check(lib().mixfe_copy_async(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src.data_ptr()), nbytes, _stream(src.device)))
+
+
+def push_peers(dst_ptrs: Sequence[int], src: torch.Tensor, nbytes: int, n_ctas: int) -> None:
+    """SM-driven copy of `nbytes` from the (contiguous) tensor `src` to every raw device address in dst_ptrs (NVLink peer
+    mappings) on the current stream of src's device (kernel K11)."""
+    arr = (ctypes.c_void_p * len(dst_ptrs))(*dst_ptrs)
+    _check(lib().mixfe_push_peers(arr, len(dst_ptrs), ctypes.c_void_p(src.data_ptr()), nbytes, n_ctas, _stream(src.device)))
 
 
 class Plan:

@@ -22,6 +22,34 @@
 
 using namespace mixfe;
 
+// K11: the all-gather of BASELINE config 5 as ONE kernel on a few SMs: 128-bit loads of this rank's slice, 128-bit stores
+// into the same offset of every peer's buffer over NVLink peer mappings (torch symmetric memory).  It runs beside K1's
+// persistent grid (mixfe_plan_reserve_sms leaves it the SMs), so the gather of chunk c overlaps the kernels of chunk c + 1.
+constexpr int kMaxPushPeers = 15;
+constexpr int kPushThreads = 512;
+struct PushParams {
+    const void* src;
+    void* dst[kMaxPushPeers];
+    size_t bytes;
+    int n_peers;
+};
+__global__ void __launch_bounds__(kPushThreads) k11_push_peers(const __grid_constant__ PushParams p) {
+    const size_t n = p.bytes / 16, stride = (size_t)gridDim.x * kPushThreads;
+    const int4* __restrict__ src = reinterpret_cast<const int4*>(p.src);
+    for (size_t i = (size_t)blockIdx.x * kPushThreads + threadIdx.x; i < n; i += 4 * stride) {
+        int4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (i + u * stride < n) v[u] = __ldg(src + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (i + u * stride < n) {
+                for (int q = 0; q < p.n_peers; ++q) reinterpret_cast<int4*>(p.dst[q])[i + u * stride] = v[u];
+            }
+        }
+    }
+}
+
 
 namespace {
 
@@ -791,6 +819,25 @@ int mixfe_plan_set_filterbank(mixfe_plan* pl, const float* fb_host) {
 int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream) {
     if (!dst || !src) return fail(MIXFE_EINVAL, "null dst or src");
     MIXFE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(cuda_stream)));
+    return MIXFE_OK;
+}
+
+int mixfe_push_peers(void* const* dst, int n_peers, const void* src, size_t bytes, int n_ctas, void* cuda_stream) {
+    if (!dst || !src || n_peers < 0 || n_peers > kMaxPushPeers) return fail(MIXFE_EINVAL, "bad peers (at most %d)", kMaxPushPeers);
+    if (n_peers == 0 || bytes == 0) return MIXFE_OK;
+    if (n_ctas <= 0 || n_ctas > 1024) return fail(MIXFE_EINVAL, "bad CTA count");
+    PushParams p{};
+    p.src = src; p.bytes = bytes; p.n_peers = n_peers;
+    bool vec = (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && bytes % 16 == 0;
+    for (int i = 0; i < n_peers; ++i) {
+        if (!dst[i]) return fail(MIXFE_EINVAL, "peer pointer %d is NULL", i);
+        p.dst[i] = dst[i];
+        vec = vec && (reinterpret_cast<uintptr_t>(dst[i]) & 15u) == 0;
+    }
+    if (!vec) return fail(MIXFE_EINVAL, "push: pointers and size must be multiples of 16 bytes");
+    k11_push_peers<<<n_ctas, kPushThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(p);
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter()++;
     return MIXFE_OK;
 }
 

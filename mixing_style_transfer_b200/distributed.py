@@ -60,6 +60,7 @@ class GlobalBatch:
         self._handle = None
         self._mc = None                             # multicast mode: (address of features, address of logmel) in the multicast mapping
         self._stage = None                          # multicast mode: this rank's results before they are multicast
+        self.push_sms = 0                           # symmetric="sm": CTAs of the SM-driven push kernel (0: copy engines)
         if symmetric and self.world > 1:
             # One NVLink-mapped allocation per rank (torch symmetric memory); the gather is then a set of
             # copy-engine pushes into the peers' buffers: no SMs, so it runs under the persistent feature kernel.
@@ -74,6 +75,8 @@ class GlobalBatch:
                 return f, (t[nf:].view(n, 8, n_mels, n_frames) if with_logmel else None)
             self.features, self.logmel = views(flat)
             self._peers = [views(self._handle.get_buffer(r, (nf + nl,), torch.float32)) for r in range(self.world)]
+            if symmetric == "sm":
+                self.push_sms = 16
             if symmetric == "multicast":
                 # One copy to the NVSwitch multicast mapping lands in EVERY rank's buffer (this one included), so the
                 # kernels write a local staging slice and 2 copies per chunk replace the 2 (world - 1) pushes.
@@ -125,8 +128,16 @@ class GlobalBatch:
                     copy_async(self._mc[1] + 4 * lo * self.logmel[0].numel(), lm, 4 * lm.numel())
                 copy_async(self._mc[0] + 4 * lo * self.features.shape[1], f, 4 * f.numel())
                 continue
-            for k in range(1, self.world):
-                pf, plm = self._peers[(self.rank + k) % self.world]
+            order = [(self.rank + k) % self.world for k in range(1, self.world)]
+            if self.push_sms:
+                # one kernel on a few SMs stores the slice into all peers (K11); the feature kernel leaves it the SMs
+                from ._native import push_peers
+                if lm is not None:
+                    push_peers([self._peers[r][1][lo:lo + self.cs].data_ptr() for r in order], lm, 4 * lm.numel(), self.push_sms)
+                push_peers([self._peers[r][0][lo:lo + self.cs].data_ptr() for r in order], f, 4 * f.numel(), 1)
+                continue
+            for r in order:
+                pf, plm = self._peers[r]
                 if lm is not None:
                     plm[lo:lo + self.cs].copy_(lm, non_blocking=True)
                 pf[lo:lo + self.cs].copy_(f, non_blocking=True)
@@ -179,6 +190,17 @@ def extract_global_batch(extractor, local_stems: Dict[str, torch.Tensor], group=
     side = gather and gb.world > 1 and first.is_cuda and n_chunks > 1
     if side and comm_stream is None:
         comm_stream = torch.cuda.Stream(device=first.device)
+    reserve = gb.push_sms if (side and gb.push_sms) else 0
+    if reserve:
+        plan.reserve_sms(reserve)                   # K1's persistent grid leaves the push kernel its SMs
+    try:
+        return _extract_chunks(plan, gb, local_stems, STEMS, n_chunks, with_logmel, gather, side, comm_stream, first)
+    finally:
+        if reserve:
+            plan.reserve_sms(0)
+
+
+def _extract_chunks(plan, gb, local_stems, STEMS, n_chunks, with_logmel, gather, side, comm_stream, first):
     for c in range(n_chunks):
         f, lm = gb.local_views(c)
         sl = slice(c * gb.cs, (c + 1) * gb.cs)
