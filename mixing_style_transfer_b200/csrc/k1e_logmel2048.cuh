@@ -1,0 +1,309 @@
+// K1E: log-mel of the n_fft = 2048 configurations -- the reference's trained encoder and evaluation extractor use
+// (2048, 512, 80) (scripts/train_baseline.sh:42-44, src/train_style_transfer.py:523-533, inference/validate_retrieval.py:355)
+// -- on the one-warp 1024-point transform of K1.  (Features at n_fft = 2048, and every other n_fft, stay on K1G.)
+//
+// Reference behaviour being replaced: MelSpectrogramPreprocessor.forward (src/model.py:41-67) for that configuration.
+//
+// A 2048-point frame does not fit the register-resident transform (64 complex values per lane), so it is split by
+// decimation in time: E = FFT_1024(even samples), O = FFT_1024(odd samples), X[k] = E[k] + W_2048^k O[k],
+// X[k + 1024] = E[k] - W_2048^k O[k].  TWO WARPS share a frame: the even warp and the odd warp each run K1's transform on
+// their windowed half (L and R packed as one complex sequence), the odd warp applies W_2048^k, both park their
+// spectra in their exchange regions, and each then forms half of the frame's 1025 (L, R) powers from shared memory:
+//   X[k] = E[k] + O'[k],  X[2048 - k] = E[1024 - k] - O'[1024 - k],  P_L = |X[k] + conj X[2048 - k]|^2,  P_R = |X[k] - conj X[2048 - k]|^2.
+// A CTA (8 warps, 2 per SM, persistent) therefore handles tiles of 4 frames; staging (TMA bulk copies one (tile, stem) ahead,
+// cooperative loads with torch's 'reflect' at the clip edges), the exchange layout and the log epilogue are K1's.
+// Mel projection: thread = (work item, frame pair).  The filterbank by filter (CSR) is cut into at most 128 items, the
+// longest filters split in two halves that sit in neighbouring lanes and are joined by one shuffle, items sorted by
+// length so that a warp's lanes walk similar supports; sums run in a fixed order (deterministic).
+#pragma once
+
+#include "k1_features.cuh"
+
+namespace mixfe {
+
+constexpr int kETF = 4;                  // frames per tile (2 warps each)
+constexpr int kEThreads = 256;
+constexpr int kEItems = 128;             // mel work items per frame pair
+constexpr int kEColOff = kWarpRegion - 4096;      // the power column starts here in the even warp's region and runs on
+                                                  // into the odd warp's: 512 entries + 513 entries, contiguous
+
+struct K1EParams {
+    const float* stem[kNumStems];
+    long long stride_b, stride_c;
+    int B, T, F, hop, n_mels, n_tiles;
+    int nxs;                         // staged samples per channel = (kETF - 1) * hop + 2048
+    int tma_lo, tma_hi;              // tiles staged by TMA (empty range = none)
+    long long total_items;
+    float* logmel;
+    long long lm_stride_b;
+    const float2* tw;                // [1024] 32 x 32 twiddles of the 1024-point transform
+    const int4* items;               // [kEItems] (filter, first bin, bins, weight offset | split flag << 30)
+    const float* wts;                // CSR weights
+    int n_wts;
+    int off_ex, off_tw, off_items, off_wts, off_bar;
+};
+
+// cos / sin of 2 pi j / 64, j = 0..31 (compile-time after unrolling)
+__device__ __forceinline__ constexpr float cos64(int j) {
+    constexpr float c[17] = {1.0f, 0.99518472667219688624f, 0.98078528040323044913f, 0.95694033573220886494f,
+                             0.92387953251128675613f, 0.88192126434835502971f, 0.83146961230254523708f, 0.77301045336273696081f,
+                             0.70710678118654752440f, 0.63439328416364549822f, 0.55557023301960222474f, 0.47139673682599764856f,
+                             0.38268343236508977173f, 0.29028467725446236764f, 0.19509032201612826785f, 0.09801714032956060199f, 0.0f};
+    return j <= 16 ? c[j] : -c[32 - j];
+}
+__device__ __forceinline__ constexpr float sin64(int j) { return j <= 16 ? cos64(16 - j) : cos64(j - 16); }
+
+__device__ __forceinline__ void named_bar(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+__global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_constant__ K1EParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float* const xsL = reinterpret_cast<float*>(smem);                          // [nxs] left, then [nxs] right
+    unsigned char* const ex = smem + p.off_ex;                                  // 8 warp regions
+    float2* const tw = reinterpret_cast<float2*>(smem + p.off_tw);              // [31][32], rows k1 = 1..31
+    int4* const items = reinterpret_cast<int4*>(smem + p.off_items);            // [kEItems]
+    float* const wts = reinterpret_cast<float*>(smem + p.off_wts);
+    const unsigned bar = smem_u32(smem + p.off_bar);
+    int* const arrivals = reinterpret_cast<int*>(smem + p.off_bar + 8);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q = warp >> 1, par = warp & 1;            // frame of the tile, even / odd half
+    long long item = blockIdx.x;
+    if (item >= p.total_items) return;
+
+    for (int i = tid; i < 31 * 32; i += kEThreads) tw[i] = p.tw[32 + i];
+    for (int i = tid; i < kEItems; i += kEThreads) items[i] = p.items[i];
+    for (int i = tid; i < p.n_wts; i += kEThreads) wts[i] = p.wts[i];
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        *arrivals = 0;
+    }
+    // per-lane constants: window phase B = pi (2 lane + par) / 1024; the odd warp's W_2048^lane
+    float cb, sb, wlx, wly;
+    sincospif((float)(2 * lane + par) * (1.0f / 1024.0f), &sb, &cb);
+    sincospif((float)lane * (1.0f / 1024.0f), &wly, &wlx);
+    wly = -wly;                                         // exp(-i pi lane / 1024)
+    __syncthreads();
+
+    unsigned char* const region = ex + warp * kWarpRegion;
+    float2* const exw = reinterpret_cast<float2*>(region);
+    unsigned char* const regE = ex + (2 * q) * kWarpRegion;        // the pair's even / odd regions
+    unsigned char* const regO = regE + kWarpRegion;
+    const long long span = (long long)kETF * p.hop;
+
+    auto stage_base = [&](int tile) { return (long long)tile * span - 1024; };
+    auto stage_tma = [&](int b, int tile, int s) {                 // one thread
+        const float* gL = (s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3]) + (long long)b * p.stride_b;
+        const unsigned bytes = (unsigned)p.nxs * 4u;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(bar, 2u * bytes);
+        tma_bulk_g2s(smem_u32(xsL), gL + stage_base(tile), bytes, bar);
+        tma_bulk_g2s(smem_u32(xsL + p.nxs), gL + p.stride_c + stage_base(tile), bytes, bar);
+    };
+    auto stage_coop = [&](int b, int tile, int s) {                // all threads, 'reflect' indexing
+        const float* gL = (s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3]) + (long long)b * p.stride_b;
+        const float* gR = gL + p.stride_c;
+        const long long base = stage_base(tile);
+        for (int i = tid; i < p.nxs; i += kEThreads) {
+            long long j = base + i;
+            if (j < 0) j = -j;
+            if (j >= p.T) j = 2ll * (p.T - 1) - j;
+            j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);
+            xsL[i] = __ldg(gL + j);
+            xsL[p.nxs + i] = __ldg(gR + j);
+        }
+    };
+
+    int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
+    bool cur_tma = tile >= p.tma_lo && tile <= p.tma_hi;
+    unsigned tma_parity = 0;
+    if (cur_tma) { if (tid == 0) stage_tma(b, tile, 0); } else stage_coop(b, tile, 0);
+
+    for (;;) {
+        const int u0 = tile * kETF;
+        const int nvalid = p.F - u0 < kETF ? p.F - u0 : kETF;
+        const long long next_item = item + gridDim.x;
+        for (int s = 0; s < kNumStems; ++s) {
+            if (cur_tma) {
+                mbar_wait(bar, tma_parity);
+                tma_parity ^= 1u;
+            }
+            __syncthreads();                 // B0: xs holds (tile, s); the previous mel walk has left the power columns
+            cplx64 z[32];
+            const bool active = q < nvalid;
+            if (active) {
+                // even / odd samples of frame q, window 0.5 * hann2048[2 m + par], m = 32 n1 + lane
+                const unsigned xa = smem_u32(xsL + q * p.hop + par + 2 * lane);
+                const unsigned xr_off = (unsigned)p.nxs * 4u;
+                float fl[32], fr[32];
+#pragma unroll
+                for (int n1 = 0; n1 < 32; ++n1) {
+                    fl[n1] = lds32(xa + n1 * 256);
+                    fr[n1] = lds32(xa + xr_off + n1 * 256);
+                }
+#pragma unroll
+                for (int n1 = 0; n1 < 32; ++n1) {
+                    const float ca = n1 < 16 ? w32_re(n1) : -w32_re(n1 - 16);
+                    const float sa = n1 < 16 ? w32_sin(n1) : -w32_sin(n1 - 16);
+                    const float wv = fmaf(0.25f * sa, sb, fmaf(-0.25f * ca, cb, 0.25f));
+                    z[n1] = cpack(fl[n1] * wv, fr[n1] * wv);
+                }
+            }
+            // ---- prefetch the next (tile, stem): the last warp to have its samples in registers starts the copy -------
+            {
+                int nb = b, ntile = tile, ns = s + 1;
+                if (ns == kNumStems) {
+                    nb = (int)(next_item / p.n_tiles);
+                    ntile = (int)(next_item - (long long)nb * p.n_tiles);
+                    ns = 0;
+                }
+                const bool have_next = s + 1 < kNumStems || next_item < p.total_items;
+                bool next_tma = false;
+                if (have_next) {
+                    next_tma = ntile >= p.tma_lo && ntile <= p.tma_hi;
+                    if (next_tma) {
+                        __syncwarp();
+                        if (lane == 0) {
+                            __threadfence_block();
+                            if (atomicAdd(arrivals, 1) == kEThreads / 32 - 1) {
+                                *arrivals = 0;
+                                stage_tma(nb, ntile, ns);
+                            }
+                        }
+                    } else {
+                        __syncthreads();
+                        stage_coop(nb, ntile, ns);
+                    }
+                }
+                cur_tma = next_tma;
+            }
+            if (active) {
+#pragma unroll 1
+                for (int pass = 0; pass < 2; ++pass) {
+                    dft32_dif_packed(z);
+                    if (pass == 0) {
+                        const unsigned twa = smem_u32(tw + lane) - 256;
+                        const unsigned wa = smem_u32(exw) + lane * 8;
+                        float2 tq[2][8];
+#pragma unroll
+                        for (int g = 1; g < 8; ++g) tq[0][g] = lds64<0>(twa + g * 256);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            if (g < 3) {
+#pragma unroll
+                                for (int r = 0; r < 8; ++r) tq[(g + 1) & 1][r] = lds64<0>(twa + (8 * g + 8 + r) * 256);
+                            }
+#pragma unroll
+                            for (int r = 0; r < 8; ++r) {
+                                const int k1 = 8 * g + r;
+                                if (k1 == 0) {
+                                    sts_c<0>(wa, z[0]);
+                                } else {
+                                    float yr, yi;
+                                    cunpack(z[brev5(k1)], yr, yi);
+                                    const float2 t = tq[g & 1][r];
+                                    sts64<0>(wa + k1 * kExRow, fmaf(yr, t.x, -yi * t.y), fmaf(yr, t.y, yi * t.x));
+                                }
+                            }
+                        }
+                        __syncwarp();
+                        const unsigned ra = smem_u32(exw) + lane * kExRow;
+#pragma unroll
+                        for (int n2 = 0; n2 < 32; ++n2) z[n2] = lds_c<0>(ra + n2 * 8);
+                        __syncwarp();
+                    }
+                }
+                // slot k2 (register brev5(k2)) holds bin lane + 32 k2 of E (even warp) or O (odd warp).
+                // Park the spectrum as rows [k2][lane] (256 bytes each) + row 32 = row 0 (the partner of lane 0's row r
+                // is row 32 - r); the odd warp first applies W_2048^(lane + 32 k2) = W_2048^lane * W_64^k2.
+                const unsigned pa = smem_u32(region) + lane * 8;
+#pragma unroll
+                for (int k2 = 0; k2 < 32; ++k2) {
+                    float vr, vi;
+                    cunpack(z[brev5(k2)], vr, vi);
+                    if (par) {
+                        const float c = cos64(k2), sn = sin64(k2);             // W_64^k2 = c - i sn
+                        const float tr = k2 == 0 ? vr : (k2 == 16 ? vi : fmaf(vr, c, vi * sn));
+                        const float ti = k2 == 0 ? vi : (k2 == 16 ? -vr : fmaf(vi, c, -vr * sn));
+                        vr = fmaf(tr, wlx, -ti * wly);
+                        vi = fmaf(tr, wly, ti * wlx);
+                    }
+                    sts64<0>(pa + k2 * 256, vr, vi);
+                    if (k2 == 0) sts64<0>(pa + 32 * 256, vr, vi);
+                }
+            }
+            named_bar(1 + q, 64);            // the pair's spectra are parked
+            float2 pw[16];
+            float2 pw1024 = make_float2(0.0f, 0.0f);
+            if (active) {
+                // rows r = 16 par + j: bin k = lane + 32 r; partner 1024 - k in row 31 - r (+ 1 for lane 0), lane (32 - lane) & 31
+                const unsigned eo = smem_u32(regE), oo = smem_u32(regO);
+                const unsigned own = (unsigned)(16 * par) * 256u + (unsigned)lane * 8u;
+                const unsigned prt = (unsigned)(31 - 16 * par) * 256u + (lane == 0 ? 256u : 0u) + (unsigned)((32 - lane) & 31) * 8u;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 e = lds64<0>(eo + own + j * 256), o = lds64<0>(oo + own + j * 256);
+                    const float2 ep = lds64<0>(eo + prt - j * 256), op = lds64<0>(oo + prt - j * 256);
+                    const float xr = e.x + o.x, xi = e.y + o.y;               // X[k]
+                    const float yr = ep.x - op.x, yi = ep.y - op.y;           // X[2048 - k]
+                    const float a = xr + yr, bb = xi - yi, c = xr - yr, d = xi + yi;
+                    pw[j] = make_float2(fmaf(a, a, bb * bb), fmaf(c, c, d * d));
+                }
+                if (par == 0 && lane == 0) {          // bins 0 = E[0] + O'[0] and 1024 = E[0] - O'[0] are their own partners
+                    const float2 e = lds64<0>(eo), o = lds64<0>(oo);
+                    const float sr = e.x + o.x, si = e.y + o.y, xr = e.x - o.x, xi = e.y - o.y;
+                    pw[0] = make_float2(4.0f * sr * sr, 4.0f * si * si);
+                    pw1024 = make_float2(4.0f * xr * xr, 4.0f * xi * xi);
+                }
+            }
+            named_bar(1 + q, 64);            // both warps have read the parked spectra: the regions become the power column
+            if (active) {
+                float2* const col = reinterpret_cast<float2*>(regE + kEColOff);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) col[lane + 32 * (16 * par + j)] = pw[j];
+                if (par == 0 && lane == 0) col[1024] = pw1024;
+            }
+            __syncthreads();                 // B1: the 4 power columns of the tile are complete
+
+            // ---- mel projection + log + store: thread = (item, frame pair) ----------------------------------------------
+            {
+                const int fp = tid >> 7, it = tid & (kEItems - 1);
+                const int4 im = items[it];
+                const int m = im.x, b0 = im.y, len = im.z;
+                const int woff = im.w & 0x3fffffff;
+                const bool second = (im.w >> 30) & 1, split = (im.w >> 31) & 1;
+                const float2* c0 = reinterpret_cast<const float2*>(ex + (4 * fp) * kWarpRegion + kEColOff) + b0;
+                const float2* c1 = reinterpret_cast<const float2*>(ex + (4 * fp + 2) * kWarpRegion + kEColOff) + b0;
+                const float* w = wts + woff;
+                float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll 4
+                for (int i = 0; i < len; ++i) {
+                    const float wi = w[i];
+                    const float2 u = c0[i], v = c1[i];
+                    a0 = fmaf(wi, u.x, a0);
+                    a1 = fmaf(wi, u.y, a1);
+                    a2 = fmaf(wi, v.x, a2);
+                    a3 = fmaf(wi, v.y, a3);
+                }
+                // halves of a split filter sit in lanes 2 i, 2 i + 1: first + second, in that order, in both lanes
+                const float o0 = __shfl_xor_sync(kFullMask, a0, 1), o1 = __shfl_xor_sync(kFullMask, a1, 1);
+                const float o2 = __shfl_xor_sync(kFullMask, a2, 1), o3 = __shfl_xor_sync(kFullMask, a3, 1);
+                if (split) { a0 += o0; a1 += o1; a2 += o2; a3 += o3; }
+                if (!second && m >= 0 && m < p.n_mels && p.logmel) {
+                    const int u = u0 + 2 * fp;
+                    float* d0 = p.logmel + (long long)b * p.lm_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + u;
+                    float* d1 = d0 + (long long)p.n_mels * p.F;
+                    if (u < p.F) { d0[0] = ln_fast(a0 + 1e-10f); d1[0] = ln_fast(a1 + 1e-10f); }
+                    if (u + 1 < p.F) { d0[1] = ln_fast(a2 + 1e-10f); d1[1] = ln_fast(a3 + 1e-10f); }
+                }
+            }
+        }
+        if (next_item >= p.total_items) break;
+        item = next_item;
+        b = (int)(item / p.n_tiles);
+        tile = (int)(item - (long long)b * p.n_tiles);
+    }
+}
+
+}  // namespace mixfe

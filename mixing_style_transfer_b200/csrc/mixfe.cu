@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "k1_features.cuh"
 #include "k1g_features.cuh"
+#include "k1e_logmel2048.cuh"
 #include "k6_logmel_bwd.cuh"
 #include "k6f_logmel_bwd.cuh"
 #include "plan.cuh"
@@ -356,10 +357,74 @@ int upload_fft_twiddles(mixfe_plan* pl) {
     return rc;
 }
 
+// K1E tables (n_fft = 2048): the filterbank by filter cut into <= 128 work items, longest supports first, the longest
+// filters split into two halves in neighbouring items (k1e_logmel2048.cuh).
+int build_k1e_tables(mixfe_plan* pl) {
+    if (pl->d_eitems) { cudaFree(pl->d_eitems); pl->d_eitems = nullptr; }
+    if (pl->d_ewts) { cudaFree(pl->d_ewts); pl->d_ewts = nullptr; }
+    if (pl->n_fft != 2048 || pl->hop % 4 || pl->n_mels > kEItems) return MIXFE_OK;
+    const int nf = pl->n_freq, nm = pl->n_mels;
+    std::vector<int> lo(nm, 0), len(nm, 0), woff(nm, 0);
+    std::vector<float> w;
+    for (int m = 0; m < nm; ++m) {
+        int first = -1, last = -1;
+        for (int k = 0; k < nf; ++k)
+            if (pl->fb[(size_t)k * nm + m] != 0.0f) { if (first < 0) first = k; last = k; }
+        woff[m] = (int)w.size();
+        if (first >= 0) {
+            lo[m] = first; len[m] = last - first + 1;
+            for (int k = first; k <= last; ++k) w.push_back(pl->fb[(size_t)k * nm + m]);
+        }
+    }
+    if (w.empty()) w.push_back(0.0f);
+    std::vector<int> order(nm);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
+    int n_split = std::min(nm, kEItems - nm);
+    while (n_split > 0 && len[order[n_split - 1]] < 8) --n_split;          // short supports are not worth a shuffle
+    std::vector<int4> items;
+    for (int i = 0; i < n_split; ++i) {
+        const int m = order[i], h = (len[m] + 1) / 2;
+        items.push_back(make_int4(m, lo[m], h, woff[m] | (int)(1u << 31)));
+        items.push_back(make_int4(m, lo[m] + h, len[m] - h, (woff[m] + h) | (int)(1u << 31) | (1 << 30)));
+    }
+    for (int i = n_split; i < nm; ++i) {
+        const int m = order[i];
+        items.push_back(make_int4(m, lo[m], len[m], woff[m]));
+    }
+    while ((int)items.size() < kEItems) items.push_back(make_int4(-1, 0, 0, 0));
+    // halves are now shorter than some unsplit filters: re-sort PAIRS of items by their longer member, keeping pairs together
+    {
+        std::vector<std::pair<int4, int4>> pairs;
+        for (int i = 0; i < kEItems; i += 2) pairs.emplace_back(items[i], items[i + 1]);
+        std::stable_sort(pairs.begin(), pairs.end(), [](const std::pair<int4, int4>& a, const std::pair<int4, int4>& b) {
+            return std::max(a.first.z, a.second.z) > std::max(b.first.z, b.second.z);
+        });
+        for (int i = 0; i < kEItems / 2; ++i) { items[2 * i] = pairs[i].first; items[2 * i + 1] = pairs[i].second; }
+    }
+    pl->e_nwts = (int)w.size();
+    pl->e_nxs = (kETF - 1) * pl->hop + 2048;
+    pl->e_off_ex = (pl->e_nxs * 8 + 127) & ~127;
+    pl->e_off_tw = pl->e_off_ex + 8 * kWarpRegion;
+    pl->e_off_items = pl->e_off_tw + 31 * 32 * 8;
+    pl->e_off_wts = pl->e_off_items + kEItems * 16;
+    pl->e_off_bar = align16(pl->e_off_wts + pl->e_nwts * 4);
+    pl->smem_e = pl->e_off_bar + 32;
+    if (pl->smem_e > 227 * 1024) return MIXFE_OK;                          // hop too large: K1G serves the plan
+    int rc;
+    if ((rc = upload(&pl->d_eitems, items)) || (rc = upload(&pl->d_ewts, w))) return rc;
+    if ((rc = smem_optin(k1e_logmel2048, pl->device, pl->smem_e))) return rc;
+    int per_sm = 0;
+    MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1e_logmel2048, kEThreads, pl->smem_e));
+    pl->e_ctas = std::max(1, per_sm) * pl->n_sms;
+    return MIXFE_OK;
+}
+
 // Which kernel serves the plan: K1 for n_fft = 1024 when its shared-memory map fits, else K1G.
 int build_tables(mixfe_plan* pl) {
     int rc = build_generic_tables(pl);
     if (rc) return rc;
+    if ((rc = build_k1e_tables(pl))) return rc;
     const char* force = getenv("MIXFE_FORCE_GENERIC");
     pl->use_generic = true;
     if (pl->n_fft == kNfft && !(force && atoi(force))) {
@@ -421,6 +486,35 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         }
         if (aligned && pl->hop % 16 == 0 && tile_span * 4 <= kWarpRegion)
             p.rows_hi = (int)std::min<long long>((long long)T / tile_span - 1, n_tiles - 1);   // (tile + 1) * span <= T
+    }
+    const char* force_g = getenv("MIXFE_FORCE_GENERIC");
+    if (pl->d_eitems && !features && !melpow && logmel && !(force_g && atoi(force_g))) {
+        // K1E: log-mel only, n_fft = 2048, on the one-warp 1024-point transform (two warps per frame)
+        K1EParams e{};
+        for (int s = 0; s < 4; ++s) e.stem[s] = stems[s];
+        e.stride_b = stride_b; e.stride_c = stride_c; e.B = B; e.T = T; e.F = F; e.hop = pl->hop; e.n_mels = pl->n_mels;
+        e.n_tiles = (F + kETF - 1) / kETF; e.nxs = pl->e_nxs; e.total_items = (long long)B * e.n_tiles;
+        e.logmel = logmel; e.lm_stride_b = lm_stride_b;
+        e.tw = pl->d_tw; e.items = pl->d_eitems; e.wts = pl->d_ewts; e.n_wts = pl->e_nwts;
+        e.off_ex = pl->e_off_ex; e.off_tw = pl->e_off_tw; e.off_items = pl->e_off_items; e.off_wts = pl->e_off_wts;
+        e.off_bar = pl->e_off_bar;
+        bool aligned = (stride_b % 4 == 0 || B == 1) && stride_c % 4 == 0;
+        for (int s = 0; s < 4; ++s) aligned = aligned && (reinterpret_cast<uintptr_t>(stems[s]) & 15u) == 0;
+        const long long span = (long long)kETF * pl->hop;
+        e.tma_lo = 1; e.tma_hi = 0;
+        if (aligned) {
+            e.tma_lo = (int)((1024 + span - 1) / span);                            // tile * span - 1024 >= 0
+            const long long room = (long long)T + 1024 - pl->e_nxs;                // tile * span - 1024 + nxs <= T
+            e.tma_hi = room < 0 ? -1 : (int)std::min<long long>(room / span, e.n_tiles - 1);
+        }
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
+            const int grid = (int)std::min<long long>(e.total_items, (long long)pl->e_ctas);
+            k1e_logmel2048<<<grid, kEThreads, pl->smem_e, stream>>>(e);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter()++;
+        return MIXFE_OK;
     }
     if (pl->use_generic) {
         K1GParams g{};
@@ -801,7 +895,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
     cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
-    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw);
+    cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw); cudaFree(pl->d_eitems); cudaFree(pl->d_ewts);
     if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
     delete pl;
     return MIXFE_OK;

@@ -30,6 +30,10 @@ struct mixfe_plan {
     float* d_mel_w = nullptr;
     int4* d_bin_meta = nullptr;         // CSR of the transposed filterbank (K6): (first filter, filters, weight offset, -) per bin
     float* d_bin_w = nullptr;
+    // K1E (k1e_logmel2048.cuh): log-mel of n_fft = 2048 plans on the one-warp transform; null items = not usable
+    int4* d_eitems = nullptr;
+    float* d_ewts = nullptr;
+    int e_nwts = 0, e_nxs = 0, e_off_ex = 0, e_off_tw = 0, e_off_items = 0, e_off_wts = 0, e_off_bar = 0, smem_e = 0, e_ctas = 0;
     float4* d_binw = nullptr;           // K6F: per bin (first filter, its weight, the next filter's weight, -); null = K6F not usable
     int f_off_ex = 0, f_off_tw = 0, f_off_binw = 0, f_off_dmel = 0, f_off_ola = 0, smem_f = 0;      // K6F shared-memory map
     int b_nf = 0, b_span = 0, b_span_pad = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)
