@@ -13,7 +13,7 @@
 // A CTA (8 warps, 2 per SM, persistent) therefore handles tiles of 4 frames; staging (TMA bulk copies one (tile, stem) ahead,
 // cooperative loads with torch's 'reflect' at the clip edges), the exchange layout and the log epilogue are K1's.
 // Mel projection: thread = (work item, frame pair).  The filterbank by filter (CSR) is cut into at most 128 items, the
-// longest filters split in two halves that sit in neighbouring lanes and are joined by one shuffle, items sorted by
+// longest filters in 2 or 4 parts that sit in neighbouring lanes and are joined by shuffles, items sorted by
 // length so that a warp's lanes walk similar supports; sums run in a fixed order (deterministic).
 #pragma once
 
@@ -37,7 +37,7 @@ struct K1EParams {
     float* logmel;
     long long lm_stride_b;
     const float2* tw;                // [1024] 32 x 32 twiddles of the 1024-point transform
-    const int4* items;               // [kEItems] (filter, first bin, bins, weight offset | split flag << 30)
+    const int4* items;               // [kEItems] (filter, first bin, bins, weight offset | log2(parts) << 28 | not-first << 30)
     const float* wts;                // CSR weights
     int n_wts;
     int off_ex, off_tw, off_items, off_wts, off_bar;
@@ -55,6 +55,37 @@ __device__ __forceinline__ constexpr float sin64(int j) { return j <= 16 ? cos64
 
 __device__ __forceinline__ void named_bar(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+__device__ __forceinline__ const float* k1e_row(const K1EParams& p, int b, int tile, int s) {      // first staged sample (left)
+    const float* g = s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3];
+    return g + (long long)b * p.stride_b + ((long long)tile * kETF * p.hop - 1024);
+}
+
+// one thread: arm the barrier and start both row copies (interior tiles, 16-byte aligned rows)
+__device__ __forceinline__ void k1e_stage_tma(const K1EParams& p, int b, int tile, int s, float* xsL, unsigned bar) {
+    const float* gL = k1e_row(p, b, tile, s);
+    const unsigned bytes = (unsigned)p.nxs * 4u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_expect_tx(bar, 2u * bytes);
+    tma_bulk_g2s(smem_u32(xsL), gL, bytes, bar);
+    tma_bulk_g2s(smem_u32(xsL + p.nxs), gL + p.stride_c, bytes, bar);
+}
+
+// all threads: torch's 'reflect' indexing (clip edges) or plain loads (unaligned rows)
+__device__ __forceinline__ void k1e_stage_coop(const K1EParams& p, int b, int tile, int s, float* xsL, int tid) {
+    const float* g = s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3];
+    const float* gL = g + (long long)b * p.stride_b;
+    const float* gR = gL + p.stride_c;
+    const long long base = (long long)tile * kETF * p.hop - 1024;
+    for (int i = tid; i < p.nxs; i += kEThreads) {
+        long long j = base + i;
+        if (j < 0) j = -j;
+        if (j >= p.T) j = 2ll * (p.T - 1) - j;
+        j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);
+        xsL[i] = __ldg(gL + j);
+        xsL[p.nxs + i] = __ldg(gR + j);
+    }
 }
 
 __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_constant__ K1EParams p) {
@@ -90,35 +121,11 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
     float2* const exw = reinterpret_cast<float2*>(region);
     unsigned char* const regE = ex + (2 * q) * kWarpRegion;        // the pair's even / odd regions
     unsigned char* const regO = regE + kWarpRegion;
-    const long long span = (long long)kETF * p.hop;
-
-    auto stage_base = [&](int tile) { return (long long)tile * span - 1024; };
-    auto stage_tma = [&](int b, int tile, int s) {                 // one thread
-        const float* gL = (s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3]) + (long long)b * p.stride_b;
-        const unsigned bytes = (unsigned)p.nxs * 4u;
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(bar, 2u * bytes);
-        tma_bulk_g2s(smem_u32(xsL), gL + stage_base(tile), bytes, bar);
-        tma_bulk_g2s(smem_u32(xsL + p.nxs), gL + p.stride_c + stage_base(tile), bytes, bar);
-    };
-    auto stage_coop = [&](int b, int tile, int s) {                // all threads, 'reflect' indexing
-        const float* gL = (s == 0 ? p.stem[0] : s == 1 ? p.stem[1] : s == 2 ? p.stem[2] : p.stem[3]) + (long long)b * p.stride_b;
-        const float* gR = gL + p.stride_c;
-        const long long base = stage_base(tile);
-        for (int i = tid; i < p.nxs; i += kEThreads) {
-            long long j = base + i;
-            if (j < 0) j = -j;
-            if (j >= p.T) j = 2ll * (p.T - 1) - j;
-            j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);
-            xsL[i] = __ldg(gL + j);
-            xsL[p.nxs + i] = __ldg(gR + j);
-        }
-    };
 
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
     bool cur_tma = tile >= p.tma_lo && tile <= p.tma_hi;
     unsigned tma_parity = 0;
-    if (cur_tma) { if (tid == 0) stage_tma(b, tile, 0); } else stage_coop(b, tile, 0);
+    if (cur_tma) { if (tid == 0) k1e_stage_tma(p, b, tile, 0, xsL, bar); } else k1e_stage_coop(p, b, tile, 0, xsL, tid);
 
     for (;;) {
         const int u0 = tile * kETF;
@@ -168,12 +175,12 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                             __threadfence_block();
                             if (atomicAdd(arrivals, 1) == kEThreads / 32 - 1) {
                                 *arrivals = 0;
-                                stage_tma(nb, ntile, ns);
+                                k1e_stage_tma(p, nb, ntile, ns, xsL, bar);
                             }
                         }
                     } else {
                         __syncthreads();
-                        stage_coop(nb, ntile, ns);
+                        k1e_stage_coop(p, nb, ntile, ns, xsL, tid);
                     }
                 }
                 cur_tma = next_tma;
@@ -271,8 +278,9 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                 const int fp = tid >> 7, it = tid & (kEItems - 1);
                 const int4 im = items[it];
                 const int m = im.x, b0 = im.y, len = im.z;
-                const int woff = im.w & 0x3fffffff;
-                const bool second = (im.w >> 30) & 1, split = (im.w >> 31) & 1;
+                const int woff = im.w & 0x0fffffff;
+                const int lg_parts = (im.w >> 28) & 3;                 // the filter is cut into 1, 2 or 4 neighbouring items
+                const bool second = (im.w >> 30) & 1;                  // not the first part: does not store
                 const float2* c0 = reinterpret_cast<const float2*>(ex + (4 * fp) * kWarpRegion + kEColOff) + b0;
                 const float2* c1 = reinterpret_cast<const float2*>(ex + (4 * fp + 2) * kWarpRegion + kEColOff) + b0;
                 const float* w = wts + woff;
@@ -286,10 +294,13 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                     a2 = fmaf(wi, v.x, a2);
                     a3 = fmaf(wi, v.y, a3);
                 }
-                // halves of a split filter sit in lanes 2 i, 2 i + 1: first + second, in that order, in both lanes
-                const float o0 = __shfl_xor_sync(kFullMask, a0, 1), o1 = __shfl_xor_sync(kFullMask, a1, 1);
-                const float o2 = __shfl_xor_sync(kFullMask, a2, 1), o3 = __shfl_xor_sync(kFullMask, a3, 1);
-                if (split) { a0 += o0; a1 += o1; a2 += o2; a3 += o3; }
+                // the parts of a cut filter sit in 2 or 4 neighbouring, aligned lanes: pairwise sums, the same order in every lane
+#pragma unroll
+                for (int d = 1; d <= 2; d <<= 1) {
+                    const float o0 = __shfl_xor_sync(kFullMask, a0, d), o1 = __shfl_xor_sync(kFullMask, a1, d);
+                    const float o2 = __shfl_xor_sync(kFullMask, a2, d), o3 = __shfl_xor_sync(kFullMask, a3, d);
+                    if (lg_parts >= d) { a0 += o0; a1 += o1; a2 += o2; a3 += o3; }
+                }
                 if (!second && m >= 0 && m < p.n_mels && p.logmel) {
                     const int u = u0 + 2 * fp;
                     float* d0 = p.logmel + (long long)b * p.lm_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + u;

@@ -380,28 +380,36 @@ int build_k1e_tables(mixfe_plan* pl) {
     std::vector<int> order(nm);
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
-    int n_split = std::min(nm, kEItems - nm);
-    while (n_split > 0 && len[order[n_split - 1]] < 8) --n_split;          // short supports are not worth a shuffle
-    std::vector<int4> items;
-    for (int i = 0; i < n_split; ++i) {
-        const int m = order[i], h = (len[m] + 1) / 2;
-        items.push_back(make_int4(m, lo[m], h, woff[m] | (int)(1u << 31)));
-        items.push_back(make_int4(m, lo[m] + h, len[m] - h, (woff[m] + h) | (int)(1u << 31) | (1 << 30)));
+    // Cut the longest supports into 2 or 4 parts (neighbouring items, joined by shuffles) while items remain: greedy on
+    // the longest piece.  Groups of 4 first, then pairs, then whole filters -- each kind sorted by piece length -- so
+    // that groups stay aligned to their size and a warp's 32 lanes walk similar lengths.
+    std::vector<int> parts(nm, 1);
+    int used = nm;
+    for (;;) {
+        int best = -1, best_len = 7;                                       // pieces shorter than 8 bins are not worth a shuffle
+        for (int m = 0; m < nm; ++m) {
+            const int piece = (len[m] + parts[m] - 1) / parts[m];
+            if (parts[m] < 4 && used + parts[m] <= kEItems && piece > best_len) { best = m; best_len = piece; }
+        }
+        if (best < 0) break;
+        used += parts[best];
+        parts[best] *= 2;
     }
-    for (int i = n_split; i < nm; ++i) {
-        const int m = order[i];
-        items.push_back(make_int4(m, lo[m], len[m], woff[m]));
+    std::vector<int4> items;
+    for (int kind = 4; kind >= 1; kind >>= 1) {
+        std::vector<int> ms;
+        for (int m : order)
+            if (parts[m] == kind) ms.push_back(m);                         // `order` is by length, longest first
+        for (int m : ms) {
+            const int piece = (len[m] + kind - 1) / kind;
+            for (int i = 0; i < kind; ++i) {
+                const int o = std::min(len[m], i * piece), n = std::min(len[m], (i + 1) * piece) - o;
+                const int lg = kind == 4 ? 2 : (kind == 2 ? 1 : 0);
+                items.push_back(make_int4(m, lo[m] + o, n, (woff[m] + o) | (lg << 28) | (i ? (1 << 30) : 0)));
+            }
+        }
     }
     while ((int)items.size() < kEItems) items.push_back(make_int4(-1, 0, 0, 0));
-    // halves are now shorter than some unsplit filters: re-sort PAIRS of items by their longer member, keeping pairs together
-    {
-        std::vector<std::pair<int4, int4>> pairs;
-        for (int i = 0; i < kEItems; i += 2) pairs.emplace_back(items[i], items[i + 1]);
-        std::stable_sort(pairs.begin(), pairs.end(), [](const std::pair<int4, int4>& a, const std::pair<int4, int4>& b) {
-            return std::max(a.first.z, a.second.z) > std::max(b.first.z, b.second.z);
-        });
-        for (int i = 0; i < kEItems / 2; ++i) { items[2 * i] = pairs[i].first; items[2 * i + 1] = pairs[i].second; }
-    }
     pl->e_nwts = (int)w.size();
     pl->e_nxs = (kETF - 1) * pl->hop + 2048;
     pl->e_off_ex = (pl->e_nxs * 8 + 127) & ~127;

@@ -167,3 +167,30 @@ def test_second_configuration_from_one_read_of_the_audio(cuda_device):
     assert_logmel_close(lm2[0:1], O.log_mel({n: v[None] for n, v in clips[0].items()}, cfg, dtype=torch.float64), "second config")
     one = fe.features_and_logmel({n: v.to(cuda_device) for n, v in clips[1].items()}, second=(2048, 512, 80))
     assert one[0].shape == (64,) and torch.equal(one[0], f[1]) and torch.equal(one[2][0], lm2[1])
+
+
+@pytest.mark.parametrize("hop,n_mels,T", [(512, 80, 1025), (512, 80, 2047), (512, 80, 2048), (512, 80, 4097), (512, 80, 10240 + 3),
+                                          (512, 128, 30000), (256, 128, 9001), (1024, 64, 20000), (2048, 40, 33333), (512, 17, 8000),
+                                          (100, 80, 7000)])
+def test_k1e_lengths_hops_and_unaligned_views(cuda_device, hop, n_mels, T):
+    """K1E (log-mel of n_fft = 2048 plans; two warps per frame): clip lengths around its 4-frame tiles and the 1024-sample
+    reflect halo, hops that are multiples of 4, ragged filter counts, and views that start 1..3 floats into a wider
+    tensor (cooperative staging instead of TMA).  Against the fp64 oracle."""
+    cfg = O.FrontEndConfig(n_fft=2048, hop_length=hop, n_mels=n_mels)
+    clips = [O.musical_clip(500 + T % 97 + i, T) for i in range(2)]
+    off = 1 + T % 3
+    wide = torch.zeros(2, 8, T + 8, device=cuda_device)
+    for i, c in enumerate(clips):
+        for k, n in enumerate(O.STEMS):
+            wide[i, 2 * k:2 * k + 2, off:off + T] = c[n].to(cuda_device)
+    pre = pkg.MelSpectrogramPreprocessor(44100, 2048, hop, n_mels)
+    views = {n: wide[:, 2 * k:2 * k + 2, off:off + T] for k, n in enumerate(O.STEMS)}
+    n0 = pkg.launch_count()
+    lm_u = pre(views)
+    assert pkg.launch_count() == n0 + 1
+    lm_a = pre({n: v.contiguous() for n, v in views.items()})         # aligned copy: the TMA path
+    assert torch.equal(lm_u, lm_a)
+    assert lm_u.shape == (2, 8, n_mels, 1 + T // hop)
+    for i, c in enumerate(clips):
+        ref = O.log_mel({n: v[None] for n, v in c.items()}, cfg, dtype=torch.float64)
+        assert_logmel_close(lm_u[i:i + 1], ref, f"K1E hop={hop} n_mels={n_mels} T={T} clip {i}")
