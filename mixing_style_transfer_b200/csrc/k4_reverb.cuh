@@ -531,18 +531,21 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     auto carve = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_clips = carve(sizeof(AugClipDev) * B);
     const size_t o_sections = carve(sizeof(AugSection) * al.sections.size());
-    const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
     const size_t o_slots = carve(sizeof(int) * (size_t)std::max(1, n_slots));
+    const size_t o_tables = off;                                    // [0, o_tables) is uploaded from the host in one copy
+    const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
     const size_t o_X = carve(sizeof(float2) * (size_t)lay.n * n_slots * std::max(1, n_seg));
     const size_t o_H = carve(sizeof(float2) * (size_t)lay.n * n_slots);
     rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, al.clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size(),
-                               cudaMemcpyHostToDevice, stream));
-    if (n_slots)
-        MIXFE_CUDA(cudaMemcpyAsync(ws + o_slots, slot_clip.data(), sizeof(int) * n_slots, cudaMemcpyHostToDevice, stream));
+    ParamUpload up(pl, stream);
+    rc = up.reserve(o_tables);
+    if (rc) return rc;
+    if ((rc = up.stage(o_clips, al.clips.data(), sizeof(AugClipDev) * B))) return rc;
+    if ((rc = up.stage(o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size()))) return rc;
+    if ((rc = up.stage(o_slots, slot_clip.data(), sizeof(int) * (size_t)n_slots))) return rc;
+    if ((rc = up.upload(ws))) return rc;
 
     K3Params p3{};
     for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in[s]; p3.out[s] = out[s]; }
@@ -589,9 +592,12 @@ inline int run_effects(mixfe_plan* pl, const float* in, float* out, long long st
     rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_clips, al.clips.data(), sizeof(AugClipDev) * B, cudaMemcpyHostToDevice, stream));
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size(),
-                               cudaMemcpyHostToDevice, stream));
+    ParamUpload up(pl, stream);
+    rc = up.reserve(off);
+    if (rc) return rc;
+    if ((rc = up.stage(o_clips, al.clips.data(), sizeof(AugClipDev) * B))) return rc;
+    if ((rc = up.stage(o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size()))) return rc;
+    if ((rc = up.upload(ws))) return rc;
     K3Params p3{};
     for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in; p3.out[s] = out; }
     p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = al.chunk; p3.warm = al.warm;
@@ -632,7 +638,11 @@ inline int run_reverb(mixfe_plan* pl, const float* in, float* out, long long str
     int rc = ensure_workspace(pl, off, stream);
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
-    MIXFE_CUDA(cudaMemcpyAsync(ws + o_slots, slot_clip.data(), sizeof(int) * B, cudaMemcpyHostToDevice, stream));
+    ParamUpload up(pl, stream);
+    rc = up.reserve(sizeof(int) * (size_t)B);
+    if (rc) return rc;
+    if ((rc = up.stage(o_slots, slot_clip.data(), sizeof(int) * (size_t)B))) return rc;
+    if ((rc = up.upload(ws))) return rc;
     K4Params p4{};
     p4.out[0] = out;
     p4.stride_b = stride_b; p4.stride_c = stride_c; p4.T = T; p4.L = L; p4.half = L / 2; p4.seg_len = seg_len;

@@ -901,10 +901,13 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
-    cudaFree(pl->ws); cudaFree(pl->aug_params_dev);
+    cudaFree(pl->ws);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw); cudaFree(pl->d_eitems); cudaFree(pl->d_ewts);
-    if (pl->aug_params_host) cudaFreeHost(pl->aug_params_host);
+    for (int i = 0; i < mixfe_plan::kParamSlots; ++i) {
+        if (pl->param_done[i]) { cudaEventSynchronize(pl->param_done[i]); cudaEventDestroy(pl->param_done[i]); }
+        if (pl->param_host[i]) cudaFreeHost(pl->param_host[i]);
+    }
     delete pl;
     return MIXFE_OK;
 }

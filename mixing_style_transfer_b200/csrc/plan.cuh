@@ -1,6 +1,8 @@
 // The plan object behind the opaque mixfe_plan handle of include/mixfe.h.
 #pragma once
 
+#include <algorithm>
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -41,9 +43,14 @@ struct mixfe_plan {
     // plan-owned workspace (grows to the high-water mark, then never reallocates)
     void* ws = nullptr;
     size_t ws_bytes = 0;
-    void* aug_params_dev = nullptr;     // device copy of the per-clip augmentation decisions
-    void* aug_params_host = nullptr;    // pinned staging buffer for them
-    size_t aug_params_cap = 0;
+    // pinned staging ring for the per-call parameter tables (clip decisions, filter sections, reverb slots): a
+    // pageable cudaMemcpyAsync waits for the stream to drain before it copies, which serialises the host with
+    // the GPU once per call; a pinned source does not.  One slot per call in flight, guarded by an event.
+    static constexpr int kParamSlots = 8;
+    char* param_host[kParamSlots] = {};
+    size_t param_cap[kParamSlots] = {};
+    cudaEvent_t param_done[kParamSlots] = {};
+    int param_next = 0;
     // optional per-kernel timing (bench.py): event pairs recorded around launches, drained on query
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[MIXFE_NUM_KERNELS];
@@ -63,6 +70,47 @@ inline int ensure_workspace(mixfe_plan* pl, size_t bytes, cudaStream_t stream) {
     pl->ws_bytes = bytes;
     return MIXFE_OK;
 }
+
+// One call's parameter upload: take() hands out pinned bytes of the current ring slot (after the copy that last
+// used the slot has finished), upload() queues the copy to the device, and the destructor marks the slot busy
+// until the stream has passed the copies.
+struct ParamUpload {
+    mixfe_plan* pl;
+    cudaStream_t stream;
+    int slot;
+    size_t used = 0;
+    bool queued = false;
+    ParamUpload(mixfe_plan* p, cudaStream_t s) : pl(p), stream(s), slot(p->param_next) {
+        pl->param_next = (slot + 1) % mixfe_plan::kParamSlots;
+    }
+    int reserve(size_t bytes) {
+        if (pl->param_done[slot]) MIXFE_CUDA(cudaEventSynchronize(pl->param_done[slot]));
+        else MIXFE_CUDA(cudaEventCreateWithFlags(&pl->param_done[slot], cudaEventDisableTiming));
+        if (bytes > pl->param_cap[slot]) {
+            if (pl->param_host[slot]) MIXFE_CUDA(cudaFreeHost(pl->param_host[slot]));
+            pl->param_host[slot] = nullptr;
+            pl->param_cap[slot] = 0;
+            const size_t cap = (bytes + 65535) & ~(size_t)65535;
+            MIXFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pl->param_host[slot]), cap, cudaHostAllocDefault));
+            pl->param_cap[slot] = cap;
+        }
+        return MIXFE_OK;
+    }
+    // the tables of one call sit in the slot at the offsets they have in the device workspace, so that ONE copy moves them
+    int stage(size_t offset, const void* src, size_t bytes) {
+        if (offset + bytes > pl->param_cap[slot]) return fail(MIXFE_EINVAL, "parameter ring slot overrun");
+        std::memcpy(pl->param_host[slot] + offset, src, bytes);
+        used = std::max(used, offset + bytes);
+        return MIXFE_OK;
+    }
+    int upload(void* dst_base) {
+        if (!used) return MIXFE_OK;
+        MIXFE_CUDA(cudaMemcpyAsync(dst_base, pl->param_host[slot], used, cudaMemcpyHostToDevice, stream));
+        queued = true;
+        return MIXFE_OK;
+    }
+    ~ParamUpload() { if (queued) cudaEventRecord(pl->param_done[slot], stream); }
+};
 
 // RAII bracket: records an event pair around the launches issued in its scope when timing is on.
 struct KernelTimer {

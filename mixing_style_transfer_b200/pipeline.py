@@ -58,6 +58,7 @@ class HostPipeline:
         self.s_up = torch.cuda.Stream(self.device)
         self.s_run = torch.cuda.Stream(self.device)
         self.s_down = torch.cuda.Stream(self.device)
+        self._n_chunks_done = 0         # chunks queued so far, over all batches: slot = parity, waits from the third on
         self.h2d_bytes = 4 * 2 * T * 4 * n_clips
         self.d2h_bytes = 4 * n_clips * (self.plan.feature_dim + (8 * self.plan.n_mels * F if with_logmel else 0))
 
@@ -68,11 +69,24 @@ class HostPipeline:
     def run(self, host_stems: Dict[str, torch.Tensor], feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
         """host_stems: dict of pinned (N,2,T); feat_out pinned (N,D); lm_out pinned (N,8,n_mels,F) or None.
         Returns after everything has landed in host memory."""
+        self.wait(self.submit(host_stems, feat_out, lm_out))
+
+    @staticmethod
+    def wait(ticket: torch.cuda.Event) -> None:
+        """Block until the batch `submit` returned the ticket for has landed in its host buffers."""
+        ticket.synchronize()
+
+    def submit(self, host_stems: Dict[str, torch.Tensor], feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
+        """`run` without the final wait: queues the whole batch and returns a ticket for `wait`.  Submitting batch
+        k+1 before waiting for batch k lets its first upload run under batch k's last download (the two legs `run`
+        cannot overlap); the caller then owns two sets of host output buffers, as with any prefetching loader."""
         cur = torch.cuda.current_stream(self.device)
         for s in (self.s_up, self.s_run, self.s_down):
             s.wait_stream(cur)
-        for i, (lo, hi) in enumerate(self.bounds):
+        for (lo, hi) in self.bounds:
             m = hi - lo
+            i = self._n_chunks_done
+            self._n_chunks_done += 1
             slot = self.slots[i & 1]
             with torch.cuda.stream(self.s_up):
                 if i >= 2:
@@ -94,8 +108,9 @@ class HostPipeline:
                 if self.with_logmel:
                     lm_out[lo:hi].copy_(slot["lm"][:m], non_blocking=True)
                 slot["drained"].record(self.s_down)
-        self.s_down.synchronize()
-        self.s_run.synchronize()
+        ticket = torch.cuda.Event()
+        ticket.record(self.s_down)
+        return ticket
 
 
 class TripletPipeline:
@@ -138,6 +153,7 @@ class TripletPipeline:
         self.s_up = torch.cuda.Stream(self.device)
         self.s_run = torch.cuda.Stream(self.device)
         self.s_down = torch.cuda.Stream(self.device)
+        self._n_chunks_done = 0
         self.h2d_bytes = 4 * 2 * T * 4 * 2 * n_triplets
         self.d2h_bytes = 4 * 3 * n_triplets * (self.plan.feature_dim + (8 * self.plan.n_mels * F if with_logmel else 0))
 
@@ -145,14 +161,22 @@ class TripletPipeline:
         """host_stems: dict of pinned (2G,2,T), anchors then positives; decisions: G augmentation decisions (a list of
         ClipAugmentation or the BatchAugmentation of AudioAugmenter.draw_batch); feat_out pinned (3G,D); lm_out pinned
         (3G,8,n_mels,F) or None.  Returns after everything has landed in host memory."""
+        self.wait(self.submit(host_stems, decisions, feat_out, lm_out))
+
+    wait = staticmethod(HostPipeline.wait)
+
+    def submit(self, host_stems: Dict[str, torch.Tensor], decisions, feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
+        """`run` without the final wait (see HostPipeline.submit): returns a ticket for `wait`."""
         G = self.G
         if len(decisions) != G:
             raise ValueError(f"{len(decisions)} decisions for {G} anchors")
         cur = torch.cuda.current_stream(self.device)
         for s in (self.s_up, self.s_run, self.s_down):
             s.wait_stream(cur)
-        for i, (lo, hi) in enumerate(self.bounds):
+        for (lo, hi) in self.bounds:
             m = hi - lo
+            i = self._n_chunks_done
+            self._n_chunks_done += 1
             slot = self.slots[i & 1]
             with torch.cuda.stream(self.s_up):
                 if i >= 2:
@@ -179,5 +203,6 @@ class TripletPipeline:
                     if self.with_logmel:
                         lm_out[part * G + lo:part * G + hi].copy_(slot["lm"][part * m:(part + 1) * m], non_blocking=True)
                 slot["drained"].record(self.s_down)
-        self.s_down.synchronize()
-        self.s_run.synchronize()
+        ticket = torch.cuda.Event()
+        ticket.record(self.s_down)
+        return ticket
