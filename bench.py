@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default=os.environ.get("MIXFE_BENCH_WORKLOAD", "features_mel_aug"),
                     choices=["features_mel_aug", "features_mel", "sweep30s"])
-    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--e2e-steps", type=int, default=12)
     ap.add_argument("--sweep-clips", type=int, default=4096, help="sweep30s: clips in the whole job")
     ap.add_argument("--sweep-batch", type=int, default=24, help="sweep30s: resident clips per batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -45,9 +45,11 @@ struct mixfe_plan {
     size_t ws_bytes = 0;
     // pinned staging ring for the per-call parameter tables (clip decisions, filter sections, reverb slots): a
     // pageable cudaMemcpyAsync waits for the stream to drain before it copies, which serialises the host with
-    // the GPU once per call; a pinned source does not.  One slot per call in flight, guarded by an event.
+    // the GPU once per call; a pinned source does not.  One slot per call in flight, guarded by an event; the
+    // bytes reach the workspace through k_param_fetch (below), not through a copy engine.
     static constexpr int kParamSlots = 8;
     char* param_host[kParamSlots] = {};
+    char* param_host_dev[kParamSlots] = {};     // the same bytes as the device sees them (mapped)
     size_t param_cap[kParamSlots] = {};
     cudaEvent_t param_done[kParamSlots] = {};
     int param_next = 0;
@@ -71,6 +73,14 @@ inline int ensure_workspace(mixfe_plan* pl, size_t bytes, cudaStream_t stream) {
     return MIXFE_OK;
 }
 
+// Copies a call's parameter tables from mapped pinned host memory into the workspace with SM loads over PCIe.  A
+// cudaMemcpyAsync would do, but it rides the host-to-device copy engine, and when a pipeline keeps that engine busy
+// with waveform uploads on another stream the few KB of tables queue behind tens of MB (measured: the kernels of a
+// chunk started 0.5 ms late, scripts/e2e_timeline.py) -- a kernel on the compute stream has no such neighbour.
+__global__ void __launch_bounds__(256) k_param_fetch(uint4* __restrict__ dst, const uint4* __restrict__ src, int n16) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 // One call's parameter upload: take() hands out pinned bytes of the current ring slot (after the copy that last
 // used the slot has finished), upload() queues the copy to the device, and the destructor marks the slot busy
 // until the stream has passed the copies.
@@ -91,7 +101,8 @@ struct ParamUpload {
             pl->param_host[slot] = nullptr;
             pl->param_cap[slot] = 0;
             const size_t cap = (bytes + 65535) & ~(size_t)65535;
-            MIXFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pl->param_host[slot]), cap, cudaHostAllocDefault));
+            MIXFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pl->param_host[slot]), cap, cudaHostAllocMapped));
+            MIXFE_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&pl->param_host_dev[slot]), pl->param_host[slot], 0));
             pl->param_cap[slot] = cap;
         }
         return MIXFE_OK;
@@ -105,7 +116,11 @@ struct ParamUpload {
     }
     int upload(void* dst_base) {
         if (!used) return MIXFE_OK;
-        MIXFE_CUDA(cudaMemcpyAsync(dst_base, pl->param_host[slot], used, cudaMemcpyHostToDevice, stream));
+        const int n16 = (int)((used + 15) / 16);                 // slots and workspace offsets are 256-byte aligned
+        k_param_fetch<<<std::min(32, (n16 + 255) / 256), 256, 0, stream>>>(
+            reinterpret_cast<uint4*>(dst_base), reinterpret_cast<const uint4*>(pl->param_host_dev[slot]), n16);
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter()++;
         queued = true;
         return MIXFE_OK;
     }
