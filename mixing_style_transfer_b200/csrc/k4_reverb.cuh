@@ -177,34 +177,60 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
         }
     }
     // ---- stage N1 rows x kCols columns ------------------------------------------------------------
+    // Rows are taken kBatch at a time with every global load of the batch issued before the first use: a thread then
+    // has up to 32 loads in flight (r02w: one row at a time left the big passes waiting on the long scoreboard at
+    // ~25 % of the DRAM rate).  Out-of-range samples load a clamped address and are zeroed afterwards.
     {
+        constexpr int kRowStep = 256 / G::kCols, kBatch = 4;
+        static_assert(G::N1 % (kRowStep * kBatch) == 0, "row batches");
         const int c = tid % G::kCols;
-        for (int r = tid / G::kCols; r < G::N1; r += 256 / G::kCols) {
-            const long long n = (long long)r * kRevN2 + col0 + c;
-            float2 v = make_float2(0.0f, 0.0f);
-            if (MODE == kColsX) {
-                const long long t = seg0 - p.half + n;
-                if (t >= 0 && t < p.T) {
-                    const long long o = (long long)b * p.stride_b + t;
-                    float mL = 0.0f, mR = 0.0f;
-                    if (p.standalone) {
-                        mL = __ldg(p.sa_in + o);
-                        if (p.n_ch == 2) mR = __ldg(p.sa_in + o + p.stride_c);
-                    } else {
+        for (int r0 = tid / G::kCols; r0 < G::N1; r0 += kRowStep * kBatch) {
+            float2 v[kBatch];
+            if (MODE == kColsX && !p.standalone) {
+                float x[kBatch][2 * kNumStems];
+                bool ok[kBatch];
 #pragma unroll
-                        for (int s = 0; s < kNumStems; ++s) {          // ((0 + v) + b) + d) + o
-                            mL += p.out[s][o];
-                            mR += p.out[s][o + p.stride_c];
-                        }
+                for (int u = 0; u < kBatch; ++u) {
+                    const long long t = seg0 - p.half + (long long)(r0 + u * kRowStep) * kRevN2 + col0 + c;
+                    ok[u] = t >= 0 && t < p.T;
+                    const long long o = (long long)b * p.stride_b + (ok[u] ? t : 0);
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {
+                        x[u][2 * s] = p.out[s][o];
+                        x[u][2 * s + 1] = p.out[s][o + p.stride_c];
                     }
-                    v = make_float2(mL, mR);
                 }
-            } else if (MODE == kColsH) {
-                if (n < p.L) v.x = __ldg(p.impulse + (long long)b * p.imp_stride + n);
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) {
+                    float mL = 0.0f, mR = 0.0f;
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {              // ((0 + v) + b) + d) + o
+                        mL += x[u][2 * s];
+                        mR += x[u][2 * s + 1];
+                    }
+                    v[u] = ok[u] ? make_float2(mL, mR) : make_float2(0.0f, 0.0f);
+                }
             } else {
-                v = Xs[n];
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) {
+                    const long long n = (long long)(r0 + u * kRowStep) * kRevN2 + col0 + c;
+                    v[u] = make_float2(0.0f, 0.0f);
+                    if (MODE == kColsX) {
+                        const long long t = seg0 - p.half + n;
+                        if (t >= 0 && t < p.T) {
+                            const long long o = (long long)b * p.stride_b + t;
+                            v[u].x = __ldg(p.sa_in + o);
+                            if (p.n_ch == 2) v[u].y = __ldg(p.sa_in + o + p.stride_c);
+                        }
+                    } else if (MODE == kColsH) {
+                        if (n < p.L) v[u].x = __ldg(p.impulse + (long long)b * p.imp_stride + n);
+                    } else {
+                        v[u] = Xs[n];
+                    }
+                }
             }
-            tile[c * G::kStride + r] = v;
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) tile[c * G::kStride + r0 + u * kRowStep] = v[u];
         }
     }
     __syncthreads();
@@ -265,36 +291,58 @@ __global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params 
     __syncthreads();
     // ---- write back (coalesced runs of kCols elements) / reverb epilogue ------------------------------
     {
+        constexpr int kRowStep = 256 / G::kCols;
         const int c = tid % G::kCols;
-        for (int r = tid / G::kCols; r < G::N1; r += 256 / G::kCols) {
-            const long long n = (long long)r * kRevN2 + col0 + c;
-            const float2 v = tile[c * G::kStride + r];
-            if (MODE == kColsX) {
-                Xs[n] = v;
-            } else if (MODE == kColsH) {
-                Hs[n] = v;
-            } else {
-                const long long t = seg0 + n;                        // c[m] is the output sample seg0 + m
-                if (n < p.seg_len && t < p.T && p.standalone) {
+        if (MODE != kColsInv) {
+            float2* const dst = MODE == kColsX ? Xs : Hs;
+#pragma unroll 4
+            for (int r = tid / G::kCols; r < G::N1; r += kRowStep)
+                dst[(long long)r * kRevN2 + col0 + c] = tile[c * G::kStride + r];
+        } else if (p.standalone) {
+#pragma unroll 4
+            for (int r = tid / G::kCols; r < G::N1; r += kRowStep) {
+                const long long n = (long long)r * kRevN2 + col0 + c;
+                const long long t = seg0 + n;                            // c[m] is the output sample seg0 + m
+                const float2 v = tile[c * G::kStride + r];
+                if (n < p.seg_len && t < p.T) {
                     const long long o = (long long)b * p.stride_b + t;
                     p.out[0][o] = __ldg(p.sa_in + o) * 0.7f + v.x * 0.3f;                           // :478-479
                     if (p.n_ch == 2) p.out[0][o + p.stride_c] = __ldg(p.sa_in + o + p.stride_c) * 0.7f + v.y * 0.3f;
-                } else if (n < p.seg_len && t < p.T) {
-                    const long long o = (long long)b * p.stride_b + t;
-                    float y[kNumStems][2];
+                }
+            }
+        } else {
+            constexpr int kBatch = 2;                                    // 16 loads in flight, then 16 stores
+            for (int r0 = tid / G::kCols; r0 < G::N1; r0 += kRowStep * kBatch) {
+                float y[kBatch][kNumStems][2];
+                long long o[kBatch];
+                bool ok[kBatch];
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) {
+                    const long long n = (long long)(r0 + u * kRowStep) * kRevN2 + col0 + c;
+                    const long long t = seg0 + n;
+                    ok[u] = n < p.seg_len && t < p.T;
+                    o[u] = (long long)b * p.stride_b + (ok[u] ? t : 0);
+#pragma unroll
+                    for (int s = 0; s < kNumStems; ++s) {
+                        y[u][s][0] = p.out[s][o[u]];
+                        y[u][s][1] = p.out[s][o[u] + p.stride_c];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) {
+                    if (!ok[u]) continue;
+                    const float2 v = tile[c * G::kStride + r0 + u * kRowStep];
                     float mL = 0.0f, mR = 0.0f;
 #pragma unroll
                     for (int s = 0; s < kNumStems; ++s) {
-                        y[s][0] = p.out[s][o];
-                        y[s][1] = p.out[s][o + p.stride_c];
-                        mL += y[s][0];
-                        mR += y[s][1];
+                        mL += y[u][s][0];
+                        mR += y[u][s][1];
                     }
                     const float wetL = mL * 0.7f + v.x * 0.3f, wetR = mR * 0.7f + v.y * 0.3f;      // :478-479
 #pragma unroll
                     for (int s = 0; s < kNumStems; ++s) {
-                        p.out[s][o] = y[s][0] + (wetL * share[s]) * 0.3f;                       // :417
-                        p.out[s][o + p.stride_c] = y[s][1] + (wetR * share[s]) * 0.3f;
+                        p.out[s][o[u]] = y[u][s][0] + (wetL * share[s]) * 0.3f;                 // :417
+                        p.out[s][o[u] + p.stride_c] = y[u][s][1] + (wetR * share[s]) * 0.3f;
                     }
                 }
             }

@@ -45,7 +45,9 @@ for l in lines[start + 1:]:
         sass.append((m.group(2).strip(), list(chain)))
         fresh = True
 
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+# NCU_LAUNCH=<n>: the n-th captured launch of a report that holds several kernels (default: the first)
+sel = ["--launch-skip", os.environ["NCU_LAUNCH"], "--launch-count", "1"] if os.environ.get("NCU_LAUNCH") else []
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + sel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 hdr = rows[1]
 ia, isrc, isamp = hdr.index("Instructions Executed"), hdr.index("Source"), hdr.index("# Samples")
