@@ -105,16 +105,24 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
         const long long base = 256ll * t - 512 + lane;
         const bool inside = base - lane >= 0 && base - lane + 1024 <= (long long)p.T;
         float fl[32], fr[32];
+        if (inside) {                                    // interior frame: one pointer per row, immediate offsets
+            const float* const pl = gL + base;
+            const float* const pr = gR + base;
 #pragma unroll
-        for (int n1 = 0; n1 < 32; ++n1) {
-            long long j = base + 32 * n1;
-            if (!inside) {
+            for (int n1 = 0; n1 < 32; ++n1) {
+                fl[n1] = __ldg(pl + 32 * n1);
+                fr[n1] = __ldg(pr + 32 * n1);
+            }
+        } else {
+#pragma unroll
+            for (int n1 = 0; n1 < 32; ++n1) {
+                long long j = base + 32 * n1;
                 if (j < 0) j = -j;
                 if (j >= p.T) j = 2ll * (p.T - 1) - j;
                 j = j < 0 ? 0 : (j >= p.T ? p.T - 1 : j);
+                fl[n1] = __ldg(gL + j);
+                fr[n1] = __ldg(gR + j);
             }
-            fl[n1] = __ldg(gL + j);
-            fr[n1] = __ldg(gR + j);
         }
 #pragma unroll
         for (int n1 = 0; n1 < 32; ++n1) {
@@ -159,55 +167,54 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
                 //      G_L = 2 L dP_L, G_R = 2 R dP_R; the inverse transform's conjugated input is
                 //      (a - di, -(bi + c)) / 2 at k and (a + di, -(c - bi)) / 2 at 1024 - k; (a, -c) at k = 0 and 512.
                 const int src = (32 - lane) & 31;
+                const bool l0 = lane == 0;
                 const float2* dm = dmel + warp * dm_stride;
-                // One slot: own value o = X[kap], partner q = X[1024 - kap]  ->  conjugated inverse-transform input at kap.
-                auto grad_slot = [&](int k2, cplx64 o, cplx64 q) -> cplx64 {
-                    float ox, oy, qx, qy;
-                    cunpack(o, ox, oy);
-                    cunpack(q, qx, qy);
-                    const int kap = lane + 32 * k2;
-                    const bool lower = kap <= 512;
-                    const int kk = lower ? kap : 1024 - kap;
-                    const float xx = lower ? ox : qx, xy = lower ? oy : qy;          // X[kk]
-                    const float yx = lower ? qx : ox, yy = lower ? qy : oy;          // X[1024 - kk]
+                // One PAIR of bins per evaluation: o = X[kk] (kk <= 512), q = X[1024 - kk]  ->  the conjugated inverse-
+                // transform inputs at kk (lo) and at 1024 - kk (hi).  With xa.. as above and the factors 2 and 1/2 folded:
+                //   lo = ( xa dL + xc dR, -(xb dL + xd dR) ),   hi = ( xa dL - xc dR, xb dL - xd dR ).
+                auto grad_pair = [&](int kk, cplx64 o, cplx64 q, cplx64& lo, cplx64& hi) {
+                    float xx, xy, yx, yy;
+                    cunpack(o, xx, xy);
+                    cunpack(q, yx, yy);
                     const float4 bw = binw[kk];
                     const int m0 = __float_as_int(bw.x);
                     const float2 d0 = dm[m0], d1 = dm[m0 + 1];
                     const float dL = fmaf(bw.y, d0.x, bw.z * d1.x), dR = fmaf(bw.y, d0.y, bw.z * d1.y);
                     const float xa = xx + yx, xb = xy - yy, xc = xx - yx, xd = xy + yy;
-                    const float a = 2.0f * xa * dL, bi = 2.0f * xb * dL;
-                    const float c = 2.0f * xd * dR, di = -2.0f * xc * dR;
-                    float rx, ry;
-                    if (kk == 0 || kk == 512) { rx = a; ry = -c; }
-                    else if (lower) { rx = 0.5f * (a - di); ry = -0.5f * (bi + c); }
-                    else { rx = 0.5f * (a + di); ry = -0.5f * (c - bi); }
-                    return cpack(rx, ry);
+                    const float pa = xa * dL, pb = xb * dL;
+                    lo = cpack(fmaf(xc, dR, pa), -fmaf(xd, dR, pb));
+                    hi = cpack(fmaf(-xc, dR, pa), fmaf(-xd, dR, pb));
                 };
                 auto shfl_c = [&](cplx64 v) -> cplx64 {
                     float x, y;
                     cunpack(v, x, y);
                     return cpack(__shfl_sync(kFullMask, x, src), __shfl_sync(kFullMask, y, src));
                 };
-                // Slots k2 and 31 - k2 are each other's partners (in the partner lane): handled as a pair, results in place.
-                // Lane 0 pairs with itself: slot k2 with slot (32 - k2) & 31 -- the previous pair's second value, saved --
-                // and slot 31 - k2 with slot k2 + 1, not yet overwritten.
-                cplx64 prev_o2 = 0ull;
-#pragma unroll
-                for (int k2 = 0; k2 < 16; ++k2) {
-                    const cplx64 o1 = z[brev5(k2)], o2 = z[brev5(31 - k2)];
-                    cplx64 q1 = shfl_c(o2), q2 = shfl_c(o1);
-                    if (lane == 0) {
-                        q1 = k2 == 0 ? o1 : prev_o2;
-                        q2 = z[brev5(k2 + 1)];
-                    }
-                    prev_o2 = o2;
-                    z[brev5(k2)] = grad_slot(k2, o1, q1);
-                    z[brev5(31 - k2)] = grad_slot(31 - k2, o2, q2);
-                }
-                // natural slot order for the second transform (slot k2 <- register brev5(k2))
+                auto twice = [](cplx64 v) -> cplx64 {
+                    float x, y;
+                    cunpack(v, x, y);
+                    return cpack(2.0f * x, 2.0f * y);
+                };
+                // Slot k2 <= 15 of every lane is the lower member of a pair; the upper member sits in the partner lane's
+                // slot 31 - k2 and receives `hi` by shuffle.  Lane 0 pairs with itself, slot k2 with slot 32 - k2: it feeds
+                // its own slot 32 - k2 as the partner value and files what comes back one slot later (carry); its slots 0
+                // and 16 (bins 0 and 512) are their own partners and take twice the `lo` value.
                 cplx64 zn[32];
+                cplx64 carry, unused;
+                grad_pair(512, z[brev5(16)], z[brev5(16)], carry, unused);
+                carry = twice(carry);
 #pragma unroll
-                for (int k2 = 0; k2 < 32; ++k2) zn[k2] = z[brev5(k2)];
+                for (int k2 = 15; k2 >= 0; --k2) {
+                    const cplx64 o = z[brev5(k2)];
+                    const cplx64 q = shfl_c(l0 ? z[brev5((32 - k2) & 31)] : z[brev5(31 - k2)]);
+                    cplx64 lo, hi;
+                    grad_pair(lane + 32 * k2, o, q, lo, hi);
+                    const cplx64 recv = shfl_c(hi);
+                    zn[k2] = (k2 == 0 && l0) ? twice(lo) : lo;
+                    zn[31 - k2] = l0 ? carry : recv;
+                    carry = recv;
+                }
+                // natural slot order for the second transform
 #pragma unroll
                 for (int k2 = 0; k2 < 32; ++k2) z[k2] = zn[k2];
             }
