@@ -73,38 +73,16 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
     for (int i = tid; i < 31 * 32; i += kBwThreads) tw[i] = p.tw[32 + i];
     for (int i = tid; i < kNfreq; i += kBwThreads) binw[i] = p.binw[i];
     for (int i = tid; i < kBwSpan; i += kBwThreads) ola[i] = make_float2(0.0f, 0.0f);
-    // ---- dmel of the 16 frames: thread = (frame, filter) with the frame fastest (64-byte runs along time) ----------
-    {
-        const float* gb = p.g + (long long)b * p.g_stride_b + (long long)(2 * s) * p.n_mels * p.F;
-        const float* lb = p.lm + (long long)b * p.lm_stride_b + (long long)(2 * s) * p.n_mels * p.F;
-        const long long chs = (long long)p.n_mels * p.F;
-        for (int idx = tid; idx < kBwWarps * dm_stride; idx += kBwThreads) {
-            const int f = idx & (kBwWarps - 1), m = idx >> 4;
-            const int t = t_first + f;
-            float2 v = make_float2(0.0f, 0.0f);
-            if (m < p.n_mels && t >= 0 && t < p.F) {
-                const long long o = (long long)m * p.F + t;
-                v.x = __ldg(gb + o) * __expf(-__ldg(lb + o));
-                v.y = __ldg(gb + chs + o) * __expf(-__ldg(lb + chs + o));
-            }
-            dmel[f * dm_stride + m] = v;
-        }
-    }
-    __syncthreads();
-
+    // ---- this warp's frame -> registers with torch's 'reflect' indexing.  Issued BEFORE the dmel stage so that the 64
+    //      loads fly under it (one CTA per SM: nothing else hides their latency) -----------------------------------------
     const int t = t_first + warp;                        // this warp's frame
     const bool active = t >= 0 && t < p.F;
-    float2* const exw = reinterpret_cast<float2*>(ex + warp * kWarpRegion);
-    cplx64 z[32];
+    float fl[32], fr[32];
     if (active) {
-        // ---- frame -> registers with torch's 'reflect' indexing, Hann window on the fly (as K1) --------------------
         const float* gL = p.stem[s] + (long long)b * p.stride_b;
         const float* gR = gL + p.stride_c;
-        const float2 wl = tw[lane];
-        const float cb = wl.x, sb = -wl.y;
         const long long base = 256ll * t - 512 + lane;
         const bool inside = base - lane >= 0 && base - lane + 1024 <= (long long)p.T;
-        float fl[32], fr[32];
         if (inside) {                                    // interior frame: one pointer per row, immediate offsets
             const float* const pl = gL + base;
             const float* const pr = gR + base;
@@ -124,6 +102,33 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
                 fr[n1] = __ldg(gR + j);
             }
         }
+    }
+    // ---- dmel of the 16 frames: thread = (frame, filter) with the frame fastest (64-byte runs along time) ----------
+    {
+        const float* const gbL = p.g + (long long)b * p.g_stride_b + (long long)(2 * s) * p.n_mels * p.F;
+        const float* const lbL = p.lm + (long long)b * p.lm_stride_b + (long long)(2 * s) * p.n_mels * p.F;
+        const float* const gbR = gbL + (long long)p.n_mels * p.F;
+        const float* const lbR = lbL + (long long)p.n_mels * p.F;
+        for (int idx = tid; idx < kBwWarps * dm_stride; idx += kBwThreads) {
+            const int f = idx & (kBwWarps - 1), m = idx >> 4;
+            const int tf = t_first + f;
+            float2 v = make_float2(0.0f, 0.0f);
+            if (m < p.n_mels && tf >= 0 && tf < p.F) {
+                const int o = m * p.F + tf;                              // one (clip, channel) plane: fits an int
+                v.x = __ldg(gbL + o) * __expf(-__ldg(lbL + o));
+                v.y = __ldg(gbR + o) * __expf(-__ldg(lbR + o));
+            }
+            dmel[f * dm_stride + m] = v;
+        }
+    }
+    __syncthreads();
+
+    float2* const exw = reinterpret_cast<float2*>(ex + warp * kWarpRegion);
+    cplx64 z[32];
+    if (active) {
+        // ---- Hann window on the fly (as K1) -----------------------------------------------------------------------------
+        const float2 wl = tw[lane];
+        const float cb = wl.x, sb = -wl.y;
 #pragma unroll
         for (int n1 = 0; n1 < 32; ++n1) {
             const float ca = n1 < 16 ? w32_re(n1) : -w32_re(n1 - 16);
@@ -248,6 +253,20 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
     {
         float* dL = p.out[s] + (long long)b * p.ostride_b;
         float* dR = dL + p.ostride_c;
+        const long long first = p0 + 768;                            // padded position of the first owned sample
+        const bool interior = first >= kBwEdge && first + kBwOwn * 256 <= (long long)p.T - kBwEdge
+                              && ((reinterpret_cast<unsigned long long>(dL + first) | reinterpret_cast<unsigned long long>(dR + first)) & 15) == 0;
+        if (interior) {                                              // no reflection, no strip: four samples per thread
+            float4* const vL = reinterpret_cast<float4*>(dL + first);
+            float4* const vR = reinterpret_cast<float4*>(dR + first);
+            const float4* const src4 = reinterpret_cast<const float4*>(ola + 768);
+            for (int i = tid; i < kBwOwn * 64; i += kBwThreads) {
+                const float4 a = src4[2 * i], c = src4[2 * i + 1];   // (L0 R0 L1 R1), (L2 R2 L3 R3)
+                vL[i] = make_float4(a.x, a.z, c.x, c.z);
+                vR[i] = make_float4(a.y, a.w, c.y, c.w);
+            }
+            return;
+        }
         for (int i = tid; i < kBwOwn * 256; i += kBwThreads) {
             const int o = 768 + i;
             const long long pp = p0 + o;                              // padded position
