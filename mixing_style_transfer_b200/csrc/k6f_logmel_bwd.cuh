@@ -72,7 +72,6 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
 
     for (int i = tid; i < 31 * 32; i += kBwThreads) tw[i] = p.tw[32 + i];
     for (int i = tid; i < kNfreq; i += kBwThreads) binw[i] = p.binw[i];
-    for (int i = tid; i < kBwSpan; i += kBwThreads) ola[i] = make_float2(0.0f, 0.0f);
     // ---- this warp's frame -> registers with torch's 'reflect' indexing.  Issued BEFORE the dmel stage so that the 64
     //      loads fly under it (one CTA per SM: nothing else hides their latency) -----------------------------------------
     const int t = t_first + warp;                        // this warp's frame
@@ -225,25 +224,33 @@ __global__ void __launch_bounds__(kBwThreads, 1) k6f_logmel_bwd(const __grid_con
             }
         }
     }
-    // ---- window, overlap-add: frames 4 apart do not overlap, so the 16 warps add in 4 turns ---------------------------
+    // ---- window, overlap-add.  Quarter q of frame w lands in hop region w + q, so in turn q every warp adds its q-th
+    //      quarter and no two warps meet (all 16 warps busy in every turn; the first cut let 4 of 16 work per turn).
+    //      Turn 0 is the first writer of every region and stores (no zero-fill); regions outside the 13 owned ones
+    //      (3 .. 15) are never read and are skipped. -----------------------------------------------------------------------
     {
         const float2 wl = tw[lane];
         const float cb = wl.x, sb = -wl.y;
         float2* const dst = ola + 256 * warp + lane;
-#pragma unroll 1
-        for (int turn = 0; turn < 4; ++turn) {
-            if (active && (warp & 3) == turn) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
+        for (int q = 0; q < 4; ++q) {
+            const int h = warp + q;
+            if (h >= 3 && h < 3 + kBwOwn) {
+#pragma unroll
+                for (int j = 8 * q; j < 8 * q + 8; ++j) {
                     const float ca = j < 16 ? w32_re(j) : -w32_re(j - 16);
                     const float sa = j < 16 ? w32_sin(j) : -w32_sin(j - 16);
                     const float hw = fmaf(0.5f * sa, sb, fmaf(-0.5f * ca, cb, 0.5f));             // hann[32 j + lane]
                     float rx, ry;
                     cunpack(z[brev5(j)], rx, ry);
-                    float2 acc = dst[32 * j];
-                    acc.x = fmaf(hw, rx, acc.x);
-                    acc.y = fmaf(-hw, ry, acc.y);
-                    dst[32 * j] = acc;
+                    if (q == 0) {
+                        dst[32 * j] = active ? make_float2(hw * rx, -hw * ry) : make_float2(0.0f, 0.0f);
+                    } else if (active) {
+                        float2 acc = dst[32 * j];
+                        acc.x = fmaf(hw, rx, acc.x);
+                        acc.y = fmaf(-hw, ry, acc.y);
+                        dst[32 * j] = acc;
+                    }
                 }
             }
             __syncthreads();
