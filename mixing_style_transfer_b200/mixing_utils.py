@@ -110,19 +110,20 @@ class MixingFeatureExtractor:
         return feats
 
     # -- additive API ----------------------------------------------------------------------
-    def features_and_logmel(self, stems_dict, second=None, chunk_clips: int = 4):
+    def features_and_logmel(self, stems_dict, second=None, chunk_clips: Optional[int] = None):
         """One fused pass: (features (D,)|(B,D), logmel (B,8,n_mels,F)) -- the encoder's
         MelSpectrogramPreprocessor output (src/model.py:41-67) for the same (n_fft, hop, n_mels).
 
         second = (n_fft2, hop2, n_mels2): ALSO the log-mel of a second STFT configuration -- the reference trains its
         encoder on (2048, 512, 80) while the extractor keeps its own triple (src/train_style_transfer.py:523-533,
-        scripts/train_baseline.sh:42-44) -- from ONE read of the audio out of HBM: the batch is walked in chunks of
-        `chunk_clips` clips (56 MB of 10 s audio at the default, well inside the 126 MB L2) and the second
-        configuration's kernel runs on each chunk right behind the first one's, so its loads hit L2 (measured on 72 x 10 s
-        clips, profiles/r02n_two_config_traffic.txt: 1.20 GB read from DRAM instead of 2.07 GB; 6.3 ms instead of 5.3 ms
-        for two whole-batch passes, which `chunk_clips=None` selects -- small launches fill the GPU less well).  Returns
-        (features, logmel, logmel2 (B,8,n_mels2,F2)).  (Two kernels sharing the samples through L2, not one kernel
-        sharing them through shared memory; DESIGN.md section 4, K1G, says what that would take.)"""
+        scripts/train_baseline.sh:42-44).  Returns (features, logmel, logmel2 (B,8,n_mels2,F2)).
+        Default (`chunk_clips=None`): two whole-batch passes, the fastest (72 x 10 s clips: 3.65 ms; neither kernel is
+        bound by HBM, so reading the audio twice costs nothing).  `chunk_clips=n` walks the batch n clips at a time with
+        the second configuration's kernel right behind the first one's on each chunk: with 4 clips (56 MB of 10 s
+        audio, inside the 126 MB L2) the second kernel's loads mostly hit L2 (1.41 GB read from
+        DRAM instead of 2.07 GB, profiles/r03b_two_config_traffic.txt) at 4.76 ms -- small launches fill the GPU less
+        well; the mode for a pipeline whose other kernels need the HBM bandwidth.  (Two kernels sharing the samples
+        through L2, not one kernel sharing them through shared memory)"""
         if second is None:
             return self._run(stems_dict, True, True)
         first = stems_dict[STEMS[0]]
