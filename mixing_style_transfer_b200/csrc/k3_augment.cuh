@@ -77,6 +77,7 @@ struct K3Params {
     float* out[kNumStems];
     long long stride_b, stride_c;
     int B, T, chunk, warm, n_chunks, n_stems;
+    int stem_in_y;                         // 1: one-warp CTAs, grid.y = 2 * stem + channel; 0: warp = stem, grid.y = channel
     const AugClipDev* clips;
     const AugSection* sections;            // [B][kNumStems][kAugSections]
     double* part_energy;                   // [B][4][2][n_chunks], or NULL
@@ -208,13 +209,15 @@ __global__ void __launch_bounds__(kAugWarps * 32, MIXFE_K3_CTAS) k3_augment(cons
     __shared__ __align__(16) AugWarpState state[kAugWarps][kAugSections];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // one warp per (chunk, channel, clip, stem): the warps of a CTA take the stems of one chunk
+    // (stem_in_y: one-warp CTAs, the stem rides in blockIdx.y -- a finished warp then frees its registers at once instead
+    // of waiting for the slowest of four stems whose effect chains differ by up to 4x)
     const int chunk = blockIdx.x;
-    const int ch = blockIdx.y, b = blockIdx.z;
+    const int ch = p.stem_in_y ? (int)(blockIdx.y & 1) : (int)blockIdx.y, b = blockIdx.z;
     const AugClipDev& cp = p.clips[b];
     const long long row = (long long)b * p.stride_b + (long long)ch * p.stride_c;
     const long long c0 = (long long)chunk * p.chunk;
     const long long c1 = c0 + p.chunk < p.T ? c0 + p.chunk : p.T;
-    const int s = warp;
+    const int s = p.stem_in_y ? (int)(blockIdx.y >> 1) : warp;
     if (s >= p.n_stems) return;
 
     // (selects, not p.in[s]: a runtime index into kernel parameters would copy them to local memory)

@@ -603,7 +603,10 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     p3.part_energy = reinterpret_cast<double*>(ws + o_energy);
     {
         KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
-        k3_augment<<<dim3(n_chunks, 2, B), kAugWarps * 32, 0, stream>>>(p3);
+        static const bool split = !(std::getenv("MIXFE_K3_SPLIT") && std::atoi(std::getenv("MIXFE_K3_SPLIT")) == 0);
+        p3.stem_in_y = split ? 1 : 0;
+        if (split) k3_augment<<<dim3(n_chunks, 2 * kNumStems, B), 32, 0, stream>>>(p3);
+        else k3_augment<<<dim3(n_chunks, 2, B), kAugWarps * 32, 0, stream>>>(p3);
     }
     MIXFE_CUDA(cudaGetLastError());
     launch_counter()++;
