@@ -95,15 +95,21 @@ struct ParamUpload {
     }
     int reserve(size_t bytes) {
         if (pl->param_done[slot]) MIXFE_CUDA(cudaEventSynchronize(pl->param_done[slot]));
-        else MIXFE_CUDA(cudaEventCreateWithFlags(&pl->param_done[slot], cudaEventDisableTiming));
+        // every slot is (re)sized together, on the first call that needs the size: cudaHostAlloc takes a millisecond and
+        // waits for the device, which must not happen in call 6, 7, 8 of a steady-state loop that warmed up for 5
         if (bytes > pl->param_cap[slot]) {
-            if (pl->param_host[slot]) MIXFE_CUDA(cudaFreeHost(pl->param_host[slot]));
-            pl->param_host[slot] = nullptr;
-            pl->param_cap[slot] = 0;
             const size_t cap = (bytes + 65535) & ~(size_t)65535;
-            MIXFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pl->param_host[slot]), cap, cudaHostAllocMapped));
-            MIXFE_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&pl->param_host_dev[slot]), pl->param_host[slot], 0));
-            pl->param_cap[slot] = cap;
+            for (int i = 0; i < mixfe_plan::kParamSlots; ++i) {
+                if (pl->param_cap[i] >= cap) continue;
+                if (pl->param_done[i]) MIXFE_CUDA(cudaEventSynchronize(pl->param_done[i]));
+                else MIXFE_CUDA(cudaEventCreateWithFlags(&pl->param_done[i], cudaEventDisableTiming));
+                if (pl->param_host[i]) MIXFE_CUDA(cudaFreeHost(pl->param_host[i]));
+                pl->param_host[i] = nullptr;
+                pl->param_cap[i] = 0;
+                MIXFE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&pl->param_host[i]), cap, cudaHostAllocMapped));
+                MIXFE_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&pl->param_host_dev[i]), pl->param_host[i], 0));
+                pl->param_cap[i] = cap;
+            }
         }
         return MIXFE_OK;
     }
