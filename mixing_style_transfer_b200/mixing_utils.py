@@ -324,11 +324,28 @@ def butter_sos_batch(order: int, cutoff_hz, btype: str, fs: float):
         gain = (1.0 / np.prod(-p)).real * ((4.0 ** order) / gain_den).real
         zsign = -1.0
     sos = np.zeros((wn.size, order // 2, 6))
-    for i in range(wn.size):
-        upper = sorted([q for q in pz[i] if q.imag > 0], key=abs)
-        for j, q in enumerate(upper):
-            sos[i, j] = [1.0, 2.0 * zsign, 1.0, 1.0, -2.0 * q.real, abs(q) ** 2]
-        sos[i, 0, :3] *= gain[i]
+    if wn.size == 0:
+        return sos
+    # The bilinear map keeps a pole's half plane and orders the radii by the prototype's real parts, so the columns of the
+    # upper-half-plane poles and their order by radius are the same for every cutoff: take them from the first row ...
+    cols = np.nonzero(pz[0].imag > 0)[0]
+    cols = cols[np.argsort(np.abs(pz[0, cols]))]
+    q = pz[:, cols]
+    rad = np.abs(q)
+    if cols.size != order // 2 or not ((pz[:, cols].imag > 0).all() and (np.diff(rad, axis=1) > 0).all()):
+        for i in range(wn.size):                         # ... and fall back to the per-row sort if that ever fails
+            upper = sorted([v for v in pz[i] if v.imag > 0], key=abs)
+            for j, v in enumerate(upper):
+                sos[i, j] = [1.0, 2.0 * zsign, 1.0, 1.0, -2.0 * v.real, abs(v) ** 2]
+            sos[i, 0, :3] *= gain[i]
+        return sos
+    sos[:, :, 0] = 1.0
+    sos[:, :, 1] = 2.0 * zsign
+    sos[:, :, 2] = 1.0
+    sos[:, :, 3] = 1.0
+    sos[:, :, 4] = -2.0 * q.real
+    sos[:, :, 5] = rad ** 2
+    sos[:, 0, :3] *= gain[:, None]
     return sos
 
 
