@@ -145,8 +145,16 @@ struct K4Params {
 enum { kColsX = 0, kColsH = 1, kColsInv = 2 };
 
 // grid (1024 / kCols column groups, n_seg, n_slots); 8 warps, warp w transforms column(s) kColsPerWarp * w (+ 1) of the group.
+// Register targets of the reverb passes, measured through MIXFE_LIB variants (12 reverbs of the bench step): rows / cols
+// = 1 / 2 -> 0.306 ms, 1 / 1 -> 0.336, 2 / 1 -> 0.363, 1 / 3 -> 0.378, 2 / 3 -> 0.410, no bound (as before) -> 0.355.
+#ifndef MIXFE_K4_ROWS_CTAS
+#define MIXFE_K4_ROWS_CTAS 1            // resident CTAs per SM the register allocation of the row pass aims at
+#endif
+#ifndef MIXFE_K4_COLS_CTAS
+#define MIXFE_K4_COLS_CTAS 2            // same for the column passes (74 KB of tile each)
+#endif
 template <int MODE, int LOG1>
-__global__ void __launch_bounds__(256) k4_cols(const __grid_constant__ K4Params p) {
+__global__ void __launch_bounds__(256, MIXFE_K4_COLS_CTAS) k4_cols(const __grid_constant__ K4Params p) {
     using G = RevGeom<LOG1>;
     constexpr int N = G::N1 * kRevN2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -354,7 +362,7 @@ enum { kRowsX = 0, kRowsH = 1 };
 
 // grid (N1 / 8 row groups, n_seg, n_slots); 8 warps, warp w transforms row 8*group + w (1024 points).
 template <int MODE, int LOG1>
-__global__ void __launch_bounds__(256) k4_rows(const __grid_constant__ K4Params p) {
+__global__ void __launch_bounds__(256, MIXFE_K4_ROWS_CTAS) k4_rows(const __grid_constant__ K4Params p) {
     using G = RevGeom<LOG1>;
     constexpr int N = G::N1 * kRevN2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
