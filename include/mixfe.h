@@ -154,6 +154,19 @@ int mixfe_weighted_masking(mixfe_plan* plan, const float* logmel, long long logm
                            const float* band_weights, double band_weight_sum, float beta, float tau, float* out,
                            void* cuda_stream);
 
+/* NO COUNTERPART IN THE REFERENCE.  mixfe_weighted_masking for callers that
+ * must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): same
+ * arguments, same two launches, same result, but the partial sums the two launches exchange live in a static 256 KB
+ * device array inside libmixfe (held by every GPU that loads the library until exit) instead of the plan's workspace.
+ * The call allocates nothing (no cudaMalloc / cudaFree / events; the plan is only read).
+ * Limit: B * ceil((1 + T / hop) / 128) <= MIXFE_NOALLOC_MASKING_MAX_BLOCKS, else MIXFE_EUNSUPPORTED (e.g. 10 s clips at
+ * hop 256: 14 blocks per clip, 585 clips per call).  ALL calls on one GPU share the array: calls that overlap on the GPU
+ * (different streams, or graphs replayed concurrently) race; serialise them.  Nothing in it needs clearing between calls. */
+#define MIXFE_NOALLOC_MASKING_MAX_BLOCKS 8192
+int mixfe_weighted_masking_noalloc(mixfe_plan* plan, const float* logmel, long long logmel_stride_b, int B, int T,
+                                   const float* band_weights, double band_weight_sum, float beta, float tau, float* out,
+                                   void* cuda_stream);
+
 /* EXTENSION (same status): a compressor with an envelope follower, which the brief names and the reference does not have
  * (its apply_compression is memoryless, src/mixing_utils.py:435-447).  Decoupled smooth peak detector (Giannoulis,
  * Massberg, Reiss, JAES 2012): p[n] = max(|x[n]|, release_coeff p[n-1]); s[n] = attack_coeff s[n-1] + (1 - attack_coeff) p[n];

@@ -79,7 +79,8 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_enable_timing", "mixfe_plan_kernel_time", "mixfe_debug_feature_kernel_config",
            "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
            "mixfe_stft_loss_forward", "mixfe_stft_loss_backward", "mixfe_plan_create_augment", "mixfe_effects",
-           "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress", "mixfe_push_peers")
+           "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress", "mixfe_push_peers",
+           "mixfe_weighted_masking_noalloc")
 
 
 def lib() -> ctypes.CDLL:
@@ -118,6 +119,7 @@ def lib() -> ctypes.CDLL:
         L.mixfe_effects.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, ctypes.POINTER(AugParams), vp]
         L.mixfe_reverb.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, vp, ll, ci, vp]
         L.mixfe_weighted_masking.argtypes = [vp, vp, ll, ci, ci, vp, ctypes.c_double, ctypes.c_float, ctypes.c_float, vp, vp]
+        L.mixfe_weighted_masking_noalloc.argtypes = L.mixfe_weighted_masking.argtypes
         L.mixfe_envelope_compress.argtypes = [vp, vp, vp, ll, ll, ci, ci, ci, ctypes.c_float, ctypes.c_float, ctypes.c_float,
                                               ctypes.c_float, vp]
         L.mixfe_launch_count.restype = ll

@@ -51,8 +51,31 @@ __global__ void __launch_bounds__(kPushThreads) k11_push_peers(const __grid_cons
     }
 }
 
+// Scratch of mixfe_weighted_masking_noalloc: the per-(clip, 128-frame block) partial sums K9 exchanges between its two
+// launches, held in the library image instead of the plan's cudaMalloc'ed workspace.  256 KB on every GPU that loads
+// libmixfe, until exit.  This name is a HOST-SIDE STAND-IN in host code: the device address comes from
+// cudaGetSymbolAddress (noalloc_setup below, once per device with that device current) and only that goes to a kernel.
+constexpr int kNoAllocMaskEntries = MIXFE_NOALLOC_MASKING_MAX_BLOCKS;
+static __device__ __align__(256) float g_noalloc_mask_part[kNoAllocMaskEntries * 8];
 
 namespace {
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_part[kNoAllocMaxDevices] = {};      // device address of g_noalloc_mask_part per device ordinal
+
+// Set-up half (called from mixfe_plan_create with `device` current): resolve the array's address on this device once.
+int noalloc_setup(int device) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return MIXFE_OK;     // such a device simply has no no-alloc entry
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_part[device]) return MIXFE_OK;
+    float* ptr = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_mask_part);
+    if (err != cudaSuccess || !ptr)
+        return fail(MIXFE_ECUDA, "cudaGetSymbolAddress(g_noalloc_mask_part) on device %d: %s", device, cudaGetErrorString(err));
+    g_noalloc_part[device] = ptr;
+    return MIXFE_OK;
+}
 
 template <class T>
 int upload(T** dst, const std::vector<T>& v) {
@@ -870,6 +893,7 @@ int mixfe_plan_create(mixfe_plan** out, int device, int sample_rate, int n_fft, 
     pl->fb = default_filterbank(sample_rate, n_fft, n_mels);
     int rc = upload_fft_twiddles(pl);
     if (!rc) rc = build_tables(pl);
+    if (!rc) rc = noalloc_setup(device);                 // address of the static scratch of mixfe_weighted_masking_noalloc
     if (rc) { mixfe_plan_destroy(pl); return rc; }
     *out = pl;
     return MIXFE_OK;
@@ -1060,6 +1084,47 @@ int mixfe_weighted_masking(mixfe_plan* pl, const float* logmel, long long logmel
                            void* cuda_stream) {
     return run_weighted_masking(pl, logmel, logmel_stride_b, B, T, band_weights, band_weight_sum, beta, tau, out,
                                 static_cast<cudaStream_t>(cuda_stream));
+}
+
+// mixfe_weighted_masking without any allocation: same two K9 launches, partial sums in g_noalloc_mask_part.  No
+// cudaMalloc / cudaFree / event creation / workspace growth here or below; the plan is only read.
+int mixfe_weighted_masking_noalloc(mixfe_plan* pl, const float* logmel, long long logmel_stride_b, int B, int T,
+                                   const float* band_weights, double band_weight_sum, float beta, float tau, float* out,
+                                   void* cuda_stream) {
+    if (!pl || !logmel || !band_weights || !out) return fail(MIXFE_EINVAL, "null plan, log-mel, band weights or output");
+    if (!pl->n_fft) return fail(MIXFE_EINVAL, "augmentation-only plan (mixfe_plan_create_augment) has no feature tables");
+    if (B < 0 || T < 0) return fail(MIXFE_EINVAL, "negative B or T");
+    if (!(tau > 0.0f) || !(band_weight_sum > 0.0)) return fail(MIXFE_EINVAL, "tau and the band-weight sum must be positive");
+    if (B == 0) return MIXFE_OK;
+    if (B > 65535) return fail(MIXFE_EUNSUPPORTED, "weighted masking: B=%d > 65535 clips per call", B);
+    const int F = 1 + T / pl->hop;
+    const int n_blocks = (F + kMaskThreads - 1) / kMaskThreads;
+    if ((long long)B * n_blocks > kNoAllocMaskEntries)
+        return fail(MIXFE_EUNSUPPORTED,
+                    "mixfe_weighted_masking_noalloc: B=%d clips x %d blocks of %d frames = %lld partial sums exceed the static "
+                    "scratch of %d (MIXFE_NOALLOC_MASKING_MAX_BLOCKS); split the batch or call mixfe_weighted_masking",
+                    B, n_blocks, kMaskThreads, (long long)B * n_blocks, kNoAllocMaskEntries);
+    float* part = nullptr;
+    if (pl->device >= 0 && pl->device < kNoAllocMaxDevices) {
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        part = g_noalloc_part[pl->device];
+    }
+    if (!part) return fail(MIXFE_EUNSUPPORTED, "device %d has no static scratch (ordinal >= %d)", pl->device, kNoAllocMaxDevices);
+    DeviceGuard guard(pl->device);
+    K9Params p{};
+    p.logmel = logmel; p.lm_stride_b = logmel_stride_b; p.B = B; p.F = F; p.n_mels = pl->n_mels; p.n_blocks = n_blocks;
+    p.beta = beta; p.inv_tau = 1.0f / tau;
+    p.e0 = 1e-6f * (3.0f * (float)pl->n_fft / 8.0f) * (float)pl->n_freq;          // as run_weighted_masking
+    p.aw = band_weights; p.aw_sum = band_weight_sum; p.out = out;
+    // every entry [0, B * n_blocks) is written by the first launch before the second reads it: nothing has to start at
+    // zero, whatever an earlier call left behind
+    p.part = part;
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    k9_masking_partials<<<dim3(n_blocks, B), kMaskThreads, 0, stream>>>(p);
+    k9_masking_finish<<<B, 32, 0, stream>>>(p);
+    MIXFE_CUDA(cudaGetLastError());
+    launch_counter() += 2;
+    return MIXFE_OK;
 }
 
 int mixfe_envelope_compress(mixfe_plan* pl, const float* in, float* out, long long stride_b, long long stride_c, int B, int C,
