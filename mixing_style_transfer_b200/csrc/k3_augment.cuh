@@ -28,7 +28,7 @@
 // scipy's fp64 sosfilt: <= 5e-6 of the output peak for the slowest filter (500 Hz low-pass, poles at r = 0.951);
 // tolerance 1e-4.
 // Chunks are independent: a warp starts `warm` samples early from zero state; with pole radius r the start-state
-// error decays as r^warm (the host sizes `warm` so that r^warm < 1e-13; a chunk that starts at sample 0 is exact).
+// error decays as r^warm (the host sizes `warm` so that r^warm < 1e-10; a chunk that starts at sample 0 is exact).
 //
 // Compressor (memoryless): a = |x| + 1e-8; above the knee  sign(x) 10^((thr + (20 log10 a - thr)/ratio)/20)
 // = sign(x) 2^(c0 + lg2(a)/ratio); below it the reference evaluates sign(x) 10^(log10 a) = sign(x) a up to its own
@@ -77,7 +77,9 @@ struct K3Params {
     float* out[kNumStems];
     long long stride_b, stride_c;
     int B, T, chunk, warm, n_chunks, n_stems;
-    int stem_in_y;                         // 1: one-warp CTAs, grid.y = 2 * stem + channel; 0: warp = stem, grid.y = channel
+    int stem_in_y;                         // 1: one-warp CTAs, grid.y = 2 * stem + channel; 0: warp = stem, grid.y = channel;
+                                           // 2: one-warp CTAs, grid.z indexes `order`, grid.y = channel
+    const int* order;                      // [B * 4] (clip * 4 + stem), heaviest rows first (mode 2)
     const AugClipDev* clips;
     const AugSection* sections;            // [B][kNumStems][kAugSections]
     double* part_energy;                   // [B][4][2][n_chunks], or NULL
@@ -211,13 +213,16 @@ __global__ void __launch_bounds__(kAugWarps * 32, MIXFE_K3_CTAS) k3_augment(cons
     // one warp per (chunk, channel, clip, stem): the warps of a CTA take the stems of one chunk
     // (stem_in_y: one-warp CTAs, the stem rides in blockIdx.y -- a finished warp then frees its registers at once instead
     // of waiting for the slowest of four stems whose effect chains differ by up to 4x)
+    // (stem_in_y == 2: blockIdx.z walks the (clip, stem) rows in the host's order, heaviest effect chains first)
     const int chunk = blockIdx.x;
-    const int ch = p.stem_in_y ? (int)(blockIdx.y & 1) : (int)blockIdx.y, b = blockIdx.z;
+    const int pair = p.stem_in_y == 2 ? __ldg(p.order + blockIdx.z) : 0;
+    const int ch = p.stem_in_y == 1 ? (int)(blockIdx.y & 1) : (int)blockIdx.y;
+    const int b = p.stem_in_y == 2 ? pair >> 2 : (int)blockIdx.z;
     const AugClipDev& cp = p.clips[b];
     const long long row = (long long)b * p.stride_b + (long long)ch * p.stride_c;
     const long long c0 = (long long)chunk * p.chunk;
     const long long c1 = c0 + p.chunk < p.T ? c0 + p.chunk : p.T;
-    const int s = p.stem_in_y ? (int)(blockIdx.y >> 1) : warp;
+    const int s = p.stem_in_y == 2 ? (pair & 3) : (p.stem_in_y ? (int)(blockIdx.y >> 1) : warp);
     if (s >= p.n_stems) return;
 
     // (selects, not p.in[s]: a runtime index into kernel parameters would copy them to local memory)

@@ -489,10 +489,12 @@ inline int prepare_augment(const mixfe_aug_params* params, int B, int T, int n_s
             }
         }
     }
-    // warm-up so that r^warm < 1e-13, in whole 512-sample blocks; chunk >= 8 * warm keeps the overhead <= 12.5 %
+    // warm-up so that r^warm < 1e-10 (the fp32 output resolves 6e-8; 1e-13 cost the 500 Hz low-pass, r = 0.951, a second
+    // 512-sample block per 8192-sample chunk: 12.5 % instead of 6.25 % of extra reads and arithmetic), in whole blocks;
+    // chunk >= 8 * warm keeps the overhead <= 12.5 %
     int warm = 0;
     if (rmax > 0.0) {
-        const double need = std::log(1e-13) / std::log(rmax);
+        const double need = std::log(1e-10) / std::log(rmax);
         warm = need > 4.0e6 ? 1 << 30 : ((int)std::ceil(need) + kAugBlock - 1) / kAugBlock * kAugBlock;
     }
     int chunk = 8192;
@@ -588,6 +590,7 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     const size_t o_clips = carve(sizeof(AugClipDev) * B);
     const size_t o_sections = carve(sizeof(AugSection) * al.sections.size());
     const size_t o_slots = carve(sizeof(int) * (size_t)std::max(1, n_slots));
+    const size_t o_order = carve(sizeof(int) * (size_t)B * kNumStems);
     const size_t o_tables = off;                                    // [0, o_tables) is uploaded from the host in one copy
     const size_t o_energy = carve(sizeof(double) * (size_t)B * kNumStems * 2 * n_chunks);
     const size_t o_X = carve(sizeof(float2) * (size_t)lay.n * n_slots * std::max(1, n_seg));
@@ -607,14 +610,29 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     if (rc) return rc;
     char* ws = reinterpret_cast<char*>(pl->ws);
     ParamUpload up(pl, stream);
-    rc = up.reserve(o_tables + sizeof(int) * (size_t)B);
+    rc = up.reserve(o_tables + sizeof(int) * (size_t)B + 256);
     if (rc) return rc;
     if ((rc = up.stage(o_clips, al.clips.data(), sizeof(AugClipDev) * B))) return rc;
     if ((rc = up.stage(o_sections, al.sections.data(), sizeof(AugSection) * al.sections.size()))) return rc;
     if ((rc = up.stage(o_slots, slot_clip.data(), sizeof(int) * (size_t)n_slots))) return rc;
+    // (clip, stem) rows in order of decreasing work: the block scheduler hands out CTAs in grid order, so the rows with
+    // the long effect chains start first and the launch ends on cheap copies instead of on a straggler
+    static const int k3_mode = std::getenv("MIXFE_K3_SPLIT") ? std::atoi(std::getenv("MIXFE_K3_SPLIT")) : 2;
+    const bool sorted = k3_mode == 2 && (long long)B * kNumStems <= 65535;
+    if (sorted) {
+        std::vector<int> order((size_t)B * kNumStems);
+        std::iota(order.begin(), order.end(), 0);
+        auto cost = [&](int pair) {
+            const int f = al.clips[pair >> 2].flags[pair & 3];
+            return ((f & 1) ? 3 : 0) + ((f & 2) ? 2 : 0) + ((f & 4) ? 6 : 0);
+        };
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost(x) > cost(y); });
+        if ((rc = up.stage(o_order, order.data(), sizeof(int) * order.size()))) return rc;
+    }
     if ((rc = up.upload(ws))) return rc;
 
     K3Params p3{};
+    p3.order = reinterpret_cast<const int*>(ws + o_order);
     for (int s = 0; s < kNumStems; ++s) { p3.in[s] = in[s]; p3.out[s] = out[s]; }
     p3.stride_b = stride_b; p3.stride_c = stride_c; p3.B = B; p3.T = T; p3.chunk = al.chunk; p3.warm = al.warm;
     p3.n_chunks = n_chunks; p3.n_stems = kNumStems; p3.clips = reinterpret_cast<const AugClipDev*>(ws + o_clips);
@@ -622,9 +640,9 @@ inline int run_augment(mixfe_plan* pl, const float* const in[kNumStems], float* 
     p3.part_energy = reinterpret_cast<double*>(ws + o_energy);
     {
         KernelTimer timer(pl, MIXFE_KERNEL_AUGMENT, stream);
-        static const bool split = !(std::getenv("MIXFE_K3_SPLIT") && std::atoi(std::getenv("MIXFE_K3_SPLIT")) == 0);
-        p3.stem_in_y = split ? 1 : 0;
-        if (split) k3_augment<<<dim3(n_chunks, 2 * kNumStems, B), 32, 0, stream>>>(p3);
+        p3.stem_in_y = sorted ? 2 : (k3_mode != 0 ? 1 : 0);
+        if (sorted) k3_augment<<<dim3(n_chunks, 2, B * kNumStems), 32, 0, stream>>>(p3);
+        else if (p3.stem_in_y) k3_augment<<<dim3(n_chunks, 2 * kNumStems, B), 32, 0, stream>>>(p3);
         else k3_augment<<<dim3(n_chunks, 2, B), kAugWarps * 32, 0, stream>>>(p3);
     }
     MIXFE_CUDA(cudaGetLastError());
