@@ -697,7 +697,10 @@ def run_native(args):
         hls = [HostPipeline.pinned_like((N_CLIPS, 8, N_MELS, F)) for _ in range(2)]
         hf, hl = hfs[0], hls[0]
         if with_aug:
-            host = {n: HostPipeline.pinned_like((2 * N_TRI, 2, T)) for n in pkg.STEMS}
+            # the loader's collate buffer: one pinned allocation, the four stems as views (TripletPipeline then moves a
+            # chunk of all four stems in one strided transfer; separate tensors take one transfer per stem)
+            host_all = HostPipeline.pinned_like((len(pkg.STEMS), 2 * N_TRI, 2, T))
+            host = {n: host_all[k] for k, n in enumerate(pkg.STEMS)}
             for n, s in zip(pkg.STEMS, stems):
                 host[n].copy_(s[:2 * N_TRI])
             pipe = TripletPipeline(fe, pkg.AudioAugmenter(prob=0.5), N_TRI, T, chunk=4, device=dev, with_logmel=True)

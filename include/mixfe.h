@@ -208,6 +208,15 @@ int mixfe_debug_feature_kernel_config(const mixfe_plan* plan, int* ctas_per_sm, 
  * the all-gather of BASELINE config 5 without kernels). */
 int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream);
 
+/* Strided copy by a copy engine, stream-ordered: `blocks` blocks of `rows` runs of width_bytes; run r of block k goes from
+ * src + (k*src_block_rows + r)*src_pitch to dst + (k*dst_block_rows + r)*dst_pitch (blocks = 1: the block strides are
+ * ignored).  Either side may be pinned host memory (direction inferred).  The host pipelines (pipeline.py) use it to move
+ * the anchor and the positive rows of a triplet chunk -- two ranges a constant stride apart in the caller's (2G, 2, T)
+ * stem tensors (the reference's collate layout, src/data.py:231-265) -- in ONE transfer instead of two, and all four
+ * stems in one when the caller's stem tensors are equally spaced views of one allocation. */
+int mixfe_copy_strided_async(void* dst, size_t dst_pitch, size_t dst_block_rows, const void* src, size_t src_pitch,
+                             size_t src_block_rows, size_t width_bytes, size_t rows, size_t blocks, void* cuda_stream);
+
 /* The all-gather of BASELINE config 5 driven by SMs: copies `bytes` (a multiple of 16) from src to the same position of
  * n_peers peer buffers (dst: HOST array of device pointers that are NVLink peer mappings of this process, e.g. torch
  * symmetric-memory buffers; <= 15), 128-bit loads and stores, n_ctas CTAs of 512 threads, stream-ordered.  Meant to run beside

@@ -80,7 +80,7 @@ EXPORTS = ("mixfe_abi_version", "mixfe_last_error", "mixfe_plan_create", "mixfe_
            "mixfe_plan_reserve_sms", "mixfe_copy_async", "mixfe_gated_loudness", "mixfe_short_term_loudness_iqr",
            "mixfe_stft_loss_forward", "mixfe_stft_loss_backward", "mixfe_plan_create_augment", "mixfe_effects",
            "mixfe_reverb", "mixfe_weighted_masking", "mixfe_envelope_compress", "mixfe_push_peers",
-           "mixfe_weighted_masking_noalloc")
+           "mixfe_weighted_masking_noalloc", "mixfe_copy_strided_async")
 
 
 def lib() -> ctypes.CDLL:
@@ -126,6 +126,8 @@ def lib() -> ctypes.CDLL:
         L.mixfe_debug_feature_kernel_config.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.mixfe_plan_reserve_sms.argtypes = [vp, ci]
         L.mixfe_copy_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
+        sz = ctypes.c_size_t
+        L.mixfe_copy_strided_async.argtypes = [vp, sz, sz, vp, sz, sz, sz, sz, sz, vp]
         L.mixfe_push_peers.argtypes = [ctypes.POINTER(vp), ci, vp, ctypes.c_size_t, ci, vp]
         L.mixfe_gated_loudness.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
         L.mixfe_short_term_loudness_iqr.argtypes = [vp, ctypes.POINTER(vp), ll, ll, ci, ci, vp, vp]
@@ -222,6 +224,16 @@ def copy_async(dst_ptr: int, src: torch.Tensor, nbytes: int) -> None:
     """Copy-engine D2D copy of `nbytes` from the (contiguous) tensor `src` to the raw device address `dst_ptr` on the
     current stream of src's device; dst_ptr may be an NVSwitch multicast address."""
     _check(lib().mixfe_copy_async(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src.data_ptr()), nbytes, _stream(src.device)))
+
+
+def copy2d_async(dst: torch.Tensor, dst_pitch: int, src: torch.Tensor, src_pitch: int, width_bytes: int, rows: int,
+                 device, blocks: int = 1, dst_block_rows: int = 0, src_block_rows: int = 0) -> None:
+    """Copy-engine strided copy on the current stream of `device`: `blocks` x `rows` runs of width_bytes starting at dst / src
+    (tensor views whose data_ptr is the first byte), pitches in bytes, block strides in rows; host tensors must be pinned for
+    the copy to be asynchronous."""
+    _check(lib().mixfe_copy_strided_async(ctypes.c_void_p(dst.data_ptr()), dst_pitch, dst_block_rows,
+                                          ctypes.c_void_p(src.data_ptr()), src_pitch, src_block_rows,
+                                          width_bytes, rows, blocks, _stream(device)))
 
 
 def push_peers(dst_ptrs: Sequence[int], src: torch.Tensor, nbytes: int, n_ctas: int) -> None:

@@ -951,6 +951,26 @@ int mixfe_copy_async(void* dst, const void* src, size_t bytes, void* cuda_stream
     return MIXFE_OK;
 }
 
+int mixfe_copy_strided_async(void* dst, size_t dst_pitch, size_t dst_block_rows, const void* src, size_t src_pitch,
+                             size_t src_block_rows, size_t width_bytes, size_t rows, size_t blocks, void* cuda_stream) {
+    if (!dst || !src) return fail(MIXFE_EINVAL, "null dst or src");
+    if (rows == 0 || width_bytes == 0 || blocks == 0) return MIXFE_OK;
+    if (dst_pitch < width_bytes || src_pitch < width_bytes) return fail(MIXFE_EINVAL, "pitch smaller than the row width");
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    if (blocks == 1) {
+        MIXFE_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, rows, cudaMemcpyDefault, stream));
+        return MIXFE_OK;
+    }
+    if (dst_block_rows < rows || src_block_rows < rows) return fail(MIXFE_EINVAL, "block stride smaller than the rows of a block");
+    cudaMemcpy3DParms q{};
+    q.srcPtr = make_cudaPitchedPtr(const_cast<void*>(src), src_pitch, width_bytes, src_block_rows);
+    q.dstPtr = make_cudaPitchedPtr(dst, dst_pitch, width_bytes, dst_block_rows);
+    q.extent = make_cudaExtent(width_bytes, rows, blocks);
+    q.kind = cudaMemcpyDefault;
+    MIXFE_CUDA(cudaMemcpy3DAsync(&q, stream));
+    return MIXFE_OK;
+}
+
 int mixfe_push_peers(void* const* dst, int n_peers, const void* src, size_t bytes, int n_ctas, void* cuda_stream) {
     if (!dst || !src || n_peers < 0 || n_peers > kMaxPushPeers) return fail(MIXFE_EINVAL, "bad peers (at most %d)", kMaxPushPeers);
     if (n_peers == 0 || bytes == 0) return MIXFE_OK;

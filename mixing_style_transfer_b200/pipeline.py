@@ -11,11 +11,12 @@ and log-mels out, copies of chunk i+1 and i-1 overlapping the kernels of chunk i
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
 
-from ._native import STEMS
+from ._native import STEMS, copy2d_async
 
 
 class HostPipeline:
@@ -125,6 +126,7 @@ class TripletPipeline:
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.plan = extractor._new_plan(self.device)
         self.G, self.T = n_triplets, T
+        self.copy2d = os.environ.get("MIXFE_PIPE_COPY2D", "1") != "0"        # strided transfers (A/B knob)
         self.chunk = max(1, min(chunk, n_triplets))
         self.with_logmel = with_logmel
         sizes, left = [], n_triplets
@@ -145,7 +147,9 @@ class TripletPipeline:
         self.slots = []
         for _ in range(2):
             self.slots.append({
-                "stems": [torch.empty((c3, 2, T), dtype=torch.float32, device=self.device) for _ in STEMS],
+                # one allocation for the four stems: a chunk of m triplets lays them out 3m clips apart, so that the four
+                # stems of a chunk can arrive in ONE strided transfer
+                "flat": torch.empty((len(STEMS) * c3 * 2 * T,), dtype=torch.float32, device=self.device),
                 "feat": torch.empty((c3, self.plan.feature_dim), dtype=torch.float32, device=self.device),
                 "lm": torch.empty((c3, 8, self.plan.n_mels, F), dtype=torch.float32, device=self.device) if with_logmel else None,
                 "uploaded": torch.cuda.Event(), "computed": torch.cuda.Event(), "drained": torch.cuda.Event(),
@@ -178,30 +182,56 @@ class TripletPipeline:
             i = self._n_chunks_done
             self._n_chunks_done += 1
             slot = self.slots[i & 1]
+            per = 3 * m * 2 * self.T
+            stems_d = [slot["flat"][k * per:(k + 1) * per].view(3 * m, 2, self.T) for k in range(len(STEMS))]
             with torch.cuda.stream(self.s_up):
                 if i >= 2:
                     self.s_up.wait_event(slot["computed"])
-                for d, name in zip(slot["stems"], STEMS):
-                    d[:m].copy_(host_stems[name][lo:hi], non_blocking=True)
-                    d[m:2 * m].copy_(host_stems[name][G + lo:G + hi], non_blocking=True)
+                hs = [host_stems[name] for name in STEMS]
+                row = 2 * self.T * 4
+                strided = self.copy2d and all(h.is_contiguous() and h.is_pinned() and h.dtype == torch.float32 for h in hs)
+                gap = hs[1].data_ptr() - hs[0].data_ptr()
+                if strided and gap > 0 and gap % (G * row) == 0 and \
+                        all(hs[k + 1].data_ptr() - hs[k].data_ptr() == gap for k in range(len(hs) - 1)):
+                    # the caller's four stem tensors are equally spaced views of one pinned allocation: anchors and positives
+                    # of all four stems in ONE transfer (blocks = stems, rows = anchors | positives)
+                    copy2d_async(stems_d[0], m * row, hs[0][lo], G * row, m * row, 2, self.device,
+                                 blocks=len(STEMS), dst_block_rows=3, src_block_rows=gap // (G * row))
+                elif strided:
+                    # anchors [lo, hi) and positives [G + lo, G + hi): two runs one stride apart -> one transfer per stem
+                    for d, h in zip(stems_d, hs):
+                        copy2d_async(d, m * row, h[lo], G * row, m * row, 2, self.device)
+                else:
+                    for d, h in zip(stems_d, hs):
+                        d[:m].copy_(h[lo:hi], non_blocking=True)
+                        d[m:2 * m].copy_(h[G + lo:G + hi], non_blocking=True)
                 slot["uploaded"].record(self.s_up)
             with torch.cuda.stream(self.s_run):
                 self.s_run.wait_event(slot["uploaded"])
                 if i >= 2:
                     self.s_run.wait_event(slot["drained"])
                 dec = decisions.slice(lo, hi) if hasattr(decisions, "slice") else decisions[lo:hi]
-                self.aug.apply({n: d[:m] for n, d in zip(STEMS, slot["stems"])}, dec,
-                               out={n: d[2 * m:3 * m] for n, d in zip(STEMS, slot["stems"])})
-                self.plan.features_logmel([d[:3 * m] for d in slot["stems"]], True, self.with_logmel,
+                self.aug.apply({n: d[:m] for n, d in zip(STEMS, stems_d)}, dec,
+                               out={n: d[2 * m:3 * m] for n, d in zip(STEMS, stems_d)})
+                self.plan.features_logmel(stems_d, True, self.with_logmel,
                                           features_out=slot["feat"][:3 * m],
                                           logmel_out=slot["lm"][:3 * m] if self.with_logmel else None)
                 slot["computed"].record(self.s_run)
             with torch.cuda.stream(self.s_down):
                 self.s_down.wait_event(slot["computed"])
-                for part in range(3):
-                    feat_out[part * G + lo:part * G + hi].copy_(slot["feat"][part * m:(part + 1) * m], non_blocking=True)
+                if self.copy2d and feat_out.is_contiguous() and feat_out.is_pinned() and \
+                        (lm_out is None or (lm_out.is_contiguous() and lm_out.is_pinned())):
+                    # the three parts (anchors | positives | negatives) of the chunk land G rows apart: one transfer each
+                    rf = feat_out.shape[1] * 4
+                    copy2d_async(feat_out[lo], G * rf, slot["feat"], m * rf, m * rf, 3, self.device)
                     if self.with_logmel:
-                        lm_out[part * G + lo:part * G + hi].copy_(slot["lm"][part * m:(part + 1) * m], non_blocking=True)
+                        rl = lm_out[0].numel() * 4
+                        copy2d_async(lm_out[lo], G * rl, slot["lm"], m * rl, m * rl, 3, self.device)
+                else:
+                    for part in range(3):
+                        feat_out[part * G + lo:part * G + hi].copy_(slot["feat"][part * m:(part + 1) * m], non_blocking=True)
+                        if self.with_logmel:
+                            lm_out[part * G + lo:part * G + hi].copy_(slot["lm"][part * m:(part + 1) * m], non_blocking=True)
                 slot["drained"].record(self.s_down)
         ticket = torch.cuda.Event()
         ticket.record(self.s_down)

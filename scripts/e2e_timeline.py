@@ -13,7 +13,11 @@ dev = torch.device("cuda:0")
 fe = pkg.MixingFeatureExtractor()
 plan = fe._plan(dev)
 F = plan.num_frames(T)
-host = {n: HostPipeline.pinned_like((2 * N_TRI, 2, T)) for n in pkg.STEMS}
+if os.environ.get("E2E_ONE_ALLOC", "1") != "0":
+    host_all = HostPipeline.pinned_like((4, 2 * N_TRI, 2, T))
+    host = {n: host_all[k] for k, n in enumerate(pkg.STEMS)}
+else:
+    host = {n: HostPipeline.pinned_like((2 * N_TRI, 2, T)) for n in pkg.STEMS}
 for n in pkg.STEMS:
     host[n].uniform_(-0.2, 0.2)
 hfs = [HostPipeline.pinned_like((3 * N_TRI, 64)) for _ in range(2)]

@@ -65,8 +65,9 @@ def test_prefetching_submit_wait_matches_run(cuda_device):
         assert torch.equal(wf, gf) and torch.equal(wl, gl)
 
 
-@pytest.mark.parametrize("G,chunk", [(5, 2), (9, 2), (3, 4)])
-def test_triplet_pipeline_matches_resident(cuda_device, G, chunk):
+@pytest.mark.parametrize("one_alloc", [False, True])
+@pytest.mark.parametrize("G,chunk", [(5, 2), (9, 2), (3, 4), (11, 4)])
+def test_triplet_pipeline_matches_resident(cuda_device, G, chunk, one_alloc):
     """TripletPipeline (host anchors + positives -> device negatives -> features + log-mel of 3G clips) against the
     resident calls on the same decisions; blocking run and prefetching submit/wait."""
     from mixing_style_transfer_b200.pipeline import TripletPipeline
@@ -74,7 +75,11 @@ def test_triplet_pipeline_matches_resident(cuda_device, G, chunk):
     fe = pkg.MixingFeatureExtractor()
     aug = pkg.AudioAugmenter(prob=0.6)
     clips = [O.musical_clip(300 + i, T) for i in range(2 * G)]
-    host = {name: HostPipeline.pinned_like((2 * G, 2, T)) for name in O.STEMS}
+    if one_alloc:        # the four stems as equally spaced views of one pinned buffer: one strided transfer per chunk
+        whole = HostPipeline.pinned_like((4, 2 * G, 2, T))
+        host = {name: whole[k] for k, name in enumerate(O.STEMS)}
+    else:                # separate tensors: one strided transfer per stem
+        host = {name: HostPipeline.pinned_like((2 * G, 2, T)) for name in O.STEMS}
     for name in O.STEMS:
         host[name].copy_(torch.stack([c[name] for c in clips]))
     torch.manual_seed(11)
