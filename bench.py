@@ -711,7 +711,8 @@ def run_native(args):
                    "the negatives on the device (decisions drawn per step) -> features_and_logmel kernels -> D2H of the 72 "
                    "feature vectors and log-mels into pinned host memory")
         else:
-            host = {n: HostPipeline.pinned_like((N_CLIPS, 2, T)) for n in pkg.STEMS}
+            host_all = HostPipeline.pinned_like((len(pkg.STEMS), N_CLIPS, 2, T))
+            host = {n: host_all[k] for k, n in enumerate(pkg.STEMS)}
             for n, s in zip(pkg.STEMS, stems):
                 host[n].copy_(s)
             pipe = HostPipeline(fe, N_CLIPS, T, chunk=12, device=dev, with_logmel=True)

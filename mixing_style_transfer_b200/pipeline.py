@@ -19,6 +19,13 @@ import torch
 from ._native import STEMS, copy2d_async
 
 
+def _one_storage(tensors) -> bool:
+    """True when the tensors are views of ONE allocation (a strided transfer must not cross allocations, even when separate
+    pinned buffers happen to lie equally spaced)."""
+    first = tensors[0].untyped_storage().data_ptr()
+    return all(t.untyped_storage().data_ptr() == first for t in tensors)
+
+
 class HostPipeline:
     def __init__(self, extractor, n_clips: int, T: int, chunk: int = 12, device=None, with_logmel: bool = True):
         self.fe = extractor
@@ -27,6 +34,7 @@ class HostPipeline:
         # so it owns a private plan instead of borrowing the extractor's
         self.plan = extractor._new_plan(self.device)
         self.n, self.T, self.chunk = n_clips, T, max(1, min(chunk, n_clips))
+        self.copy2d = os.environ.get("MIXFE_PIPE_COPY2D", "1") != "0"        # strided transfers (A/B knob)
         self.with_logmel = with_logmel
         # chunk boundaries: short chunks at both ends (the first upload and the last download are the only legs
         # that nothing overlaps), full ones in between
@@ -50,7 +58,7 @@ class HostPipeline:
         self.slots = []
         for _ in range(2):
             self.slots.append({
-                "stems": [torch.empty((self.chunk, 2, T), dtype=torch.float32, device=self.device) for _ in STEMS],
+                "flat": torch.empty((len(STEMS) * self.chunk * 2 * T,), dtype=torch.float32, device=self.device),
                 "feat": torch.empty((self.chunk, self.plan.feature_dim), dtype=torch.float32, device=self.device),
                 "lm": torch.empty((self.chunk, 8, self.plan.n_mels, F), dtype=torch.float32, device=self.device)
                 if with_logmel else None,
@@ -89,17 +97,26 @@ class HostPipeline:
             i = self._n_chunks_done
             self._n_chunks_done += 1
             slot = self.slots[i & 1]
+            per = m * 2 * self.T
+            stems_d = [slot["flat"][k * per:(k + 1) * per].view(m, 2, self.T) for k in range(len(STEMS))]
             with torch.cuda.stream(self.s_up):
                 if i >= 2:
                     self.s_up.wait_event(slot["computed"])       # kernels of chunk i-2 have consumed the slot
-                for d, name in zip(slot["stems"], STEMS):
-                    d[:m].copy_(host_stems[name][lo:hi], non_blocking=True)
+                hs = [host_stems[name] for name in STEMS]
+                gap = hs[1].data_ptr() - hs[0].data_ptr()
+                if self.copy2d and gap > 0 and all(h.is_contiguous() and h.is_pinned() and h.dtype == torch.float32 for h in hs) \
+                        and _one_storage(hs) and all(hs[k + 1].data_ptr() - hs[k].data_ptr() == gap for k in range(len(hs) - 1)):
+                    # equally spaced views of one pinned buffer: the chunk of all four stems in ONE strided transfer
+                    copy2d_async(stems_d[0], per * 4, hs[0][lo], gap, per * 4, len(STEMS), self.device)
+                else:
+                    for d, h in zip(stems_d, hs):
+                        d.copy_(h[lo:hi], non_blocking=True)
                 slot["uploaded"].record(self.s_up)
             with torch.cuda.stream(self.s_run):
                 self.s_run.wait_event(slot["uploaded"])
                 if i >= 2:
                     self.s_run.wait_event(slot["drained"])        # outputs of chunk i-2 have left the slot
-                self.plan.features_logmel([d[:m] for d in slot["stems"]], True, self.with_logmel,
+                self.plan.features_logmel(stems_d, True, self.with_logmel,
                                           features_out=slot["feat"][:m],
                                           logmel_out=slot["lm"][:m] if self.with_logmel else None)
                 slot["computed"].record(self.s_run)
@@ -191,7 +208,7 @@ class TripletPipeline:
                 row = 2 * self.T * 4
                 strided = self.copy2d and all(h.is_contiguous() and h.is_pinned() and h.dtype == torch.float32 for h in hs)
                 gap = hs[1].data_ptr() - hs[0].data_ptr()
-                if strided and gap > 0 and gap % (G * row) == 0 and \
+                if strided and gap > 0 and gap % (G * row) == 0 and _one_storage(hs) and \
                         all(hs[k + 1].data_ptr() - hs[k].data_ptr() == gap for k in range(len(hs) - 1)):
                     # the caller's four stem tensors are equally spaced views of one pinned allocation: anchors and positives
                     # of all four stems in ONE transfer (blocks = stems, rows = anchors | positives)

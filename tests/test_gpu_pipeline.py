@@ -31,6 +31,23 @@ def test_pipeline_matches_resident(cuda_device, n, chunk):
     assert pipe.h2d_bytes == 4 * 8 * T * n and pipe.d2h_bytes == 4 * n * (64 + 8 * 128 * (1 + T // 256))
 
 
+def test_pipeline_one_allocation_matches_resident(cuda_device):
+    """The four stems as equally spaced views of one pinned buffer: one strided transfer per chunk."""
+    T, n = 9000, 7
+    fe = pkg.MixingFeatureExtractor()
+    clips = [O.musical_clip(170 + i, T) for i in range(n)]
+    whole = HostPipeline.pinned_like((4, n, 2, T))
+    host = {name: whole[k] for k, name in enumerate(O.STEMS)}
+    for name in O.STEMS:
+        host[name].copy_(torch.stack([c[name] for c in clips]))
+    pipe = HostPipeline(fe, n, T, chunk=3, device=cuda_device)
+    hf = HostPipeline.pinned_like((n, 64)).fill_(-1)
+    hl = HostPipeline.pinned_like((n, 8, 128, 1 + T // 256)).fill_(-1)
+    pipe.run(host, hf, hl)
+    f, lm = fe.features_and_logmel({k: v.to(cuda_device) for k, v in host.items()})
+    assert torch.equal(hf, f.cpu()) and torch.equal(hl, lm.cpu())
+
+
 def test_prefetching_submit_wait_matches_run(cuda_device):
     """Three different batches queued with one batch of prefetch (submit k+1 before wait k, two sets of host outputs,
     odd number of chunks per batch so that the slot parity flips between batches) give what the blocking run gives."""
