@@ -67,6 +67,9 @@ struct K1Params {
     int tma_lo, tma_hi;              // tiles tma_lo..tma_hi are staged by TMA bulk copies (empty range = none)
     int rows_hi;                     // tiles 0..rows_hi get their time-statistics rows by TMA (-1 = none)
     long long total_items;           // B * n_tiles
+    int* work;                       // [2] zeroed counters (items handed out beyond the first per CTA, CTAs finished), or NULL:
+                                     // NULL = CTA i takes items i, i + grid, ...; else every item after the first comes from
+                                     // an atomic counter, so a CTA that drew slow tiles (clip edges) does not end the launch late
     float* logmel;
     long long lm_stride_b;
     float* melpow;                   // debug output (mel power before the log) or nullptr
@@ -394,7 +397,8 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long item = blockIdx.x;
-    if (item >= p.total_items) return;
+    if (item >= p.total_items) return;                  // (the launcher never starts more CTAs than items)
+    int* const next_slot = reinterpret_cast<int*>(smem + p.off_red + 24);
 
     // ---- constant tables -> shared memory (once per persistent CTA) ----------------------------
     for (int i = tid; i < 31 * 32; i += kK1Threads) tw[i] = p.tw[32 + i];      // rows k1 = 1..31
@@ -427,7 +431,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
     for (;;) {
         const int t0 = tile * kTF;
         const int nvalid = p.F - t0 < kTF ? p.F - t0 : kTF;          // frames of this tile that exist
-        const long long next_item = item + gridDim.x;
+        long long next_item = item + gridDim.x;
+        int drawn = 0;
+        if (p.work && tid == 0) drawn = atomicAdd(p.work, 1);         // in flight until the last stem needs it
         float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};                     // masking partial sums of this thread
 
         for (int s = 0; s < kNumStems; ++s) {
@@ -435,7 +441,9 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                 mbar_wait(bar, tma_parity);
                 tma_parity ^= 1u;
             }
+            if (p.work && s == kNumStems - 1 && tid == 0) *next_slot = drawn;
             __syncthreads();                 // B0: xs holds (tile, s); the mel walk of the previous stem has left the power columns
+            if (p.work && s == kNumStems - 1) next_item = (long long)gridDim.x + *next_slot;
             bool stats_rows = false;
             if (s == 0 && p.want_stats) {
                 // The tile's own region of all 8 rows (64 KB = the idle exchange regions) by TMA when it lies inside
@@ -707,6 +715,13 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
         item = next_item;
         b = (int)(item / p.n_tiles);
         tile = (int)(item - (long long)b * p.n_tiles);
+    }
+    // the last CTA to finish leaves the counters at zero for the next launch (launches of one plan are stream-ordered)
+    if (p.work && tid == 0) {
+        if (atomicAdd(p.work + 1, 1) == (int)gridDim.x - 1) {
+            p.work[0] = 0;
+            p.work[1] = 0;
+        }
     }
 }
 

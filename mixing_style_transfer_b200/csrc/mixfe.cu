@@ -230,6 +230,10 @@ int build_mel_tables(mixfe_plan* pl) {
     if (pl->smem_k1 > 227 * 1024)
         return fail(MIXFE_EUNSUPPORTED, "K1 needs %d bytes of shared memory (hop too large or filters too wide)", pl->smem_k1);
     if (int rc = smem_optin(k1_features, pl->device, pl->smem_k1)) return rc;
+    if (!pl->d_k1_work) {
+        MIXFE_CUDA(cudaMalloc(&pl->d_k1_work, 2 * sizeof(int)));
+        MIXFE_CUDA(cudaMemset(pl->d_k1_work, 0, 2 * sizeof(int)));
+    }
     int per_sm = 0;
     MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_features, kK1Threads, pl->smem_k1));
     pl->k1_ctas = std::max(1, per_sm) * pl->n_sms;
@@ -562,6 +566,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
         const int per_sm = pl->n_sms ? pl->k1_ctas / pl->n_sms : 1;
         const int grid = (int)std::min<long long>(p.total_items, (long long)per_sm * (pl->n_sms - pl->reserved_sms));
+        static const bool dynamic = !(std::getenv("MIXFE_K1_DYNAMIC") && std::atoi(std::getenv("MIXFE_K1_DYNAMIC")) == 0);
+        p.work = dynamic ? pl->d_k1_work : nullptr;
         k1_features<<<grid, kK1Threads, pl->smem_k1, stream>>>(p);
     }
     MIXFE_CUDA(cudaGetLastError());
@@ -925,7 +931,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
-    cudaFree(pl->ws);
+    cudaFree(pl->ws); cudaFree(pl->d_k1_work);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw); cudaFree(pl->d_eitems); cudaFree(pl->d_ewts);
     for (int i = 0; i < mixfe_plan::kParamSlots; ++i) {

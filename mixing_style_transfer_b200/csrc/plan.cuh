@@ -22,6 +22,7 @@ struct mixfe_plan {
     int wmeta[8][2][4] = {};            // per warp, per group slot: steps, weight offset, group index, 0
     // K1 shared-memory map and persistent grid
     int nxs = 0, smem_k1 = 0, n_sms = 0, k1_ctas = 0;
+    int* d_k1_work = nullptr;           // K1's two work counters (k1_features.cuh), zero between launches
     int reserved_sms = 0;               // SMs K1's persistent grid leaves free (for a collective running beside it)
     int off_ex = 0, off_tw = 0, off_s = 0, off_wsteps = 0, off_flo = 0, off_red = 0;
     // K1G (k1g_features.cuh): generic power-of-two n_fft path; used when K1 does not cover the configuration
