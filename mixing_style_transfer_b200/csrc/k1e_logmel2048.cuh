@@ -34,6 +34,7 @@ struct K1EParams {
     int nxs;                         // staged samples per channel = (kETF - 1) * hop + 2048
     int tma_lo, tma_hi;              // tiles staged by TMA (empty range = none)
     long long total_items;
+    int* work;                       // K1's work counters (k1_features.cuh: dynamic item distribution), or NULL
     float* logmel;
     long long lm_stride_b;
     const float2* tw;                // [1024] 32 x 32 twiddles of the 1024-point transform
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
     const int q = warp >> 1, par = warp & 1;            // frame of the tile, even / odd half
     long long item = blockIdx.x;
     if (item >= p.total_items) return;
+    int* const next_slot = reinterpret_cast<int*>(smem + p.off_bar + 16);
 
     for (int i = tid; i < 31 * 32; i += kEThreads) tw[i] = p.tw[32 + i];
     for (int i = tid; i < kEItems; i += kEThreads) items[i] = p.items[i];
@@ -130,13 +132,17 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
     for (;;) {
         const int u0 = tile * kETF;
         const int nvalid = p.F - u0 < kETF ? p.F - u0 : kETF;
-        const long long next_item = item + gridDim.x;
+        long long next_item = item + gridDim.x;
+        int drawn = 0;
+        if (p.work && tid == 0) drawn = atomicAdd(p.work, 1);         // in flight until the last stem needs it
         for (int s = 0; s < kNumStems; ++s) {
             if (cur_tma) {
                 mbar_wait(bar, tma_parity);
                 tma_parity ^= 1u;
             }
+            if (p.work && s == kNumStems - 1 && tid == 0) *next_slot = drawn;
             __syncthreads();                 // B0: xs holds (tile, s); the previous mel walk has left the power columns
+            if (p.work && s == kNumStems - 1) next_item = (long long)gridDim.x + *next_slot;
             cplx64 z[32];
             const bool active = q < nvalid;
             if (active) {
@@ -314,6 +320,12 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
         item = next_item;
         b = (int)(item / p.n_tiles);
         tile = (int)(item - (long long)b * p.n_tiles);
+    }
+    if (p.work && tid == 0) {            // the last CTA out leaves the counters at zero for the next launch
+        if (atomicAdd(p.work + 1, 1) == (int)gridDim.x - 1) {
+            p.work[0] = 0;
+            p.work[1] = 0;
+        }
     }
 }
 

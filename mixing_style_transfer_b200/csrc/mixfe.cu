@@ -448,6 +448,10 @@ int build_k1e_tables(mixfe_plan* pl) {
     if (pl->smem_e > 227 * 1024) return MIXFE_OK;                          // hop too large: K1G serves the plan
     int rc;
     if ((rc = upload(&pl->d_eitems, items)) || (rc = upload(&pl->d_ewts, w))) return rc;
+    if (!pl->d_k1_work) {
+        MIXFE_CUDA(cudaMalloc(&pl->d_k1_work, 2 * sizeof(int)));
+        MIXFE_CUDA(cudaMemset(pl->d_k1_work, 0, 2 * sizeof(int)));
+    }
     if ((rc = smem_optin(k1e_logmel2048, pl->device, pl->smem_e))) return rc;
     int per_sm = 0;
     MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1e_logmel2048, kEThreads, pl->smem_e));
@@ -545,6 +549,8 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         {
             KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
             const int grid = (int)std::min<long long>(e.total_items, (long long)pl->e_ctas);
+            static const bool dynamic = !(std::getenv("MIXFE_K1_DYNAMIC") && std::atoi(std::getenv("MIXFE_K1_DYNAMIC")) == 0);
+            e.work = dynamic ? pl->d_k1_work : nullptr;
             k1e_logmel2048<<<grid, kEThreads, pl->smem_e, stream>>>(e);
         }
         MIXFE_CUDA(cudaGetLastError());
