@@ -114,8 +114,8 @@ int mixfe_reverb(mixfe_plan* plan, const float* in, float* out, long long stride
  * loop differentiates (src/train_style_transfer.py:206-215): given d loss / d logmel, WRITES d loss / d stems into
  * grad_stems (every sample of the T-long rows is overwritten; no initialisation needed).  stems: the forward inputs,
  * addressed as in mixfe_features_logmel; logmel: the tensor the forward wrote for them (same addressing as there) or
- * NULL -- with it, the (1024, 256) configuration runs the fast kernel K6F (dmel = g exp(-logmel), no mel recomputation,
- * every gradient sample written once); without it, or for any other configuration, the generic kernel K6 recomputes
+ * NULL -- with it, the (1024, 256) and (2048, 512) configurations run the fast kernels K6F / K6E (dmel = g exp(-logmel),
+ * no mel recomputation, every gradient sample written once); without it, or for any other configuration, the generic kernel K6 recomputes
  * the mel spectrum; grad_logmel: device, same addressing as logmel; grad_stems[s]: device, element (b, c, t) at
  * grad_stems[s][b*grad_stride_b + c*grad_stride_c + t].  Returns MIXFE_ESHORT when T <= n_fft/2. */
 int mixfe_logmel_backward(mixfe_plan* plan, const float* const stems[MIXFE_NUM_STEMS],

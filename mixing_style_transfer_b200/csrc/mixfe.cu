@@ -14,6 +14,7 @@
 #include "k1e_logmel2048.cuh"
 #include "k6_logmel_bwd.cuh"
 #include "k6f_logmel_bwd.cuh"
+#include "k6e_logmel_bwd2048.cuh"
 #include "plan.cuh"
 #include "k3_augment.cuh"
 #include "k4_reverb.cuh"
@@ -460,10 +461,49 @@ int build_k1e_tables(mixfe_plan* pl) {
 }
 
 // Which kernel serves the plan: K1 for n_fft = 1024 when its shared-memory map fits, else K1G.
+// K6E: per-bin filter pairs of the 1025 one-sided bins, the 2048-point twiddles, the shared-memory map.
+int build_k6e_tables(mixfe_plan* pl) {
+    if (pl->d_ebinw) { cudaFree(pl->d_ebinw); pl->d_ebinw = nullptr; }
+    if (pl->d_ew2048) { cudaFree(pl->d_ew2048); pl->d_ew2048 = nullptr; }
+    if (pl->n_fft != 2048 || pl->hop != 512) return MIXFE_OK;
+    const int nf = pl->n_freq, nm = pl->n_mels;                     // nf = 1025
+    std::vector<float4> binw(nf);
+    for (int k = 0; k < nf; ++k) {
+        int first = -1, last = -1;
+        for (int m = 0; m < nm; ++m)
+            if (pl->fb[(size_t)k * nm + m] != 0.0f) { if (first < 0) first = m; last = m; }
+        if (first < 0) first = last = 0;
+        if (last - first > 1) return MIXFE_OK;                       // not a bank of adjacent triangles: K6 serves the plan
+        float4 e;
+        e.x = __int_as_float_host(first);
+        e.y = pl->fb[(size_t)k * nm + first];
+        e.z = last > first ? pl->fb[(size_t)k * nm + last] : 0.0f;
+        e.w = 0.0f;
+        binw[k] = e;
+    }
+    std::vector<float2> w(513);
+    for (int k = 0; k <= 512; ++k) {
+        const double a = -2.0 * M_PI * (double)k / 2048.0;
+        w[k] = make_float2((float)std::cos(a), (float)std::sin(a));
+    }
+    w[512] = make_float2(0.0f, -1.0f);
+    pl->x_off_tw = kBwWarps * kWarpRegion;
+    pl->x_off_binw = pl->x_off_tw + 31 * 32 * 8;
+    pl->x_off_w = pl->x_off_binw + nf * 16;
+    pl->x_off_dmel = align16(pl->x_off_w + 513 * 8);
+    pl->x_off_ola = align16(pl->x_off_dmel + kBwWarps * (nm + 1) * 4);
+    pl->smem_x = pl->x_off_ola + kBwSpan * 8;
+    if (pl->smem_x > 227 * 1024) return MIXFE_OK;
+    int rc;
+    if ((rc = upload(&pl->d_ebinw, binw)) || (rc = upload(&pl->d_ew2048, w))) return rc;
+    return smem_optin(k6e_logmel_bwd, pl->device, pl->smem_x);
+}
+
 int build_tables(mixfe_plan* pl) {
     int rc = build_generic_tables(pl);
     if (rc) return rc;
     if ((rc = build_k1e_tables(pl))) return rc;
+    if ((rc = build_k6e_tables(pl))) return rc;
     const char* force = getenv("MIXFE_FORCE_GENERIC");
     pl->use_generic = true;
     if (pl->n_fft == kNfft && !(force && atoi(force))) {
@@ -628,6 +668,27 @@ int run_logmel_backward(mixfe_plan* pl, const float* const stems[4], long long s
             KernelTimer timer(pl, MIXFE_KERNEL_LOGMEL_BWD, stream);
             k6f_zero_edges<<<dim3(2 * B, kNumStems), 128, 0, stream>>>(p);
             k6f_logmel_bwd<<<dim3(p.n_tiles, B, kNumStems), kBwThreads, pl->smem_f, stream>>>(p);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter() += 2;
+        return MIXFE_OK;
+    }
+    if (logmel && pl->d_ebinw && !(force && atoi(force))) {
+        // K6E: the same scheme for (2048, 512); a CTA serves one (clip, stem, channel)
+        K6EParams p{};
+        for (int s = 0; s < 4; ++s) { p.stem[s] = stems[s]; p.out[s] = grad_stems[s]; }
+        p.stride_b = stride_b; p.stride_c = stride_c; p.ostride_b = ostride_b; p.ostride_c = ostride_c;
+        p.g = grad_logmel; p.g_stride_b = g_stride_b; p.lm = logmel; p.lm_stride_b = lm_stride_b;
+        p.B = B; p.T = T; p.F = F; p.n_mels = pl->n_mels;
+        const int hlast = ((T + 1) / 2 + 511) / 256;                 // last hop region (units of 2 samples) the padded signal reaches
+        p.n_tiles = (hlast + 3 + kBwOwn - 1) / kBwOwn;
+        p.tw = pl->d_tw; p.binw = pl->d_ebinw; p.w2048 = pl->d_ew2048;
+        p.off_ex = 0; p.off_tw = pl->x_off_tw; p.off_binw = pl->x_off_binw; p.off_w = pl->x_off_w;
+        p.off_dmel = pl->x_off_dmel; p.off_ola = pl->x_off_ola;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_LOGMEL_BWD, stream);
+            k6e_zero_edges<<<dim3(2 * B, kNumStems), 128, 0, stream>>>(p);
+            k6e_logmel_bwd<<<dim3(p.n_tiles, B, 2 * kNumStems), kBwThreads, pl->smem_x, stream>>>(p);
         }
         MIXFE_CUDA(cudaGetLastError());
         launch_counter() += 2;
@@ -937,7 +998,7 @@ int mixfe_plan_destroy(mixfe_plan* pl) {
     if (!pl) return MIXFE_OK;
     DeviceGuard guard(pl->device);
     cudaFree(pl->d_tw); cudaFree(pl->d_twfine); cudaFree(pl->d_twlin); cudaFree(pl->d_flo); cudaFree(pl->d_wsteps);
-    cudaFree(pl->ws); cudaFree(pl->d_k1_work);
+    cudaFree(pl->ws); cudaFree(pl->d_k1_work); cudaFree(pl->d_ebinw); cudaFree(pl->d_ew2048);
     cudaFree(pl->d_twg); cudaFree(pl->d_win); cudaFree(pl->d_mel_meta);
     cudaFree(pl->d_mel_w); cudaFree(pl->d_bin_meta); cudaFree(pl->d_bin_w); cudaFree(pl->d_binw); cudaFree(pl->d_eitems); cudaFree(pl->d_ewts);
     for (int i = 0; i < mixfe_plan::kParamSlots; ++i) {

@@ -37,6 +37,10 @@ struct mixfe_plan {
     int4* d_eitems = nullptr;
     float* d_ewts = nullptr;
     int e_nwts = 0, e_nxs = 0, e_off_ex = 0, e_off_tw = 0, e_off_items = 0, e_off_wts = 0, e_off_bar = 0, smem_e = 0, e_ctas = 0;
+    // K6E (k6e_logmel_bwd2048.cuh): backward of (2048, 512) plans on the one-warp transform; null table = not usable
+    float4* d_ebinw = nullptr;          // [1025] per bin (first filter, its weight, the next filter's weight, -)
+    float2* d_ew2048 = nullptr;         // [513] exp(-2 pi i k / 2048)
+    int x_off_tw = 0, x_off_binw = 0, x_off_w = 0, x_off_dmel = 0, x_off_ola = 0, smem_x = 0;
     float4* d_binw = nullptr;           // K6F: per bin (first filter, its weight, the next filter's weight, -); null = K6F not usable
     int f_off_ex = 0, f_off_tw = 0, f_off_binw = 0, f_off_dmel = 0, f_off_ola = 0, smem_f = 0;      // K6F shared-memory map
     int b_nf = 0, b_span = 0, b_span_pad = 0, b_off_pw = 0, b_off_mel = 0, b_off_ola = 0, smem_b = 0;   // K6 smem map (0 = unsupported)

@@ -32,7 +32,7 @@ for cfg in ((1024, 256, 128), (2048, 512, 80)):
     print(f"  logmel only:     {timed(lambda: plan.features_logmel(stems, False, True)):.3f} ms")
     gl = torch.randn(B, 8, cfg[2], F, device=dev, generator=g)
     _, lm = plan.features_logmel(stems, False, True)
-    for label, kw in (("generic K6 (no forward output)", {}), ("with the forward's log-mel (K6F at 1024/256)", {"logmel": lm})):
+    for label, kw in (("generic K6 (no forward output)", {}), ("with the forward's log-mel (K6F at 1024/256, K6E at 2048/512)", {"logmel": lm})):
         plan.enable_timing(True)
         total = timed(lambda: plan.logmel_backward(stems, gl, **kw))
         ms, n = plan.kernel_time("logmel_bwd")

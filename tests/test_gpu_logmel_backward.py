@@ -47,7 +47,7 @@ def test_backward_matches_autograd_through_oracle(cuda_device, n_fft, hop, n_mel
     lm = pre(leaves)
     assert lm.requires_grad
     (lm * gout.to(cuda_device)).sum().backward()
-    fast = (n_fft, hop) == (1024, 256)                           # K6F: edge-strip zeroing + the backward kernel
+    fast = (n_fft, hop) in ((1024, 256), (2048, 512))            # K6F / K6E: edge-strip zeroing + the backward kernel
     assert pkg.launch_count() == n0 + (3 if fast else 2)         # forward kernel + K6F / K6
     for n in O.STEMS:
         got = leaves[n].grad[0].cpu().double()
@@ -133,6 +133,51 @@ def test_fast_backward_batched_and_strided(cuda_device):
     _, lm = plan.features_logmel(views, False, True)
     g = torch.randn(lm.shape, generator=torch.Generator().manual_seed(1)).to(cuda_device)
     fast = plan.logmel_backward(views, g, logmel=lm)
+    for i in range(3):
+        one = [v[i:i + 1].contiguous() for v in views]
+        ref = plan.logmel_backward(one, g[i:i + 1], logmel=lm[i:i + 1])
+        for a, b_ in zip(fast, ref):
+            assert torch.equal(a[i:i + 1], b_)
+
+
+@pytest.mark.parametrize("T", [1025, 1400, 2049, 3072, 6655, 6656, 6657, 13311, 20001, 44100 + 17])
+def test_fast_backward_2048_lengths_and_generic_agreement(cuda_device, T):
+    """K6E ((2048, 512), with the forward's log-mel) against the generic K6 on the same inputs, over clip lengths around its
+    tiling (13 hop regions = 6656 samples per CTA), odd lengths (the kernel works in units of two samples) and the
+    reflect-fold strips (1025 samples at each end); bitwise run-to-run determinism."""
+    clip = _noisy_clip(T, T)
+    stems = [clip[n][None].to(cuda_device) for n in O.STEMS]
+    plan = pkg.MelSpectrogramPreprocessor(44100, 2048, 512, 80)._plan(cuda_device)
+    _, lm = plan.features_logmel(stems, False, True)
+    g = torch.randn(lm.shape, generator=torch.Generator().manual_seed(T)).to(cuda_device)
+    n0 = pkg.launch_count()
+    slow = plan.logmel_backward(stems, g)
+    assert pkg.launch_count() - n0 == 1
+    fast = plan.logmel_backward(stems, g, logmel=lm)
+    assert pkg.launch_count() - n0 == 3                          # + strip zeroing + K6E
+    again = plan.logmel_backward(stems, g, logmel=lm)
+    for a, b_, c in zip(slow, fast, again):
+        scale = float(a.abs().max())
+        assert float((a - b_).abs().max()) <= 2e-4 * scale, (T, float((a - b_).abs().max()), scale)
+        assert torch.equal(b_, c)
+
+
+def test_fast_backward_2048_batched_strided_and_unaligned(cuda_device):
+    """Rows that start on odd float offsets (no 8-byte alignment: the scalar load / store paths) inside a wider buffer."""
+    T = 9001
+    clips = [_noisy_clip(170 + i, T) for i in range(3)]
+    wide = torch.zeros(3, 8, T + 7, device=cuda_device)
+    for i, c in enumerate(clips):
+        for k, n in enumerate(O.STEMS):
+            wide[i, 2 * k:2 * k + 2, 3:3 + T] = c[n].to(cuda_device)
+    views = [wide[:, 2 * k:2 * k + 2, 3:3 + T] for k in range(4)]
+    plan = pkg.MelSpectrogramPreprocessor(44100, 2048, 512, 80)._plan(cuda_device)
+    _, lm = plan.features_logmel(views, False, True)
+    g = torch.randn(lm.shape, generator=torch.Generator().manual_seed(1)).to(cuda_device)
+    fast = plan.logmel_backward(views, g, logmel=lm)
+    slow = plan.logmel_backward(views, g)
+    for a, b_ in zip(slow, fast):
+        assert float((a - b_).abs().max()) <= 2e-4 * float(a.abs().max())
     for i in range(3):
         one = [v[i:i + 1].contiguous() for v in views]
         ref = plan.logmel_backward(one, g[i:i + 1], logmel=lm[i:i + 1])
