@@ -112,11 +112,13 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
         mbar_init(bar, 1);
         *arrivals = 0;
     }
-    // per-lane constants: window phase B = pi (2 lane + par) / 1024; the odd warp's W_2048^lane
-    float cb, sb, wlx, wly;
-    sincospif((float)(2 * lane + par) * (1.0f / 1024.0f), &sb, &cb);
+    // per-lane constants: the window phases B_c = pi (2 lane + c) / 1024 of the even (c = 0) and odd (c = 1) samples, and
+    // W_2048^lane = exp(-i pi lane / 1024)
+    float cb0, sb0, cb1, sb1, wlx, wly;
+    sincospif((float)(2 * lane) * (1.0f / 1024.0f), &sb0, &cb0);
+    sincospif((float)(2 * lane + 1) * (1.0f / 1024.0f), &sb1, &cb1);
     sincospif((float)lane * (1.0f / 1024.0f), &wly, &wlx);
-    wly = -wly;                                         // exp(-i pi lane / 1024)
+    wly = -wly;
     __syncthreads();
 
     unsigned char* const region = ex + warp * kWarpRegion;
@@ -146,21 +148,18 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
             cplx64 z[32];
             const bool active = q < nvalid;
             if (active) {
-                // even / odd samples of frame q, window 0.5 * hann2048[2 m + par], m = 32 n1 + lane
-                const unsigned xa = smem_u32(xsL + q * p.hop + par + 2 * lane);
-                const unsigned xr_off = (unsigned)p.nxs * 4u;
-                float fl[32], fr[32];
+                // channel `par` of frame q as z[m] = x[2m] + i x[2m+1], m = 32 n1 + lane, window 0.5 * hann2048 folded in
+                const unsigned xa = smem_u32(xsL + par * p.nxs + q * p.hop + 2 * lane);
+                float2 f[32];
 #pragma unroll
-                for (int n1 = 0; n1 < 32; ++n1) {
-                    fl[n1] = lds32(xa + n1 * 256);
-                    fr[n1] = lds32(xa + xr_off + n1 * 256);
-                }
+                for (int n1 = 0; n1 < 32; ++n1) f[n1] = lds64<0>(xa + n1 * 256);
 #pragma unroll
                 for (int n1 = 0; n1 < 32; ++n1) {
                     const float ca = n1 < 16 ? w32_re(n1) : -w32_re(n1 - 16);
                     const float sa = n1 < 16 ? w32_sin(n1) : -w32_sin(n1 - 16);
-                    const float wv = fmaf(0.25f * sa, sb, fmaf(-0.25f * ca, cb, 0.25f));
-                    z[n1] = cpack(fl[n1] * wv, fr[n1] * wv);
+                    const float w0 = fmaf(0.25f * sa, sb0, fmaf(-0.25f * ca, cb0, 0.25f));
+                    const float w1 = fmaf(0.25f * sa, sb1, fmaf(-0.25f * ca, cb1, 0.25f));
+                    z[n1] = cpack(f[n1].x * w0, f[n1].y * w1);
                 }
             }
             // ---- prefetch the next (tile, stem): the last warp to have its samples in registers starts the copy -------
@@ -227,55 +226,37 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                         __syncwarp();
                     }
                 }
-                // slot k2 (register brev5(k2)) holds bin lane + 32 k2 of E (even warp) or O (odd warp).
-                // Park the spectrum as rows [k2][lane] (256 bytes each) + row 32 = row 0 (the partner of lane 0's row r
-                // is row 32 - r); the odd warp first applies W_2048^(lane + 32 k2) = W_2048^lane * W_64^k2.
-                const unsigned pa = smem_u32(region) + lane * 8;
-#pragma unroll
-                for (int k2 = 0; k2 < 32; ++k2) {
-                    float vr, vi;
-                    cunpack(z[brev5(k2)], vr, vi);
-                    if (par) {
-                        const float c = cos64(k2), sn = sin64(k2);             // W_64^k2 = c - i sn
-                        const float tr = k2 == 0 ? vr : (k2 == 16 ? vi : fmaf(vr, c, vi * sn));
-                        const float ti = k2 == 0 ? vi : (k2 == 16 ? -vr : fmaf(vi, c, -vr * sn));
-                        vr = fmaf(tr, wlx, -ti * wly);
-                        vi = fmaf(tr, wly, ti * wlx);
-                    }
-                    sts64<0>(pa + k2 * 256, vr, vi);
-                    if (k2 == 0) sts64<0>(pa + 32 * 256, vr, vi);
-                }
             }
-            named_bar(1 + q, 64);            // the pair's spectra are parked
-            float2 pw[16];
-            float2 pw1024 = make_float2(0.0f, 0.0f);
+            // Slot k2 (register brev5(k2)) holds Z[k], k = lane + 32 k2; its partner Z[1024 - k] sits in lane (32 - lane) & 31,
+            // slot 31 - k2 (lane 0: its own slot 32 - k2).  With x^ = Z[k], y^ = Z[1024 - k]:  Se = x^ + conj y^,
+            // So = (x^ - conj y^) / i,  X[k] = Se + w So,  X[1024 - k] = conj(Se - w So),  w = W_2048^k = W_2048^lane W_64^k2.
+            // The lane that holds the lower bin writes both powers into this channel's component of the frame's (L, R) column.
+            named_bar(1 + q, 64);            // both warps of the frame are past their transposition: their regions become the column
             if (active) {
-                // rows r = 16 par + j: bin k = lane + 32 r; partner 1024 - k in row 31 - r (+ 1 for lane 0), lane (32 - lane) & 31
-                const unsigned eo = smem_u32(regE), oo = smem_u32(regO);
-                const unsigned own = (unsigned)(16 * par) * 256u + (unsigned)lane * 8u;
-                const unsigned prt = (unsigned)(31 - 16 * par) * 256u + (lane == 0 ? 256u : 0u) + (unsigned)((32 - lane) & 31) * 8u;
+                float* const colf = reinterpret_cast<float*>(regE + kEColOff) + par;
+                const int src = (32 - lane) & 31;
+                const bool l0 = lane == 0;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float2 e = lds64<0>(eo + own + j * 256), o = lds64<0>(oo + own + j * 256);
-                    const float2 ep = lds64<0>(eo + prt - j * 256), op = lds64<0>(oo + prt - j * 256);
-                    const float xr = e.x + o.x, xi = e.y + o.y;               // X[k]
-                    const float yr = ep.x - op.x, yi = ep.y - op.y;           // X[2048 - k]
-                    const float a = xr + yr, bb = xi - yi, c = xr - yr, d = xi + yi;
-                    pw[j] = make_float2(fmaf(a, a, bb * bb), fmaf(c, c, d * d));
+                for (int k2 = 0; k2 < 16; ++k2) {
+                    float xx, xy, yx, yy;
+                    cunpack(z[brev5(k2)], xx, xy);
+                    cunpack(l0 ? z[brev5((32 - k2) & 31)] : z[brev5(31 - k2)], yx, yy);
+                    yx = __shfl_sync(kFullMask, yx, src);
+                    yy = __shfl_sync(kFullMask, yy, src);
+                    const float sex = xx + yx, sey = xy - yy, sox = xy + yy, soy = yx - xx;
+                    const float c = cos64(k2), sn = sin64(k2);                 // W_64^k2 = c - i sn
+                    const float wr = k2 == 0 ? wlx : fmaf(wlx, c, wly * sn), wi = k2 == 0 ? wly : fmaf(wly, c, -wlx * sn);
+                    const float tx = fmaf(wr, sox, -wi * soy), ty = fmaf(wr, soy, wi * sox);
+                    const float ar = sex + tx, ai = sey + ty, br = sex - tx, bi = sey - ty;
+                    const int k = lane + 32 * k2;
+                    colf[2 * k] = fmaf(ar, ar, ai * ai);
+                    colf[2 * (1024 - k)] = fmaf(br, br, bi * bi);              // (lane 0, k2 = 0: bins 0 and 1024)
                 }
-                if (par == 0 && lane == 0) {          // bins 0 = E[0] + O'[0] and 1024 = E[0] - O'[0] are their own partners
-                    const float2 e = lds64<0>(eo), o = lds64<0>(oo);
-                    const float sr = e.x + o.x, si = e.y + o.y, xr = e.x - o.x, xi = e.y - o.y;
-                    pw[0] = make_float2(4.0f * sr * sr, 4.0f * si * si);
-                    pw1024 = make_float2(4.0f * xr * xr, 4.0f * xi * xi);
+                if (l0) {                    // bin 512 is its own partner: X[512] = conj Z[512] * 2
+                    float xx, xy;
+                    cunpack(z[brev5(16)], xx, xy);
+                    colf[2 * 512] = 4.0f * fmaf(xx, xx, xy * xy);
                 }
-            }
-            named_bar(1 + q, 64);            // both warps have read the parked spectra: the regions become the power column
-            if (active) {
-                float2* const col = reinterpret_cast<float2*>(regE + kEColOff);
-#pragma unroll
-                for (int j = 0; j < 16; ++j) col[lane + 32 * (16 * par + j)] = pw[j];
-                if (par == 0 && lane == 0) col[1024] = pw1024;
             }
             __syncthreads();                 // B1: the 4 power columns of the tile are complete
 
