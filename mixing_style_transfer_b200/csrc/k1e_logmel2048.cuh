@@ -4,12 +4,15 @@
 //
 // Reference behaviour being replaced: MelSpectrogramPreprocessor.forward (src/model.py:41-67) for that configuration.
 //
-// A 2048-point frame does not fit the register-resident transform (64 complex values per lane), so it is split by
-// decimation in time: E = FFT_1024(even samples), O = FFT_1024(odd samples), X[k] = E[k] + W_2048^k O[k],
-// X[k + 1024] = E[k] - W_2048^k O[k].  TWO WARPS share a frame: the even warp and the odd warp each run K1's transform on
-// their windowed half (L and R packed as one complex sequence), the odd warp applies W_2048^k, both park their
-// spectra in their exchange regions, and each then forms half of the frame's 1025 (L, R) powers from shared memory:
-//   X[k] = E[k] + O'[k],  X[2048 - k] = E[1024 - k] - O'[1024 - k],  P_L = |X[k] + conj X[2048 - k]|^2,  P_R = |X[k] - conj X[2048 - k]|^2.
+// A 2048-sample REAL frame of one channel is one 1024-point COMPLEX transform of z[m] = x[2m] + i x[2m+1] (the real-FFT
+// packing), so ONE WARP handles one (frame, channel) on K1's register-resident transform.  With Z = FFT_1024(z),
+// x^ = Z[k], y^ = Z[1024 - k], w = exp(-2 pi i k / 2048) and the window 0.5 hann folded into z:
+//   Se = x^ + conj y^,  So = (x^ - conj y^) / i,  X[k] = Se + w So,  X[1024 - k] = conj(Se - w So),  P = |X|^2;
+// the partner bin comes from lane (32 - lane) & 31 by shuffle and the lane that holds the lower bin writes both powers
+// into its channel's component of the frame's (L, R) power column.  The two warps of a frame (L, R) meet at ONE pair
+// barrier before their exchange regions become that column.  (The first cut split a frame by decimation in time over an
+// even and an odd warp with L + iR packing: parked spectra, two pair barriers, 64 shared-memory loads per lane: 2.09 ms
+// against 1.73 ms per 72 clips.)
 // A CTA (8 warps, 2 per SM, persistent) therefore handles tiles of 4 frames; staging (TMA bulk copies one (tile, stem) ahead,
 // cooperative loads with torch's 'reflect' at the clip edges), the exchange layout and the log epilogue are K1's.
 // Mel projection: thread = (work item, frame pair).  The filterbank by filter (CSR) is cut into at most 128 items, the
@@ -21,7 +24,7 @@
 
 namespace mixfe {
 
-constexpr int kETF = 4;                  // frames per tile (2 warps each)
+constexpr int kETF = 4;                  // frames per tile (2 warps each: L, R)
 constexpr int kEThreads = 256;
 constexpr int kEItems = 128;             // mel work items per frame pair
 constexpr int kEColOff = kWarpRegion - 4096;      // the power column starts here in the even warp's region and runs on
