@@ -226,13 +226,17 @@ __device__ __forceinline__ float cfold(cplx64 v) {
     return x + y;
 }
 
-__device__ __forceinline__ void k1_time_stats(const K1Params& p, int b, int tile, int tid) {
+// (P: K1Params or K1EParams -- any parameter block with stem, stride_b, stride_c, T, hop, n_tiles, part_td; an eighth of the
+// region a tile owns is p.hop / DIV samples: DIV = 1 for K1's tiles of 8 frames, 2 for K1E's tiles of 4.  The value is
+// re-read from the parameter bank at every use: as a register it pushed K1 over its 128.)
+template <int DIV, class P>
+__device__ __forceinline__ void k1_time_stats(const P& p, int b, int tile, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
-    const long long own0 = (long long)tile * kTF * p.hop;
+    const long long own0 = (long long)tile * kTF * (p.hop / DIV);
     const long long rem = (long long)p.T - own0;
-    const int own_n = rem < 0 ? 0 : (rem > (long long)kTF * p.hop ? kTF * p.hop : (int)rem);
+    const int own_n = rem < 0 ? 0 : (rem > (long long)kTF * (p.hop / DIV) ? kTF * (p.hop / DIV) : (int)rem);
     const long long cb = (long long)b * p.stride_b + own0;
-    unsigned long long amask = (unsigned long long)(p.hop & 3);
+    unsigned long long amask = (unsigned long long)((p.hop / DIV) & 3);
 #pragma unroll
     for (int s = 0; s < kNumStems; ++s)
         amask |= reinterpret_cast<unsigned long long>(p.stem[s] + cb) |
@@ -243,8 +247,8 @@ __device__ __forceinline__ void k1_time_stats(const K1Params& p, int b, int tile
     // ---- role A: stem (warp & 3), half (warp >> 2) -------------------------------------------------
     {
         const int s = warp & 3;
-        const int r0 = (warp >> 2) * (kTF / 2) * p.hop;
-        const int r1 = min(own_n, r0 + (kTF / 2) * p.hop);
+        const int r0 = (warp >> 2) * (kTF / 2) * (p.hop / DIV);
+        const int r1 = min(own_n, r0 + (kTF / 2) * (p.hop / DIV));
         const float* gL = p.stem[s] + cb;
         const float* gR = gL + p.stride_c;
         K1StemAcc a;
@@ -283,8 +287,8 @@ __device__ __forceinline__ void k1_time_stats(const K1Params& p, int b, int tile
     }
     // ---- role M: mixture energy of eighth `warp` ----------------------------------------------------
     {
-        const int r0 = warp * p.hop;
-        const int r1 = min(own_n, r0 + p.hop);
+        const int r0 = warp * (p.hop / DIV);
+        const int r1 = min(own_n, r0 + (p.hop / DIV));
         cplx64 e = 0ull;
         int i = r0;
         if (vec) {
@@ -331,12 +335,13 @@ __device__ __forceinline__ void k1_time_stats(const K1Params& p, int b, int tile
 
 // The same roles on rows the TMA engine has put into shared memory: row (2 stem + channel) holds the tile's own
 // region (kTF * hop <= 2048 samples, all of them inside the clip) at rows + 8 KB * row.
-__device__ __forceinline__ void k1_time_stats_smem(const K1Params& p, const unsigned char* rows, int b, int tile, int tid) {
+template <int DIV, class P>
+__device__ __forceinline__ void k1_time_stats_smem(const P& p, const unsigned char* rows, int b, int tile, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
     float* rec = p.part_td + ((long long)b * p.n_tiles + tile) * (2 * kTdN) + (warp >> 2) * kTdN;
     {
         const int s = warp & 3;
-        const int n4 = (kTF / 2) * p.hop / 4;                    // float4 per row of this half
+        const int n4 = (kTF / 2) * (p.hop / DIV) / 4;                    // float4 per row of this half
         const float4* rL = reinterpret_cast<const float4*>(rows + (2 * s) * kWarpRegion) + (warp >> 2) * n4;
         const float4* rR = rL + kWarpRegion / 16;
         K1StemAcc a;
@@ -359,7 +364,7 @@ __device__ __forceinline__ void k1_time_stats_smem(const K1Params& p, const unsi
         }
     }
     {
-        const int n4 = p.hop / 4;                                // float4 per row of this eighth
+        const int n4 = (p.hop / DIV) / 4;                                // float4 per row of this eighth
         const float4* r0 = reinterpret_cast<const float4*>(rows) + warp * n4;
         cplx64 e = 0ull;
 #pragma unroll 2
@@ -462,7 +467,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
                     }
                     stats_rows = true;       // consumed below, after this warp's frame is in registers
                 } else {
-                    k1_time_stats(p, b, tile, tid);
+                    k1_time_stats<1>(p, b, tile, tid);
                 }
             }
 
@@ -545,7 +550,7 @@ __global__ void __launch_bounds__(kK1Threads, 2) k1_features(const __grid_consta
             if (stats_rows) {                // the copy had the frame load to land
                 mbar_wait(bar2, stats_parity);
                 stats_parity ^= 1u;
-                k1_time_stats_smem(p, ex, b, tile, tid);
+                k1_time_stats_smem<1>(p, ex, b, tile, tid);
                 __syncthreads();             // the rows are dead: the exchange regions go back to their warps
             }
 
@@ -735,6 +740,7 @@ struct K2Params {
     int B, T, F, n_mels, n_mels_pad, n_tiles;
     int n_bins;                      // 0: low/mid/high bands, else detailed curve of n_bins points
     int D;
+    int n_spec_tiles;                // entries of part_spec per clip (n_tiles for K1 / K1G, 2 n_tiles for K1E: one per frame pair)
     int mask_per_warp;               // masking sums: 1 = slots kTdMask.. of both records (K1), 0 = slots 33..36 of record 0 (K1G)
 };
 
@@ -762,10 +768,10 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         const int s = tid >> 7, m = tid & 127;
         double slog = 0.0, smel = 0.0;
         if (m < p.n_mels) {
-            const float2* src = p.part_spec + ((long long)b * p.n_tiles * kNumStems + s) * p.n_mels_pad + m;
+            const float2* src = p.part_spec + ((long long)b * p.n_spec_tiles * kNumStems + s) * p.n_mels_pad + m;
             const long long step = (long long)kNumStems * p.n_mels_pad;
 #pragma unroll 8
-            for (int t = 0; t < p.n_tiles; ++t) {
+            for (int t = 0; t < p.n_spec_tiles; ++t) {
                 const float2 v = __ldg(src + t * step);
                 slog += (double)v.x;
                 smel += (double)v.y;

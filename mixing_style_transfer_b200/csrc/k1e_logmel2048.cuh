@@ -45,6 +45,13 @@ struct K1EParams {
     const float* wts;                // CSR weights
     int n_wts;
     int off_ex, off_tw, off_items, off_wts, off_bar;
+    // statistics for the mixing features (want_stats): K1's partials, reduced by K2
+    int want_stats, n_mels_pad;
+    int rows_hi;                     // tiles 0..rows_hi get their time-statistics rows by TMA (-1 = none)
+    float2* part_spec;               // [B][2 n_tiles][4][n_mels_pad] (sum log, sum mel): one entry per frame PAIR
+    float* part_td;                  // [B][n_tiles][2][kTdN] (k1_features.cuh)
+    float2* s_ws;                    // [grid][3][256]: S values of stems 0..2 for the masking term, one slab per CTA (global,
+                                     // L2-resident: 6 KB more of shared memory would cost the second CTA per SM)
 };
 
 // cos / sin of 2 pi j / 64, j = 0..31 (compile-time after unrolling)
@@ -92,6 +99,8 @@ __device__ __forceinline__ void k1e_stage_coop(const K1EParams& p, int b, int ti
     }
 }
 
+// STATS: also K1's partials for the mixing features (compile-time: the log-mel-only kernel keeps its register budget)
+template <bool STATS>
 __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_constant__ K1EParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float* const xsL = reinterpret_cast<float*>(smem);                          // [nxs] left, then [nxs] right
@@ -101,6 +110,8 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
     float* const wts = reinterpret_cast<float*>(smem + p.off_wts);
     const unsigned bar = smem_u32(smem + p.off_bar);
     int* const arrivals = reinterpret_cast<int*>(smem + p.off_bar + 8);
+    const unsigned bar2 = smem_u32(smem + p.off_bar + 24);                      // mbarrier of the statistics rows
+    float2* const S = STATS ? p.s_ws + (size_t)blockIdx.x * (3 * kEThreads) : nullptr;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q = warp >> 1, par = warp & 1;            // frame of the tile, even / odd half
@@ -113,6 +124,7 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
     for (int i = tid; i < p.n_wts; i += kEThreads) wts[i] = p.wts[i];
     if (tid == 0) {
         mbar_init(bar, 1);
+        mbar_init(bar2, 1);
         *arrivals = 0;
     }
     // per-lane constants: the window phases B_c = pi (2 lane + c) / 1024 of the even (c = 0) and odd (c = 1) samples, and
@@ -131,7 +143,7 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
 
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
     bool cur_tma = tile >= p.tma_lo && tile <= p.tma_hi;
-    unsigned tma_parity = 0;
+    unsigned tma_parity = 0, stats_parity = 0;
     if (cur_tma) { if (tid == 0) k1e_stage_tma(p, b, tile, 0, xsL, bar); } else k1e_stage_coop(p, b, tile, 0, xsL, tid);
 
     for (;;) {
@@ -140,6 +152,7 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
         long long next_item = item + gridDim.x;
         int drawn = 0;
         if (p.work && tid == 0) drawn = atomicAdd(p.work, 1);         // in flight until the last stem needs it
+        float msum[4] = {0.0f, 0.0f, 0.0f, 0.0f};                     // masking partial sums of this thread
         for (int s = 0; s < kNumStems; ++s) {
             if (cur_tma) {
                 mbar_wait(bar, tma_parity);
@@ -148,6 +161,27 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
             if (p.work && s == kNumStems - 1 && tid == 0) *next_slot = drawn;
             __syncthreads();                 // B0: xs holds (tile, s); the previous mel walk has left the power columns
             if (p.work && s == kNumStems - 1) next_item = (long long)gridDim.x + *next_slot;
+            bool stats_rows = false;
+            if (STATS && s == 0) {
+                // time-domain statistics of the tile's own region (kETF * hop samples = eight "hops" of hop / 2 for K1's
+                // role code): the 8 rows by TMA into the idle exchange regions, or role loads from global memory
+                if (tile <= p.rows_hi) {
+                    if (tid == 0) {
+                        const long long cb = (long long)b * p.stride_b + (long long)tile * kETF * p.hop;
+                        const unsigned bytes = (unsigned)(kETF * p.hop) * 4u;
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_expect_tx(bar2, 8u * bytes);
+#pragma unroll
+                        for (int r = 0; r < kNumStems; ++r) {
+                            tma_bulk_g2s(smem_u32(ex + (2 * r) * kWarpRegion), p.stem[r] + cb, bytes, bar2);
+                            tma_bulk_g2s(smem_u32(ex + (2 * r + 1) * kWarpRegion), p.stem[r] + cb + p.stride_c, bytes, bar2);
+                        }
+                    }
+                    stats_rows = true;       // consumed below, after this warp's frame is in registers
+                } else {
+                    k1_time_stats<2>(p, b, tile, tid);
+                }
+            }
             cplx64 z[32];
             const bool active = q < nvalid;
             if (active) {
@@ -192,6 +226,12 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                     }
                 }
                 cur_tma = next_tma;
+            }
+            if (stats_rows) {                // the copy had the frame load to land
+                mbar_wait(bar2, stats_parity);
+                stats_parity ^= 1u;
+                k1_time_stats_smem<2>(p, ex, b, tile, tid);
+                __syncthreads();             // the rows are dead: the exchange regions go back to their warps
             }
             if (active) {
 #pragma unroll 1
@@ -291,12 +331,57 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
                     const float o2 = __shfl_xor_sync(kFullMask, a2, d), o3 = __shfl_xor_sync(kFullMask, a3, d);
                     if (lg_parts >= d) { a0 += o0; a1 += o1; a2 += o2; a3 += o3; }
                 }
-                if (!second && m >= 0 && m < p.n_mels && p.logmel) {
+                if constexpr (!STATS) {
+                    if (!second && m >= 0 && m < p.n_mels && p.logmel) {
+                        const int u = u0 + 2 * fp;
+                        float* d0 = p.logmel + (long long)b * p.lm_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + u;
+                        float* d1 = d0 + (long long)p.n_mels * p.F;
+                        if (u < p.F) { d0[0] = ln_fast(a0 + 1e-10f); d1[0] = ln_fast(a1 + 1e-10f); }
+                        if (u + 1 < p.F) { d0[1] = ln_fast(a2 + 1e-10f); d1[1] = ln_fast(a3 + 1e-10f); }
+                    }
+                } else {
                     const int u = u0 + 2 * fp;
-                    float* d0 = p.logmel + (long long)b * p.lm_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + u;
-                    float* d1 = d0 + (long long)p.n_mels * p.F;
-                    if (u < p.F) { d0[0] = ln_fast(a0 + 1e-10f); d1[0] = ln_fast(a1 + 1e-10f); }
-                    if (u + 1 < p.F) { d0[1] = ln_fast(a2 + 1e-10f); d1[1] = ln_fast(a3 + 1e-10f); }
+                    const bool owner = !second && m >= 0 && m < p.n_mels;      // one thread per (filter, frame pair)
+                    const bool ok0 = u < p.F, ok1 = u + 1 < p.F;
+                    const float lg0 = ln_fast(a0 + 1e-10f), lg1 = ln_fast(a1 + 1e-10f);
+                    const float lg2 = ln_fast(a2 + 1e-10f), lg3 = ln_fast(a3 + 1e-10f);
+                    if (owner && p.logmel) {
+                        float* d0 = p.logmel + (long long)b * p.lm_stride_b + ((long long)(2 * s) * p.n_mels + m) * p.F + u;
+                        float* d1 = d0 + (long long)p.n_mels * p.F;
+                        if (ok0) { d0[0] = lg0; d1[0] = lg1; }
+                        if (ok1) { d0[1] = lg2; d1[1] = lg3; }
+                    }
+                    // K1's partials: per (stem, filter) sums of log and power over the frame pair; S = (mel_L + mel_R) / 2
+                    // kept per thread for stems 0..2, the masking sigmoids at the last stem
+                    const long long tile_id = (long long)b * p.n_tiles + tile;
+                    if (owner) {
+                        const float slog = (ok0 ? lg0 + lg1 : 0.0f) + (ok1 ? lg2 + lg3 : 0.0f);
+                        const float smel = (ok0 ? a0 + a1 : 0.0f) + (ok1 ? a2 + a3 : 0.0f);
+                        p.part_spec[((2 * tile_id + fp) * kNumStems + s) * p.n_mels_pad + m] = make_float2(slog, smel);
+                    }
+                    const float sc0 = 0.5f * (a0 + a1), sc1 = 0.5f * (a2 + a3);
+                    if (s < 3) {
+                        S[s * kEThreads + tid] = make_float2(sc0, sc1);
+                    } else {
+                        const float2 A0 = S[tid], A1 = S[kEThreads + tid], A2 = S[2 * kEThreads + tid];
+                        const float s0[2] = {A0.x, A0.y}, s1[2] = {A1.x, A1.y}, s2[2] = {A2.x, A2.y}, s3[2] = {sc0, sc1};
+                        const bool ok[2] = {owner && ok0, owner && ok1};
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            if (ok[i]) {
+                                const float m01 = fmaxf(s0[i], s1[i]), m23 = fmaxf(s2[i], s3[i]);
+                                msum[0] += fast_sigmoid_neg(s0[i] - fmaxf(s1[i], m23));
+                                msum[1] += fast_sigmoid_neg(s1[i] - fmaxf(s0[i], m23));
+                                msum[2] += fast_sigmoid_neg(s2[i] - fmaxf(m01, s3[i]));
+                                msum[3] += fast_sigmoid_neg(s3[i] - fmaxf(m01, s2[i]));
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) msum[i] = warp_sum(msum[i]);
+                        if (lane == 0)           // the warp's own slots of the tile's records (K1's layout)
+                            *reinterpret_cast<float4*>(p.part_td + tile_id * (2 * kTdN) + (warp >> 2) * kTdN + kTdMask + (warp & 3) * 4) =
+                                make_float4(msum[0], msum[1], msum[2], msum[3]);
+                    }
                 }
             }
         }

@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(kGThreads, 3) k1g_features(const __grid_consta
     const unsigned mg_nb = k1g_magic(half + 1), mg_mp = k1g_magic(p.n_mels_pad);
 
     if (p.want_stats) {
-        k1_time_stats(p, b, tile, tid);
+        k1_time_stats<1>(p, b, tile, tid);
     }
 
     for (int s = 0; s < kNumStems; ++s) {

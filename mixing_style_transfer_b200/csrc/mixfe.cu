@@ -453,10 +453,12 @@ int build_k1e_tables(mixfe_plan* pl) {
         MIXFE_CUDA(cudaMalloc(&pl->d_k1_work, 2 * sizeof(int)));
         MIXFE_CUDA(cudaMemset(pl->d_k1_work, 0, 2 * sizeof(int)));
     }
-    if ((rc = smem_optin(k1e_logmel2048, pl->device, pl->smem_e))) return rc;
+    if ((rc = smem_optin(k1e_logmel2048<false>, pl->device, pl->smem_e)) || (rc = smem_optin(k1e_logmel2048<true>, pl->device, pl->smem_e)))
+        return rc;
     int per_sm = 0;
-    MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1e_logmel2048, kEThreads, pl->smem_e));
+    MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1e_logmel2048<true>, kEThreads, pl->smem_e));
     pl->e_ctas = std::max(1, per_sm) * pl->n_sms;
+    if (std::getenv("MIXFE_DEBUG")) fprintf(stderr, "K1E: smem %d, %d CTAs per SM\n", pl->smem_e, per_sm);
     return MIXFE_OK;
 }
 
@@ -567,8 +569,10 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
             p.rows_hi = (int)std::min<long long>((long long)T / tile_span - 1, n_tiles - 1);   // (tile + 1) * span <= T
     }
     const char* force_g = getenv("MIXFE_FORCE_GENERIC");
-    if (pl->d_eitems && !features && !melpow && logmel && !(force_g && atoi(force_g))) {
-        // K1E: log-mel only, n_fft = 2048, on the one-warp 1024-point transform (two warps per frame)
+    if (pl->d_eitems && !melpow && (logmel || (features && pl->hop % 8 == 0)) && (!features || pl->hop % 8 == 0) &&
+        !(force_g && atoi(force_g))) {
+        // K1E: n_fft = 2048 on the one-warp 1024-point transform (one warp per (frame, channel)); log-mel and, for hops
+        // that are multiples of 8, K1's statistics for the mixing features
         K1EParams e{};
         for (int s = 0; s < 4; ++s) e.stem[s] = stems[s];
         e.stride_b = stride_b; e.stride_c = stride_c; e.B = B; e.T = T; e.F = F; e.hop = pl->hop; e.n_mels = pl->n_mels;
@@ -580,6 +584,20 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         bool aligned = (stride_b % 4 == 0 || B == 1) && stride_c % 4 == 0;
         for (int s = 0; s < 4; ++s) aligned = aligned && (reinterpret_cast<uintptr_t>(stems[s]) & 15u) == 0;
         const long long span = (long long)kETF * pl->hop;
+        const size_t e_spec_bytes = (size_t)B * 2 * e.n_tiles * kNumStems * pl->n_mels_pad * sizeof(float2);
+        const size_t e_td_bytes = (size_t)B * e.n_tiles * 2 * kTdN * sizeof(float);
+        e.want_stats = features ? 1 : 0; e.n_mels_pad = pl->n_mels_pad; e.rows_hi = -1;
+        const int e_grid = (int)std::min<long long>(e.total_items, (long long)pl->e_ctas);
+        if (features) {
+            const size_t s_bytes = (size_t)e_grid * 3 * kEThreads * sizeof(float2);
+            int rc = ensure_workspace(pl, e_spec_bytes + e_td_bytes + s_bytes, stream);
+            if (rc) return rc;
+            e.part_spec = reinterpret_cast<float2*>(pl->ws);
+            e.part_td = reinterpret_cast<float*>(reinterpret_cast<char*>(pl->ws) + e_spec_bytes);
+            e.s_ws = reinterpret_cast<float2*>(reinterpret_cast<char*>(pl->ws) + e_spec_bytes + e_td_bytes);
+            if (aligned && pl->hop % 32 == 0 && span * 4 <= kWarpRegion)
+                e.rows_hi = (int)std::min<long long>((long long)T / span - 1, e.n_tiles - 1);      // (tile + 1) * span <= T
+        }
         e.tma_lo = 1; e.tma_hi = 0;
         if (aligned) {
             e.tma_lo = (int)((1024 + span - 1) / span);                            // tile * span - 1024 >= 0
@@ -588,13 +606,27 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         }
         {
             KernelTimer timer(pl, MIXFE_KERNEL_FEATURES, stream);
-            const int grid = (int)std::min<long long>(e.total_items, (long long)pl->e_ctas);
+            const int grid = e_grid;
             static const bool dynamic = !(std::getenv("MIXFE_K1_DYNAMIC") && std::atoi(std::getenv("MIXFE_K1_DYNAMIC")) == 0);
             e.work = dynamic ? pl->d_k1_work : nullptr;
-            k1e_logmel2048<<<grid, kEThreads, pl->smem_e, stream>>>(e);
+            if (features) k1e_logmel2048<true><<<grid, kEThreads, pl->smem_e, stream>>>(e);
+            else k1e_logmel2048<false><<<grid, kEThreads, pl->smem_e, stream>>>(e);
         }
         MIXFE_CUDA(cudaGetLastError());
         launch_counter()++;
+        if (features) {
+            K2Params q{};
+            q.part_spec = e.part_spec; q.part_td = e.part_td; q.features = features;
+            q.B = B; q.T = T; q.F = F; q.n_mels = pl->n_mels; q.n_mels_pad = pl->n_mels_pad; q.n_tiles = e.n_tiles;
+            q.n_spec_tiles = 2 * e.n_tiles;
+            q.n_bins = pl->n_bins; q.D = pl->D; q.mask_per_warp = 1;
+            {
+                KernelTimer timer(pl, MIXFE_KERNEL_FINALIZE, stream);
+                k2_finalize<<<B, kK2Threads, 0, stream>>>(q);
+            }
+            MIXFE_CUDA(cudaGetLastError());
+            launch_counter()++;
+        }
         return MIXFE_OK;
     }
     if (pl->use_generic) {
@@ -622,6 +654,7 @@ int run_features(mixfe_plan* pl, const float* const stems[4], long long stride_b
         K2Params q{};
         q.part_spec = p.part_spec; q.part_td = p.part_td; q.features = features;
         q.B = B; q.T = T; q.F = F; q.n_mels = pl->n_mels; q.n_mels_pad = pl->n_mels_pad; q.n_tiles = n_tiles;
+        q.n_spec_tiles = n_tiles;
         q.n_bins = pl->n_bins; q.D = pl->D; q.mask_per_warp = pl->use_generic ? 0 : 1;
         {
             KernelTimer timer(pl, MIXFE_KERNEL_FINALIZE, stream);
