@@ -458,7 +458,6 @@ int build_k1e_tables(mixfe_plan* pl) {
     int per_sm = 0;
     MIXFE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1e_logmel2048<true>, kEThreads, pl->smem_e));
     pl->e_ctas = std::max(1, per_sm) * pl->n_sms;
-    if (std::getenv("MIXFE_DEBUG")) fprintf(stderr, "K1E: smem %d, %d CTAs per SM\n", pl->smem_e, per_sm);
     return MIXFE_OK;
 }
 

@@ -194,3 +194,33 @@ def test_k1e_lengths_hops_and_unaligned_views(cuda_device, hop, n_mels, T):
     for i, c in enumerate(clips):
         ref = O.log_mel({n: v[None] for n, v in c.items()}, cfg, dtype=torch.float64)
         assert_logmel_close(lm_u[i:i + 1], ref, f"K1E hop={hop} n_mels={n_mels} T={T} clip {i}")
+
+
+@pytest.mark.parametrize("hop,n_mels,T", [(512, 80, 1025), (512, 80, 2048), (512, 80, 4097), (512, 80, 10240 + 3), (512, 128, 30000),
+                                          (256, 96, 9001), (1024, 64, 20000), (520, 80, 12345), (96, 40, 7000), (2048, 40, 33333)])
+def test_k1e_features_lengths_hops_and_unaligned_views(cuda_device, hop, n_mels, T):
+    """K1E with statistics (mixing features of n_fft = 2048 plans whose hop is a multiple of 8): clip lengths around the
+    4-frame tiles, hops with (32 | hop: TMA statistics rows) and without (global role loads), ragged filter counts, and
+    views that start 1..3 floats into a wider tensor.  Features against the oracle; aligned and unaligned inputs agree
+    bit for bit; K1 + K2 = two launches."""
+    cfg = O.FrontEndConfig(n_fft=2048, hop_length=hop, n_mels=n_mels)
+    clips = [O.musical_clip(900 + T % 89 + i, T) for i in range(2)]
+    off = 1 + T % 3
+    wide = torch.zeros(2, 8, T + 8, device=cuda_device)
+    for i, c in enumerate(clips):
+        for k, n in enumerate(O.STEMS):
+            wide[i, 2 * k:2 * k + 2, off:off + T] = c[n].to(cuda_device)
+    fe = pkg.MixingFeatureExtractor(44100, 2048, hop, n_mels)
+    views = {n: wide[:, 2 * k:2 * k + 2, off:off + T] for k, n in enumerate(O.STEMS)}
+    n0 = pkg.launch_count()
+    f_u, lm_u = fe.features_and_logmel(views)
+    assert pkg.launch_count() == n0 + 2
+    f_a, lm_a = fe.features_and_logmel({n: v.contiguous() for n, v in views.items()})
+    assert torch.equal(lm_u, lm_a)
+    assert torch.allclose(f_u, f_a, rtol=1e-5, atol=1e-6)              # role loads and TMA rows sum in different orders
+    f_only = fe.extract_all_features(views)
+    assert torch.equal(f_only, f_u)
+    for i, c in enumerate(clips):
+        assert_features_close(f_u[i], O.mixing_features(c, cfg), fe.feature_names(), f"K1E hop={hop} n_mels={n_mels} T={T} clip {i}")
+        ref = O.log_mel({n: v[None] for n, v in c.items()}, cfg, dtype=torch.float64)
+        assert_logmel_close(lm_u[i:i + 1], ref, f"K1E hop={hop} n_mels={n_mels} T={T} clip {i}")
