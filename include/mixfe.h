@@ -5,7 +5,9 @@
  * (paths relative to the reference checkout).  All pointers marked "device" are CUDA device
  * pointers on the plan's device; every call is stream-ordered and asynchronous on `cuda_stream`
  * (a cudaStream_t passed as void*), never synchronises the host in steady state and never
- * allocates once the plan's workspace has reached its high-water mark.
+ * allocates once the plan's workspace has reached its high-water mark.  A plan serves ONE stream at a time: its
+ * workspace, its parameter staging ring and the work counters of its persistent kernels are per plan, so calls on one
+ * plan must not overlap on the GPU (use one plan per stream; plans are cheap).
  *
  * Return value: 0 on success, a negative MIXFE_E* code on failure; mixfe_last_error() returns a
  * thread-local human-readable message for the last failure on the calling thread.
