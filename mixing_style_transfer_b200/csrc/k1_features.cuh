@@ -758,24 +758,47 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
     __shared__ double sCurve[kNumStems][kMaxMels];
     __shared__ double sLogTot[kNumStems][4], sMelTot[kNumStems][4];
     __shared__ double sTd[kTdN];
+    __shared__ double sAcc[2][kNumStems][kMaxMels][2];   // (sum log, sum mel) per half of the tiles
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
     const double kDb = 4.342944819032518;            // 10 / ln(10)
 
-    // 1. spectral sums over tiles: thread = (stem, mel)
+    // 1. spectral sums over tiles.  The loop is bound by the latency of its loads (72 CTAs have few bytes in flight), so
+    //    a thread takes two filters (one 16-byte load) of HALF the tiles, 12 loads in flight; the halves meet in shared memory.
     {
+        const int h = tid >> 8, s = (tid >> 6) & 3, m2 = 2 * (tid & 63);
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};                 // (sum log, sum mel) of filters m2 and m2 + 1
+        if (m2 < p.n_mels_pad) {                              // n_mels_pad is a multiple of 16: m2 + 1 lies inside the row too
+            const float4* src = reinterpret_cast<const float4*>(
+                p.part_spec + ((long long)b * p.n_spec_tiles * kNumStems + s) * p.n_mels_pad + m2);
+            const long long step = (long long)kNumStems * p.n_mels_pad / 2;       // float4 per tile
+            const int t_mid = (p.n_spec_tiles + 1) / 2;
+            const int t0 = h ? t_mid : 0, t1 = h ? p.n_spec_tiles : t_mid;
+            constexpr int kU = 12;
+            for (int t = t0; t < t1; t += kU) {
+                float4 v[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) v[u] = t + u < t1 ? __ldg(src + (t + u) * step) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    acc[0] += (double)v[u].x; acc[1] += (double)v[u].y;
+                    acc[2] += (double)v[u].z; acc[3] += (double)v[u].w;
+                }
+            }
+        }
+        if (m2 < kMaxMels) {
+            sAcc[h][s][m2][0] = acc[0]; sAcc[h][s][m2][1] = acc[1];
+            sAcc[h][s][m2 + 1][0] = acc[2]; sAcc[h][s][m2 + 1][1] = acc[3];
+        }
+    }
+    __syncthreads();
+    {   // thread = (stem, mel); filters beyond n_mels (padding the kernels may leave unwritten) do not count
         const int s = tid >> 7, m = tid & 127;
         double slog = 0.0, smel = 0.0;
         if (m < p.n_mels) {
-            const float2* src = p.part_spec + ((long long)b * p.n_spec_tiles * kNumStems + s) * p.n_mels_pad + m;
-            const long long step = (long long)kNumStems * p.n_mels_pad;
-#pragma unroll 8
-            for (int t = 0; t < p.n_spec_tiles; ++t) {
-                const float2 v = __ldg(src + t * step);
-                slog += (double)v.x;
-                smel += (double)v.y;
-            }
+            slog = sAcc[0][s][m][0] + sAcc[1][s][m][0];
+            smel = sAcc[0][s][m][1] + sAcc[1][s][m][1];
             sE[s][m] = kDb * slog / (2.0 * p.F);
         } else if (m < kMaxMels) {
             sE[s][m] = 0.0;
@@ -795,6 +818,7 @@ __global__ void __launch_bounds__(kK2Threads) k2_finalize(const K2Params p) {
         if (used) {
             const float* src = p.part_td + (long long)b * p.n_tiles * (2 * kTdN);
             const int n_rec = 2 * p.n_tiles, step = (q >= 33 && q < 37) ? 2 : 1;          // K1G's masking sums live in record 0 only
+#pragma unroll 6
             for (int t = sub * step; t < n_rec; t += 8 * step) {
                 const float* r = src + (long long)t * kTdN;
                 double u = (double)__ldg(r + q);
