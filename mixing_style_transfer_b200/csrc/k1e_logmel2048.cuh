@@ -138,8 +138,7 @@ __global__ void __launch_bounds__(kEThreads, 2) k1e_logmel2048(const __grid_cons
 
     unsigned char* const region = ex + warp * kWarpRegion;
     float2* const exw = reinterpret_cast<float2*>(region);
-    unsigned char* const regE = ex + (2 * q) * kWarpRegion;        // the pair's even / odd regions
-    unsigned char* const regO = regE + kWarpRegion;
+    unsigned char* const regE = ex + (2 * q) * kWarpRegion;        // first of the two regions of the frame's warps (L, R)
 
     int b = (int)(item / p.n_tiles), tile = (int)(item - (long long)b * p.n_tiles);
     bool cur_tma = tile >= p.tma_lo && tile <= p.tma_hi;

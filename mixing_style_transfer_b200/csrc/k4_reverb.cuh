@@ -384,25 +384,25 @@ __global__ void __launch_bounds__(256, MIXFE_K4_ROWS_CTAS) k4_rows(const __grid_
         im[n1] = v.y;
     }
     warp_fft1024(re, im, exw, tw, lane);                              // X[row][lane + 32 k2]
-    if (MODE == kRowsH) {
+    if constexpr (MODE == kRowsH) {
 #pragma unroll
         for (int k2 = 0; k2 < 32; ++k2) Hs[32 * k2 + lane] = make_float2(re[k2], im[k2]);
-        return;
-    }
-    // correlation: R = X conj(H).  r = IFFT(R) = conj(FFT(conj(R)))/N and conj(R) = conj(X) H.
+    } else {
+        // correlation: R = X conj(H).  r = IFFT(R) = conj(FFT(conj(R)))/N and conj(R) = conj(X) H.
 #pragma unroll
-    for (int k2 = 0; k2 < 32; ++k2) {
-        const float2 h = Hs[32 * k2 + lane];
-        const float xr = re[k2], xi = -im[k2];
-        re[k2] = fmaf(xr, h.x, -xi * h.y);
-        im[k2] = fmaf(xr, h.y, xi * h.x);
-    }
-    warp_fft1024(re, im, exw, tw, lane);                              // now indexed by n2 = lane + 32 j
+        for (int k2 = 0; k2 < 32; ++k2) {
+            const float2 h = Hs[32 * k2 + lane];
+            const float xr = re[k2], xi = -im[k2];
+            re[k2] = fmaf(xr, h.x, -xi * h.y);
+            im[k2] = fmaf(xr, h.y, xi * h.x);
+        }
+        warp_fft1024(re, im, exw, tw, lane);                          // now indexed by n2 = lane + 32 j
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        const unsigned n2 = (unsigned)(lane + 32 * j);
-        const float2 w = twiddle_long(p.tw_lin, p.tw_fine, ((n2 * (unsigned)row) << G::kTwShift) & (unsigned)(kRevMaxN - 1));
-        Xs[n2] = make_float2(fmaf(re[j], w.x, -im[j] * w.y), fmaf(re[j], w.y, im[j] * w.x));
+        for (int j = 0; j < 32; ++j) {
+            const unsigned n2 = (unsigned)(lane + 32 * j);
+            const float2 w = twiddle_long(p.tw_lin, p.tw_fine, ((n2 * (unsigned)row) << G::kTwShift) & (unsigned)(kRevMaxN - 1));
+            Xs[n2] = make_float2(fmaf(re[j], w.x, -im[j] * w.y), fmaf(re[j], w.y, im[j] * w.x));
+        }
     }
 }
 
