@@ -181,7 +181,8 @@ class TripletPipeline:
     def run(self, host_stems: Dict[str, torch.Tensor], decisions, feat_out: torch.Tensor, lm_out: Optional[torch.Tensor]):
         """host_stems: dict of pinned (2G,2,T), anchors then positives; decisions: G augmentation decisions (a list of
         ClipAugmentation or the BatchAugmentation of AudioAugmenter.draw_batch); feat_out pinned (3G,D); lm_out pinned
-        (3G,8,n_mels,F) or None.  Returns after everything has landed in host memory."""
+        (3G,8,n_mels,F) or None.  Returns after everything has landed in host memory.  feat_out / lm_out may also be CUDA
+        tensors on the pipeline's device: the results then stay on the GPU (the encoder's input) and only the stems cross PCIe."""
         self.wait(self.submit(host_stems, decisions, feat_out, lm_out))
 
     wait = staticmethod(HostPipeline.wait)

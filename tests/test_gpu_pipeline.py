@@ -124,3 +124,26 @@ def test_triplet_pipeline_matches_resident(cuda_device, G, chunk, one_alloc):
     assert torch.equal(outs[1][0], want[1][0]) and torch.equal(outs[1][1], want[1][1])
     with pytest.raises(ValueError):
         pipe.run(host, decs[0].slice(0, G - 1) if G > 1 else [], *outs[0])
+
+
+def test_triplet_pipeline_outputs_may_stay_on_the_device(cuda_device):
+    """feat_out / lm_out may be CUDA tensors (the encoder consumes the log-mels on the GPU: only the stems cross PCIe)."""
+    from mixing_style_transfer_b200.pipeline import TripletPipeline
+    T, G = 20000, 5
+    fe = pkg.MixingFeatureExtractor()
+    aug = pkg.AudioAugmenter(prob=0.6)
+    clips = [O.musical_clip(400 + i, T) for i in range(2 * G)]
+    whole = HostPipeline.pinned_like((4, 2 * G, 2, T))
+    host = {name: whole[k] for k, name in enumerate(O.STEMS)}
+    for name in O.STEMS:
+        host[name].copy_(torch.stack([c[name] for c in clips]))
+    torch.manual_seed(5)
+    dec = aug.draw_batch(G, impulse_device=cuda_device)
+    pipe = TripletPipeline(fe, aug, G, T, chunk=2, device=cuda_device)
+    F = 1 + T // 256
+    hf, hl = HostPipeline.pinned_like((3 * G, 64)), HostPipeline.pinned_like((3 * G, 8, 128, F))
+    pipe.run(host, dec, hf, hl)
+    df = torch.full((3 * G, 64), -1.0, device=cuda_device)
+    dl = torch.full((3 * G, 8, 128, F), -1.0, device=cuda_device)
+    pipe.wait(pipe.submit(host, dec, df, dl))
+    assert torch.equal(df.cpu(), hf) and torch.equal(dl.cpu(), hl)
