@@ -610,6 +610,32 @@ def run_native(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             features_mel_ms = float(t.item())
 
+    # ---- "additionally a prob = 1.0 worst-case run (all five effects on every clip)" -----
+    worst_case = None
+    if with_aug and rank == 0:
+        aug1 = pkg.AudioAugmenter(prob=1.0)
+        plan1 = aug1._plan(dev)
+
+        def step1():
+            aug1.apply(anchors, aug1.draw_batch(N_TRI, impulse_device=dev), out=negatives)
+            plan.features_logmel(stems, True, True, features_out=f_out, logmel_out=lm_out)
+        for _ in range(3):
+            step1()
+        torch.cuda.synchronize()
+        plan1.enable_timing(True)
+        n1 = max(5, min(args.steps, 10))
+        w_ms = timed_loop(torch, step1, n1)
+        a_ms, a_n = plan1.kernel_time("augment")
+        r_ms, _ = plan1.kernel_time("reverb")
+        plan1.enable_timing(False)
+        worst_case = {"ms_per_step": w_ms, "k3_augment_ms": a_ms / max(1, a_n), "k4_reverb_ms_per_step": r_ms / n1, "steps": n1,
+                      "what": "the same step with prob = 1.0: gain, tilt, compressor, band-limit on every stem and reverb on "
+                              "all 24 negatives; not part of value"}
+        # the timed batch's negatives are gone: restore them so that later sections see what the parity check kept
+        aug.apply(anchors, last["dec"], out=negatives)
+        torch.cuda.synchronize()
+    barrier()
+
     # ---- all-gather into the global contrastive batch, timed on its own -----
     allgather = None
     if world > 1 and not args.no_allgather:
@@ -822,6 +848,8 @@ def run_native(args):
                 "kernels": kernels, "gpu_launches": launches, "clocks": clocks}
         if features_mel_ms is not None:
             line["features_mel_ms"] = features_mel_ms
+        if worst_case is not None:
+            line["augmentation_worst_case"] = worst_case
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         if e2e is not None:
