@@ -568,12 +568,17 @@ def run_native(args):
     torch.cuda.synchronize()
     sampler.mark_begin()
     n0 = pkg.launch_count()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps - 1)]     # step boundaries: median / min per step
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         step()
+        if i < args.steps - 1:
+            marks[i].record()
     e1.record()
     torch.cuda.synchronize()
     sampler.mark_end()
+    edges = [e0] + marks + [e1]
+    per_step = sorted(edges[i].elapsed_time(edges[i + 1]) for i in range(args.steps))
     barrier()
     launches = pkg.launch_count() - n0
     clocks = sampler.stop() if rank == 0 else None
@@ -846,6 +851,8 @@ def run_native(args):
                                   "note": "SURVEY.md section 8d: config 3 has the same compulsory traffic as config 2 (48 clips "
                                           "read, 24 negatives written and read back, 72 log-mels written)"},
                 "kernels": kernels, "gpu_launches": launches, "clocks": clocks}
+        line["ms_per_step_median"] = per_step[len(per_step) // 2]
+        line["ms_per_step_min"] = per_step[0]
         if features_mel_ms is not None:
             line["features_mel_ms"] = features_mel_ms
         if worst_case is not None:
