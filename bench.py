@@ -843,7 +843,7 @@ def run_native(args):
                 "config": config_dict(args.workload, world, args),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "kernel": "k1_features", "kernel_ms": k1, "peak_source": peak_src,
-                             "algorithmic_bytes_per_launch": alg,
+                             "algorithmic_bytes_per_launch": alg, "frac_of_nominal_8TBs": achieved / 8000.0,
                              "note": "K1 is bound by issue slots at 25 % occupancy (20 FLOP/B, no wasted DRAM traffic); the HBM "
                                      "fraction is what BASELINE.json asks for"},
                 "roofline_step": {"algorithmic_bytes_per_step": alg, "achieved": alg / (ms / 1e3) / 1e9, "peak": peak,
