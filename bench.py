@@ -846,6 +846,12 @@ def run_native(args):
                              "algorithmic_bytes_per_launch": alg, "frac_of_nominal_8TBs": achieved / 8000.0,
                              "note": "K1 is bound by issue slots at 25 % occupancy (20 FLOP/B, no wasted DRAM traffic); the HBM "
                                      "fraction is what BASELINE.json asks for"},
+                "roofline_fp32": {"bound": "fp32 CUDA cores (SURVEY.md section 8d: the STFT stage is FP32-pipe-bound, 20 FLOP/B)",
+                                  "algorithmic_flops_per_launch": N_CLIPS * 430.6e6,
+                                  "achieved": N_CLIPS * 430.6e6 / (k1 / 1e3) / 1e12, "peak": 74.4, "unit": "TFLOP/s",
+                                  "frac": N_CLIPS * 430.6e6 / (k1 / 1e3) / 1e12 / 74.4,
+                                  "peak_source": "148 SMs x 128 FP32 lanes x 2 FLOP x 1.965 GHz (nominal; no measured figure "
+                                                 "for the fp32 pipe in MEASURED_PEAKS.json)"},
                 "roofline_step": {"algorithmic_bytes_per_step": alg, "achieved": alg / (ms / 1e3) / 1e9, "peak": peak,
                                   "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / peak,
                                   "note": "SURVEY.md section 8d: config 3 has the same compulsory traffic as config 2 (48 clips "
