@@ -3,6 +3,8 @@ golden vectors of the real reference.  Tolerances are BASELINE.md section 5:
 features |d| <= 1e-4|ref| + 1e-5; mel power |d| <= 1e-4|ref| + 1e-6 * frame max; log-mel max-abs
 reported (the fp32 oracle itself is only good to ~1e-3 there)."""
 import numpy as np
+import os
+
 import pytest
 import torch
 
@@ -191,7 +193,8 @@ def test_thirty_second_clips_of_the_offline_sweep(fe, cuda_device):
     clip0 = {n: batch[n][0].cpu() for n in O.STEMS}
     assert_features_close(f[0], O.mixing_features(clip0), fe.feature_names(), "30 s clip 0")
     assert_logmel_close(lm[0:1], O.log_mel({n: v[None] for n, v in clip0.items()}, dtype=torch.float64), "30 s clip 0")
-    assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 2     # the shared-memory budget keeps 2 CTAs / SM
+    if os.environ.get("MIXFE_FORCE_GENERIC", "0") in ("", "0"):       # (the knob routes the plan through K1G)
+        assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 2     # the shared-memory budget keeps 2 CTAs / SM
 
 
 def test_full_size_properties(fe, cuda_device):

@@ -84,7 +84,8 @@ def test_irregular_configurations_vs_oracle(cuda_device, n_fft, hop, n_mels, T):
 def test_generic_kernel_serves_non_1024_plans(cuda_device):
     fe = pkg.MixingFeatureExtractor(44100, 2048, 512, 80)
     assert fe._plan(cuda_device).k1_config()["ctas_per_sm"] == 0          # K1G marker
-    assert pkg.MixingFeatureExtractor()._plan(cuda_device).k1_config()["ctas_per_sm"] >= 1
+    if os.environ.get("MIXFE_FORCE_GENERIC", "0") in ("", "0"):              # (the knob routes every plan through K1G)
+        assert pkg.MixingFeatureExtractor()._plan(cuda_device).k1_config()["ctas_per_sm"] >= 1
 
 
 def test_batched_2048_matches_per_clip(cuda_device):
