@@ -20,6 +20,7 @@
 #include "k4_reverb.cuh"
 #include "k7_loudness.cuh"
 #include "k8_mrstft.cuh"
+#include "k8f_mrstft1024.cuh"
 #include "k9_extensions.cuh"
 
 using namespace mixfe;
@@ -844,6 +845,19 @@ int stft_loss_common(mixfe_plan* pl, const float* x, const float* y, int B, int 
     return MIXFE_OK;
 }
 
+// K8F serves the (1024, 256) resolution (MIXFE_FORCE_GENERIC_LOSS=1: the generic kernels, for A/B runs)
+bool k8f_usable(const mixfe_plan* pl) {
+    static const bool forced = std::getenv("MIXFE_FORCE_GENERIC_LOSS") && std::atoi(std::getenv("MIXFE_FORCE_GENERIC_LOSS"));
+    return pl->n_fft == 1024 && pl->hop == 256 && pl->d_tw && !forced;
+}
+
+K8FParams k8f_params(const mixfe_plan* pl, const K8Params& p) {
+    K8FParams f{};
+    f.x = p.x; f.y = p.y; f.xs_b = p.xs_b; f.xs_c = p.xs_c; f.ys_b = p.ys_b; f.ys_c = p.ys_c;
+    f.rows = p.rows; f.C = p.C; f.T = p.T; f.F = p.F; f.n_tiles = p.n_tiles; f.tw = pl->d_tw;
+    return f;
+}
+
 int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B, int C, int T, long long xs_b, long long xs_c,
                           long long ys_b, long long ys_c, double* state, cudaStream_t stream) {
     K8Params p;
@@ -852,6 +866,25 @@ int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B,
     if (!state) return fail(MIXFE_EINVAL, "state is NULL");
     if (B == 0) return fail(MIXFE_EINVAL, "empty batch");
     DeviceGuard guard(pl->device);
+    if (k8f_usable(pl)) {
+        // K8F: the (1024, 256) resolution on the one-warp transform; same partial layout, same finish kernel
+        K8FParams f = k8f_params(pl, p);
+        f.off_tw = 8 * kWarpRegion; f.off_red = f.off_tw + 31 * 32 * 8;
+        const int smem_f = f.off_red + 8 * 3 * 4;
+        if ((rc = smem_optin(k8f_partials, pl->device, smem_f))) return rc;
+        rc = ensure_workspace(pl, sizeof(float) * 3 * (size_t)p.rows * p.n_tiles, stream);
+        if (rc) return rc;
+        f.part = p.part = reinterpret_cast<float*>(pl->ws);
+        p.state = state;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+            k8f_partials<<<dim3(p.n_tiles, p.rows), 256, smem_f, stream>>>(f);
+            k8_finish<<<1, 256, 0, stream>>>(p);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter() += 2;
+        return MIXFE_OK;
+    }
     int nf = kTF;
     while (nf > 1 && nf * fg_row(pl->n_fft) * 8 > 72 * 1024) nf >>= 1;
     p.nf = nf;
@@ -882,6 +915,22 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
     if (gs_c < T) return fail(MIXFE_EINVAL, "gradient channel stride smaller than T");
     if (B == 0) return MIXFE_OK;
     DeviceGuard guard(pl->device);
+    if (k8f_usable(pl)) {
+        K8FParams f = k8f_params(pl, p);
+        const int hlast = (T + 511) / 256;                           // last hop region the padded signal reaches (K6F's tiling)
+        f.n_tiles = (hlast + 3 + kBwOwn - 1) / kBwOwn;
+        f.off_tw = kBwWarps * kWarpRegion; f.off_ola = f.off_tw + 31 * 32 * 8;
+        const int smem_f = f.off_ola + kBwSpan * 4;
+        if ((rc = smem_optin(k8f_backward, pl->device, smem_f))) return rc;
+        f.state = state; f.gscale = gscale; f.gx = gx; f.gs_b = gs_b; f.gs_c = gs_c;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+            k8f_backward<<<dim3(f.n_tiles, p.rows), kBwThreads, smem_f, stream>>>(f);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter()++;
+        return MIXFE_OK;
+    }
     const int per = fg_row(pl->n_fft) * 8, ola = align16(p.span_pad * 4);
     if (per + ola > 200 * 1024) return fail(MIXFE_EUNSUPPORTED, "STFT loss backward: hop=%d needs too much shared memory", pl->hop);
     int nf = kTF;
