@@ -125,18 +125,21 @@ __global__ void __launch_bounds__(256, 2) k8e_partials(const __grid_constant__ K
         float2* const exw = reinterpret_cast<float2*>(smem + warp * kWarpRegion);
         const K8ELane c = k8e_lane(lane);
         cplx64 z[32];
-        float my[33];
+        // the target's 33 magnitudes per lane wait in shared memory ([i][lane]: conflict-free) while the prediction's frame is
+        // loaded and transformed: as registers they spilled (448 bytes of stack)
+        float* const my = reinterpret_cast<float*>(smem + p.off_red + 128) + warp * (33 * 32) + lane;
         k8e_load_frame(yr, t, p.T, lane, c.cb0, c.sb0, c.cb1, c.sb1, z);
         k8f_fft1024(z, exw, tw, lane);
-        k8e_magnitudes(z, c, lane, [&](int i, float m) { my[i] = m; });
+        k8e_magnitudes(z, c, lane, [&](int i, float m) { my[i * 32] = m; });
         k8e_load_frame(xr, t, p.T, lane, c.cb0, c.sb0, c.cb1, c.sb1, z);
         k8f_fft1024(z, exw, tw, lane);
         k8e_magnitudes(z, c, lane, [&](int i, float mx) {
             if (i < 32 || lane == 0) {
-                const float dm = my[i] - mx;
+                const float myv = my[i * 32];
+                const float dm = myv - mx;
                 a2 = fmaf(dm, dm, a2);
-                b2 = fmaf(my[i], my[i], b2);
-                l1 += fabsf(logf(mx + 1e-5f) - logf(my[i] + 1e-5f));
+                b2 = fmaf(myv, myv, b2);
+                l1 += fabsf(logf(mx + 1e-5f) - logf(myv + 1e-5f));
             }
         });
     }

@@ -877,7 +877,7 @@ int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B,
         const bool e = k8e_usable(pl);
         K8FParams f = k8f_params(pl, p);
         f.off_tw = 8 * kWarpRegion; f.off_red = f.off_tw + 31 * 32 * 8;
-        const int smem_f = f.off_red + 8 * 3 * 4;
+        const int smem_f = f.off_red + 128 + (e ? 8 * 33 * 32 * 4 : 0);          // K8E: + the target magnitudes of the 8 frames
         if ((rc = e ? smem_optin(k8e_partials, pl->device, smem_f) : smem_optin(k8f_partials, pl->device, smem_f))) return rc;
         rc = ensure_workspace(pl, sizeof(float) * 3 * (size_t)p.rows * p.n_tiles, stream);
         if (rc) return rc;
