@@ -52,3 +52,15 @@ print(f"loss: K8 {a:.6f}  torch {b:.6f}")
 print(f"K8    forward+backward: {timed(lambda: step(mod)):.3f} ms")
 print(f"K8    forward only:     {timed(lambda: mod(x.detach(), y)):.3f} ms")
 print(f"torch forward+backward: {timed(lambda: step(torch_loss)):.3f} ms   (peak memory {torch.cuda.max_memory_allocated() / 2**30:.2f} GiB)")
+
+# per-resolution kernel times (CUDA events inside libmixfe around the loss kernels of each plan)
+plans = mod._plans_for(dev)
+for pl in plans:
+    pl.enable_timing(True)
+for _ in range(10):
+    step(mod)
+torch.cuda.synchronize()
+for (n, h), pl in zip(zip(FFT, HOP), plans):
+    ms, cnt = pl.kernel_time("stft_loss")
+    pl.enable_timing(False)
+    print(f"  resolution ({n}, {h}): {ms / 10:.3f} ms per forward + backward ({cnt} timed brackets)")
