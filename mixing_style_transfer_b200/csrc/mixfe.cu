@@ -22,6 +22,7 @@
 #include "k8_mrstft.cuh"
 #include "k8f_mrstft1024.cuh"
 #include "k8e_mrstft2048.cuh"
+#include "k8h_mrstft512.cuh"
 #include "k9_extensions.cuh"
 
 using namespace mixfe;
@@ -851,6 +852,11 @@ bool k8f_usable(const mixfe_plan* pl) {
     static const bool forced = std::getenv("MIXFE_FORCE_GENERIC_LOSS") && std::atoi(std::getenv("MIXFE_FORCE_GENERIC_LOSS"));
     return pl->n_fft == 1024 && pl->hop == 256 && pl->d_tw && !forced;
 }
+// K8H serves the (512, 128) resolution
+bool k8h_usable(const mixfe_plan* pl) {
+    static const bool forced = std::getenv("MIXFE_FORCE_GENERIC_LOSS") && std::atoi(std::getenv("MIXFE_FORCE_GENERIC_LOSS"));
+    return pl->n_fft == 512 && pl->hop == 128 && pl->d_tw && !forced;
+}
 // K8E serves the (2048, 512) resolution
 bool k8e_usable(const mixfe_plan* pl) {
     static const bool forced = std::getenv("MIXFE_FORCE_GENERIC_LOSS") && std::atoi(std::getenv("MIXFE_FORCE_GENERIC_LOSS"));
@@ -872,6 +878,24 @@ int run_stft_loss_forward(mixfe_plan* pl, const float* x, const float* y, int B,
     if (!state) return fail(MIXFE_EINVAL, "state is NULL");
     if (B == 0) return fail(MIXFE_EINVAL, "empty batch");
     DeviceGuard guard(pl->device);
+    if (k8h_usable(pl)) {
+        K8FParams f = k8f_params(pl, p);
+        f.off_tw = 4 * kHRegion; f.off_red = f.off_tw + 1024 * 8;
+        const int smem_f = f.off_red + 128;
+        if ((rc = smem_optin(k8h_partials, pl->device, smem_f))) return rc;
+        rc = ensure_workspace(pl, sizeof(float) * 3 * (size_t)p.rows * p.n_tiles, stream);
+        if (rc) return rc;
+        f.part = p.part = reinterpret_cast<float*>(pl->ws);
+        p.state = state;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+            k8h_partials<<<dim3(p.n_tiles, p.rows), 128, smem_f, stream>>>(f);
+            k8_finish<<<1, 256, 0, stream>>>(p);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter() += 2;
+        return MIXFE_OK;
+    }
     if (k8f_usable(pl) || k8e_usable(pl)) {
         // K8F / K8E: the (1024, 256) / (2048, 512) resolution on the one-warp transform; same partial layout, same finish
         const bool e = k8e_usable(pl);
@@ -934,6 +958,22 @@ int run_stft_loss_backward(mixfe_plan* pl, const float* x, const float* y, int B
         {
             KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
             k8f_backward<<<dim3(f.n_tiles, p.rows), kBwThreads, smem_f, stream>>>(f);
+        }
+        MIXFE_CUDA(cudaGetLastError());
+        launch_counter()++;
+        return MIXFE_OK;
+    }
+    if (k8h_usable(pl)) {
+        K8FParams f = k8f_params(pl, p);
+        const int hlast = (T + 255) / 128;                           // last hop region the padded signal reaches
+        f.n_tiles = (hlast + 3 + kHOwn - 1) / kHOwn;
+        f.off_tw = 16 * kHRegion; f.off_ola = f.off_tw + 1024 * 8;
+        const int smem_f = f.off_ola + kHSpan * 4;
+        if ((rc = smem_optin(k8h_backward, pl->device, smem_f))) return rc;
+        f.state = state; f.gscale = gscale; f.gx = gx; f.gs_b = gs_b; f.gs_c = gs_c;
+        {
+            KernelTimer timer(pl, MIXFE_KERNEL_STFT_LOSS, stream);
+            k8h_backward<<<dim3(f.n_tiles, p.rows), 512, smem_f, stream>>>(f);
         }
         MIXFE_CUDA(cudaGetLastError());
         launch_counter()++;
