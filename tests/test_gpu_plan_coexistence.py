@@ -85,3 +85,28 @@ def test_output_buffers_are_validated(cuda_device):
     d = [aug.draw(), aug.draw()]
     with pytest.raises(ValueError, match="overlaps"):
         aug.apply({n: v[0:2] for n, v in buf.items()}, d, out={n: v[1:3] for n, v in buf.items()})
+
+
+def test_work_counters_survive_changing_grids(cuda_device):
+    """K1 / K1E hand out tiles through two per-plan counters that the last CTA of a launch rezeroes: launches whose grids
+    differ (1 clip, many clips, SMs reserved, short clips with fewer tiles than SMs) must leave them clean for the next."""
+    T = 30000
+    clips = [O.musical_clip(800 + i, T) for i in range(5)]
+    for cfg in ((44100, 1024, 256, 128), (44100, 2048, 512, 80)):
+        fe = pkg.MixingFeatureExtractor(*cfg)
+        plan = fe._plan(cuda_device)
+        batch = {n: torch.stack([c[n] for c in clips]).to(cuda_device) for n in O.STEMS}
+        f_ref, lm_ref = fe.features_and_logmel(batch)
+        for rounds in range(3):
+            for k in (1, 5, 2):
+                sub = {n: v[:k] for n, v in batch.items()}
+                f, lm = fe.features_and_logmel(sub)
+                assert torch.equal(f, f_ref[:k]) and torch.equal(lm, lm_ref[:k])
+            plan.reserve_sms(100)                        # a much smaller persistent grid
+            f, lm = fe.features_and_logmel(batch)
+            plan.reserve_sms(0)
+            assert torch.equal(f, f_ref) and torch.equal(lm, lm_ref)
+            short = {n: v[:1, :, :3000] for n, v in batch.items()}      # fewer tiles than SMs
+            f1, _ = fe.features_and_logmel(short)
+            f2, _ = fe.features_and_logmel(short)
+            assert torch.equal(f1, f2)
